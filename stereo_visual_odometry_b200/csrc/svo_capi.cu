@@ -1,0 +1,925 @@
+// svo_capi.cu -- C-ABI host layer (include/svo.h) over the sm_100a kernels.
+//
+// Owns the device-resident state of VisualOdometry (include/vo.h:233-268 of the
+// reference): frame id, the t0/t1 image pyramids, currentVOFeatures, the rotation /
+// translation guess and last_transform, for n_seq independent sequences.  One CUDA
+// stream per context; the per-frame chain is stream-ordered with device-side
+// predicates for every branch of stereo_callback (vo.cpp:41-137), so the host never
+// has to look at intermediate results.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "svo_kernels.cuh"
+
+using namespace svo;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                            \
+            return (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver) ? SVO_ERR_NO_DEVICE \
+                                                                                   : SVO_ERR_CUDA;  \
+        }                                                                                          \
+    } while (0)
+
+extern "C" const char* svo_version(void) { return "svo-b200 0.1 (sm_100a)"; }
+extern "C" const char* svo_last_error(void) { return g_err.c_str(); }
+extern "C" int svo_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SVO_ERR_NO_DEVICE, cudaGetErrorString(e));
+    }
+    return n;
+}
+
+extern "C" void svo_default_params(svo_params* p, int width, int height) {
+    memset(p, 0, sizeof(*p));
+    p->width = width;
+    p->height = height;
+    p->n_seq = 1;
+    p->buckets_along_height = 92;
+    p->buckets_along_width = 160;
+    p->bucket_start_row = 4;
+    p->features_per_bucket = 1;
+    p->features_threshold = 15;
+    p->pre_matching_threshold = 100;
+    p->age_threshold = 20;
+    p->fast_threshold = 20;
+    p->win_size = 10;
+    p->max_level = 3;
+    p->lk_max_iters = 30;
+    p->lk_epsilon = 1e-4f;
+    p->lk_min_eig = 1e-3f;
+    p->circular_threshold = 0.15f;
+    p->ransac_reproj_error = 8.f;
+    p->ransac_iterations = 100;
+    p->ransac_hypotheses = 256;
+    p->ransac_confidence = 0.98f;
+    p->max_translation_norm = 0.1;
+    p->max_rotation_norm = 0.5;
+    p->ransac_seed = 0x5eed5eedULL;
+    p->device = 0;
+}
+
+// ---------------------------------------------------------------------------
+struct svo_ctx {
+    svo_params p;
+    PyrGeom pg;
+    BucketGeom bg;
+    PipeConfig pc;
+    DevArrays d;
+    cudaStream_t stream = nullptr;
+    std::vector<void*> allocs;
+    uint8_t* stage_L = nullptr;
+    uint8_t* stage_R = nullptr;
+    svo_frame_result* host_result = nullptr;   // pinned
+    long long frames = 0;
+    long long launches = 0;
+    bool have_projection = false;
+    // timers
+    bool timers = false;
+    cudaEvent_t ev[6];
+    double stage_ms[5] = {0, 0, 0, 0, 0};
+    long long stage_launches[5] = {0, 0, 0, 0, 0};
+};
+
+static BucketGeom make_bucket_geom(int height, int width, int n_bh, int n_bw, int start_row, int age_thr,
+                                   int fast_thr) {
+    BucketGeom bg;
+    bg.n_bh = n_bh;
+    bg.n_bw = n_bw;
+    bg.bh = (height + n_bh - 1) / n_bh;
+    bg.bw = (width + n_bw - 1) / n_bw;
+    bg.start_row = start_row;
+    bg.age_threshold = age_thr;
+    bg.fast_threshold = fast_thr;
+    bg.nb = n_bh * n_bw;
+    return bg;
+}
+
+// cv::buildOpticalFlowPyramid stops when a level would be <= winSize in either dimension
+static PyrGeom make_pyr_geom(int w, int h, int max_level, int win) {
+    PyrGeom pg;
+    memset(&pg, 0, sizeof(pg));
+    long long off = 0;
+    int lw = w, lh = h, l = 0;
+    for (; l <= max_level && l < SVO_MAX_LEVELS; ++l) {
+        if (l > 0) {
+            const int nw = (lw + 1) / 2, nh = (lh + 1) / 2;
+            if (nw <= win || nh <= win) break;
+            lw = nw;
+            lh = nh;
+        }
+        pg.w[l] = lw;
+        pg.h[l] = lh;
+        pg.pitch[l] = (lw + 127) & ~127;
+        pg.off[l] = off;
+        off += (long long)pg.pitch[l] * lh;
+    }
+    pg.nlevels = l;
+    for (int k = l; k < SVO_MAX_LEVELS; ++k) {   // keep unused levels pointing at valid memory
+        pg.w[k] = pg.w[l - 1];
+        pg.h[k] = pg.h[l - 1];
+        pg.pitch[k] = pg.pitch[l - 1];
+        pg.off[k] = pg.off[l - 1];
+    }
+    pg.image_bytes = (off + 255) & ~255ll;
+    return pg;
+}
+
+static LkConfig make_lk_config(const svo_params& p, int nlevels) {
+    LkConfig c;
+    c.nlevels = nlevels;
+    c.max_iters = p.lk_max_iters < 0 ? 0 : (p.lk_max_iters > 100 ? 100 : p.lk_max_iters);
+    double e = p.lk_epsilon < 0.f ? 0.0 : (p.lk_epsilon > 10.f ? 10.0 : (double)p.lk_epsilon);
+    c.eps_sq = e * e;
+    c.min_eig = p.lk_min_eig;
+    return c;
+}
+
+template <class T>
+static cudaError_t dev_alloc(svo_ctx* c, T** ptr, size_t count, bool zero = true) {
+    void* q = nullptr;
+    const size_t bytes = (count ? count : 1) * sizeof(T);
+    cudaError_t e = cudaMalloc(&q, bytes);
+    if (e != cudaSuccess) return e;
+    c->allocs.push_back(q);
+    if (zero) e = cudaMemsetAsync(q, 0, bytes, c->stream);
+    *ptr = (T*)q;
+    return e;
+}
+
+static int validate_params(const svo_params* p) {
+    if (!p) return fail(SVO_ERR_INVALID, "params is NULL");
+    if (p->width < 16 || p->height < 16 || p->width > 8192 || p->height > 8192)
+        return fail(SVO_ERR_INVALID, "image size out of range (16..8192)");
+    if ((long long)p->width * p->height >= (1ll << 24)) return fail(SVO_ERR_INVALID, "image has >= 2^24 pixels");
+    if (p->n_seq < 1) return fail(SVO_ERR_INVALID, "n_seq < 1");
+    if (p->win_size != SVO_LK_WIN) return fail(SVO_ERR_INVALID, "only winSize 10x10 (vo.h:251) is built");
+    if (p->max_level < 0 || p->max_level >= SVO_MAX_LEVELS) return fail(SVO_ERR_INVALID, "max_level must be 0..3");
+    if (p->buckets_along_height < 1 || p->buckets_along_width < 1) return fail(SVO_ERR_INVALID, "bad bucket grid");
+    if (p->fast_threshold < 4 || p->fast_threshold > 255) return fail(SVO_ERR_INVALID, "fast_threshold must be 4..255");
+    if (p->ransac_hypotheses < 1 || p->ransac_hypotheses > 4096)
+        return fail(SVO_ERR_INVALID, "ransac_hypotheses must be 1..4096");
+    return SVO_OK;
+}
+
+static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
+    c->p = *p;
+    CU(cudaSetDevice(p->device));
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size);
+    c->bg = make_bucket_geom(p->height, p->width, p->buckets_along_height, p->buckets_along_width,
+                             p->bucket_start_row, p->age_threshold, p->fast_threshold);
+    PipeConfig& pc = c->pc;
+    memset(&pc, 0, sizeof(pc));
+    pc.width = p->width;
+    pc.height = p->height;
+    pc.features_threshold = p->features_threshold;
+    pc.pre_matching_threshold = p->pre_matching_threshold;
+    pc.thr_hi = p->fast_threshold;
+    pc.thr_lo = p->fast_threshold / 4;
+    pc.circular_threshold = p->circular_threshold;
+    pc.reproj_thr_sq = (float)((double)p->ransac_reproj_error * (double)p->ransac_reproj_error);
+    pc.max_t_norm = p->max_translation_norm;
+    pc.max_r_norm = p->max_rotation_norm;
+    pc.seed = p->ransac_seed;
+    pc.lk = make_lk_config(*p, c->pg.nlevels);
+    pc.check_bounds = 1;
+    pc.age_increment = 1;
+
+    DevArrays& d = c->d;
+    memset(&d, 0, sizeof(d));
+    d.n_seq = p->n_seq;
+    d.n_hyp = p->ransac_hypotheses;
+    int cap = c->bg.nb;   // one feature per bucket at most
+    if (cap_override > cap) cap = cap_override;
+    d.cap = cap;
+    const size_t S = (size_t)p->n_seq, C = S * (size_t)cap;
+    CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 4 * S));
+    CU(dev_alloc(c, &d.fastkeys, (size_t)4 * S * c->bg.nb));
+    CU(dev_alloc(c, &d.trackkeys, S * c->bg.nb));
+    CU(dev_alloc(c, &d.state, S));
+    CU(dev_alloc(c, &d.result, S));
+    CU(dev_alloc(c, &d.fs_xy, C));  CU(dev_alloc(c, &d.fs_age, C));  CU(dev_alloc(c, &d.fs_str, C));
+    CU(dev_alloc(c, &d.bk_xy, C));  CU(dev_alloc(c, &d.bk_age, C));  CU(dev_alloc(c, &d.bk_str, C));
+    CU(dev_alloc(c, &d.lk_L1, C));  CU(dev_alloc(c, &d.lk_R1, C));   CU(dev_alloc(c, &d.lk_R0, C));
+    CU(dev_alloc(c, &d.lk_C, C));   CU(dev_alloc(c, &d.lk_status, C));
+    CU(dev_alloc(c, &d.m_L0, C));   CU(dev_alloc(c, &d.m_L1, C));    CU(dev_alloc(c, &d.m_R0, C));
+    CU(dev_alloc(c, &d.m_R1, C));   CU(dev_alloc(c, &d.m_age, C));   CU(dev_alloc(c, &d.m_str, C));
+    CU(dev_alloc(c, &d.X3, C * 3));
+    CU(dev_alloc(c, &d.hyp_pose, S * d.n_hyp * 12));
+    CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
+    CU(dev_alloc(c, &d.inl_idx, C));
+    CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S, false));
+    CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S, false));
+    CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S));
+    // initial state: rotation = I, translation = 0, last_transform = I (vo.h:262-264)
+    std::vector<SeqState> init(S);
+    memset(init.data(), 0, sizeof(SeqState) * S);
+    for (size_t s = 0; s < S; ++s) {
+        init[s].R[0] = init[s].R[4] = init[s].R[8] = 1.0;
+        init[s].last_T[0] = init[s].last_T[5] = init[s].last_T[10] = init[s].last_T[15] = 1.0;
+    }
+    CU(cudaMemcpyAsync(d.state, init.data(), sizeof(SeqState) * S, cudaMemcpyHostToDevice, c->stream));
+    for (int i = 0; i < 6; ++i) CU(cudaEventCreate(&c->ev[i]));
+    CU(cudaStreamSynchronize(c->stream));
+    return SVO_OK;
+}
+
+static svo_ctx* ctx_create(const svo_params* p, int cap_override) {
+    if (validate_params(p) != SVO_OK) return nullptr;
+    if (svo_device_count() <= 0) {
+        if (g_err.empty()) g_err = "no CUDA device";
+        return nullptr;
+    }
+    svo_ctx* c = new svo_ctx();
+    if (ctx_init(c, p, cap_override) != SVO_OK) {
+        std::string keep = g_err;
+        svo_destroy(c);
+        g_err = keep;
+        return nullptr;
+    }
+    return c;
+}
+
+extern "C" svo_ctx* svo_create(const svo_params* p) {
+    if (p && p->features_per_bucket != 1) {
+        fail(SVO_ERR_INVALID, "the pipeline context is built for FEATURES_PER_BUCKET == 1 (vo.h); use svo_bucket_filter for other values");
+        return nullptr;
+    }
+    return ctx_create(p, 0);
+}
+
+extern "C" void svo_destroy(svo_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->p.device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (void* q : c->allocs) cudaFree(q);
+    if (c->host_result) cudaFreeHost(c->host_result);
+    if (c->stream) {
+        for (int i = 0; i < 6; ++i)
+            if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+        cudaStreamDestroy(c->stream);
+    }
+    delete c;
+}
+
+extern "C" int svo_set_projection(svo_ctx* c, const float Pl[12], const float Pr[12]) {
+    if (!c || !Pl || !Pr) return fail(SVO_ERR_INVALID, "NULL argument");
+    memcpy(c->pc.Pl, Pl, sizeof(float) * 12);
+    memcpy(c->pc.Pr, Pr, sizeof(float) * 12);
+    // left_camera_matrix = P_left[:, :3] (vo.cpp:16-25); projectPoints reads fx, fy, cx, cy
+    c->pc.K.fx = Pl[0];
+    c->pc.K.fy = Pl[5];
+    c->pc.K.cx = Pl[2];
+    c->pc.K.cy = Pl[6];
+    c->have_projection = true;
+    return SVO_OK;
+}
+
+extern "C" void* svo_stream(svo_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" long long svo_launch_count(svo_ctx* c) { return c ? c->launches : 0; }
+
+extern "C" int svo_enable_timers(svo_ctx* c, int on) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    c->timers = on != 0;
+    return SVO_OK;
+}
+extern "C" int svo_reset_timers(svo_ctx* c) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    for (int i = 0; i < 5; ++i) {
+        c->stage_ms[i] = 0;
+        c->stage_launches[i] = 0;
+    }
+    return SVO_OK;
+}
+extern "C" int svo_get_stage_time(svo_ctx* c, int stage, double* ms_out, long long* launches_out) {
+    if (!c || stage < 0 || stage >= 5) return fail(SVO_ERR_INVALID, "bad stage");
+    if (ms_out) *ms_out = c->stage_ms[stage];
+    if (launches_out) *launches_out = c->stage_launches[stage];
+    return SVO_OK;
+}
+
+// The stream-ordered per-frame chain.  Images are device pointers.
+static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
+                         svo_frame_result* results_dev) {
+    const bool first = c->frames == 0;
+    const int parity = (int)(c->frames & 1);
+    const bool tm = c->timers;
+    cudaStream_t st = c->stream;
+    if (tm) cudaEventRecord(c->ev[0], st);
+    launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, first ? 1 : 0, parity, st);
+    const int n_ingest = 1 + (c->pg.nlevels - 1) + 1;
+    c->launches += n_ingest;
+    if (tm) cudaEventRecord(c->ev[1], st);
+    if (first) {
+        launch_first_frame(c->d, st);
+        c->launches += 1;
+    } else {
+        launch_bucket_merge(c->d, c->bg, c->pc, parity ^ 1, st);   // FAST winners of the PREVIOUS left image
+        if (tm) cudaEventRecord(c->ev[2], st);
+        launch_klt(c->d, c->pg, c->pc, st);
+        if (tm) cudaEventRecord(c->ev[3], st);
+        launch_select(c->d, c->pc, st);
+        if (tm) cudaEventRecord(c->ev[4], st);
+        launch_pnp(c->d, c->pc, st);
+        if (tm) cudaEventRecord(c->ev[5], st);
+        c->launches += 5;
+    }
+    if (results_dev)
+        CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, st));
+    CU(cudaGetLastError());
+    if (tm) {
+        CU(cudaStreamSynchronize(st));
+        const int nst = first ? 1 : 5;
+        const int nl[5] = {n_ingest, 1, 1, 1, 2};
+        for (int i = 0; i < nst; ++i) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]);
+            c->stage_ms[i] += ms;
+            c->stage_launches[i] += nl[i];
+        }
+    }
+    c->frames += 1;
+    return SVO_OK;
+}
+
+extern "C" int svo_process_frame_batch_dev(svo_ctx* c, const uint8_t* left_dev, const uint8_t* right_dev, int stride,
+                                           long long seq_stride, svo_frame_result* results_dev) {
+    if (!c || !left_dev || !right_dev) return fail(SVO_ERR_INVALID, "NULL argument");
+    if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
+    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    CU(cudaSetDevice(c->p.device));
+    return enqueue_frame(c, left_dev, right_dev, stride, seq_stride, results_dev);
+}
+
+extern "C" int svo_process_frame_batch(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride,
+                                       long long seq_stride, svo_frame_result* results) {
+    if (!c || !left || !right) return fail(SVO_ERR_INVALID, "NULL argument");
+    if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
+    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    CU(cudaSetDevice(c->p.device));
+    const int S = c->d.n_seq, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
+    const long long plane = (long long)P0 * H;
+    if (S == 1 || seq_stride == (long long)stride * H) {
+        CU(cudaMemcpy2DAsync(c->stage_L, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpy2DAsync(c->stage_R, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, c->stream));
+    } else {
+        for (int s = 0; s < S; ++s) {
+            CU(cudaMemcpy2DAsync(c->stage_L + s * plane, P0, left + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, c->stream));
+            CU(cudaMemcpy2DAsync(c->stage_R + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, c->stream));
+        }
+    }
+    int rc = enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr);
+    if (rc != SVO_OK) return rc;
+    CU(cudaMemcpyAsync(c->host_result, c->d.result, sizeof(svo_frame_result) * S, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    int ok = 0;
+    for (int s = 0; s < S; ++s) ok += c->host_result[s].success ? 1 : 0;
+    if (results) memcpy(results, c->host_result, sizeof(svo_frame_result) * S);
+    return ok;
+}
+
+extern "C" int svo_process_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, double T_out[16]) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    if (c->d.n_seq != 1) return fail(SVO_ERR_INVALID, "svo_process_frame needs a context with n_seq == 1");
+    int rc = svo_process_frame_batch(c, left, right, stride, 0, nullptr);
+    if (rc < 0) return rc;
+    if (T_out) memcpy(T_out, c->host_result[0].transform, sizeof(double) * 16);
+    return c->host_result[0].success ? 1 : 0;
+}
+
+extern "C" int svo_synchronize(svo_ctx* c) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    CU(cudaSetDevice(c->p.device));
+    CU(cudaStreamSynchronize(c->stream));
+    return SVO_OK;
+}
+
+extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
+    if (!c || !out || seq < 0 || seq >= c->d.n_seq) return fail(SVO_ERR_INVALID, "bad argument");
+    CU(cudaSetDevice(c->p.device));
+    CU(cudaMemcpyAsync(c->host_result + seq, c->d.result + seq, sizeof(svo_frame_result), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *out = c->host_result[seq];
+    return SVO_OK;
+}
+
+extern "C" int svo_get_tap(svo_ctx* c, int seq, int which, int cap, float* f_out, int* i_out, uint8_t* u8_out) {
+    if (!c || seq < 0 || seq >= c->d.n_seq || cap < 0) return fail(SVO_ERR_INVALID, "bad argument");
+    CU(cudaSetDevice(c->p.device));
+    CU(cudaStreamSynchronize(c->stream));
+    SeqState s;
+    CU(cudaMemcpy(&s, c->d.state + seq, sizeof(s), cudaMemcpyDeviceToHost));
+    const DevArrays& d = c->d;
+    const size_t fo = (size_t)seq * d.cap;
+    auto get = [&](void* dst, const void* src, size_t bytes) { return cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost); };
+    int n = 0;
+    if (which == 0 || which == 1) n = s.n_bucketed;
+    else if (which == 2) n = s.n_matched;
+    else if (which == 3) n = s.n_feat;
+    else return fail(SVO_ERR_INVALID, "bad tap id");
+    const int m = n < cap ? n : cap;
+    if (m == 0) return n;
+    if (which == 0 || which == 3) {
+        const float2* xy = which == 0 ? d.bk_xy : d.fs_xy;
+        const int* age = which == 0 ? d.bk_age : d.fs_age;
+        const int* str = which == 0 ? d.bk_str : d.fs_str;
+        if (f_out) CU(get(f_out, xy + fo, sizeof(float2) * m));
+        if (i_out) {
+            CU(get(i_out, age + fo, sizeof(int) * m));
+            CU(get(i_out + cap, str + fo, sizeof(int) * m));
+        }
+    } else if (which == 1) {
+        if (f_out) {
+            CU(get(f_out + 0 * 2 * (size_t)cap, d.lk_L1 + fo, sizeof(float2) * m));
+            CU(get(f_out + 1 * 2 * (size_t)cap, d.lk_R1 + fo, sizeof(float2) * m));
+            CU(get(f_out + 2 * 2 * (size_t)cap, d.lk_R0 + fo, sizeof(float2) * m));
+            CU(get(f_out + 3 * 2 * (size_t)cap, d.lk_C + fo, sizeof(float2) * m));
+        }
+        if (u8_out) CU(get(u8_out, d.lk_status + fo, m));
+    } else {
+        if (f_out) {
+            CU(get(f_out + 0 * 2 * (size_t)cap, d.m_L0 + fo, sizeof(float2) * m));
+            CU(get(f_out + 1 * 2 * (size_t)cap, d.m_L1 + fo, sizeof(float2) * m));
+            CU(get(f_out + 2 * 2 * (size_t)cap, d.m_R0 + fo, sizeof(float2) * m));
+            CU(get(f_out + 3 * 2 * (size_t)cap, d.m_R1 + fo, sizeof(float2) * m));
+            CU(get(f_out + 4 * 2 * (size_t)cap, d.X3 + fo * 3, sizeof(float) * 3 * m));
+        }
+        if (i_out) CU(get(i_out, d.inl_idx + fo, sizeof(int) * (s.n_inliers < cap ? s.n_inliers : cap)));
+    }
+    return n;
+}
+
+// ===========================================================================
+// Stage-level entry points.  Each call stages its operands in fresh device buffers,
+// runs the same kernels the pipeline uses, and copies the result back.
+namespace {
+struct Scratch {
+    std::vector<void*> ptrs;
+    cudaStream_t st = nullptr;
+    ~Scratch() {
+        for (void* p : ptrs) cudaFree(p);
+        if (st) cudaStreamDestroy(st);
+    }
+    template <class T>
+    cudaError_t alloc(T** p, size_t count) {
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc(&q, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(q);
+        *p = (T*)q;
+        return e;
+    }
+};
+int need_device() {
+    int n = svo_device_count();
+    if (n <= 0) return n < 0 ? n : fail(SVO_ERR_NO_DEVICE, "no CUDA device");
+    return SVO_OK;
+}
+}  // namespace
+
+extern "C" int svo_fast_detect(const uint8_t* img, int width, int height, int stride, int threshold, float* xy_out,
+                               float* resp_out, int cap) {
+    if (!img || width < 7 || height < 7 || stride < width || threshold < 1 || threshold > 254 || cap < 0)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    const int pitch = (width + 127) & ~127;
+    uint8_t *dimg, *dmap;
+    int *rows, *dn;
+    float2* dxy;
+    float* dresp;
+    CU(s.alloc(&dimg, (size_t)pitch * height));
+    CU(s.alloc(&dmap, (size_t)pitch * height));
+    CU(s.alloc(&rows, (size_t)height + 1));
+    CU(s.alloc(&dn, 1));
+    CU(s.alloc(&dxy, (size_t)cap));
+    CU(s.alloc(&dresp, (size_t)cap));
+    CU(cudaMemcpy2DAsync(dimg, pitch, img, stride, width, height, cudaMemcpyHostToDevice, s.st));
+    BucketGeom bg;
+    memset(&bg, 0, sizeof(bg));
+    launch_fast(dimg, 0, width, height, pitch, 1, threshold, threshold, dmap, 0, pitch, nullptr, nullptr, bg, s.st);
+    launch_compact_keypoints(dmap, width, height, pitch, threshold, rows, dxy, dresp, cap, dn, s.st);
+    int n = 0;
+    CU(cudaMemcpyAsync(&n, dn, sizeof(int), cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    const int m = n < cap ? n : cap;
+    if (m > 0) {
+        if (xy_out) CU(cudaMemcpy(xy_out, dxy, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        if (resp_out) CU(cudaMemcpy(resp_out, dresp, sizeof(float) * m, cudaMemcpyDeviceToHost));
+    }
+    return n;
+}
+
+extern "C" int svo_bucket_filter(float* xy, int* ages, int* strengths, int n, int image_height, int image_width,
+                                 int buckets_along_height, int buckets_along_width, int bucket_start_row,
+                                 int features_per_bucket, int age_threshold, int fast_threshold) {
+    if (n < 0 || (n > 0 && (!xy || !ages || !strengths)) || image_height < 1 || image_width < 1 ||
+        buckets_along_height < 1 || buckets_along_width < 1 || features_per_bucket < 0 ||
+        (long long)buckets_along_height * buckets_along_width * (features_per_bucket > 0 ? features_per_bucket : 1) > (1ll << 28))
+        return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    BucketGeom bg = make_bucket_geom(image_height, image_width, buckets_along_height, buckets_along_width,
+                                     bucket_start_row, age_threshold, fast_threshold);
+    const int pb = features_per_bucket;
+    float2 *dxy, *oxy;
+    int *dage, *dstr, *oage, *ostr, *scratch, *dn;
+    const size_t out_cap = (size_t)n;
+    CU(s.alloc(&dxy, (size_t)n));   CU(s.alloc(&dage, (size_t)n));   CU(s.alloc(&dstr, (size_t)n));
+    CU(s.alloc(&oxy, out_cap));     CU(s.alloc(&oage, out_cap));     CU(s.alloc(&ostr, out_cap));
+    CU(s.alloc(&scratch, (size_t)n + 2 * (size_t)bg.nb + 1 + (size_t)bg.nb * (pb > 0 ? pb : 1)));
+    CU(s.alloc(&dn, 1));
+    if (n > 0) {
+        CU(cudaMemcpyAsync(dxy, xy, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+        CU(cudaMemcpyAsync(dage, ages, sizeof(int) * n, cudaMemcpyHostToDevice, s.st));
+        CU(cudaMemcpyAsync(dstr, strengths, sizeof(int) * n, cudaMemcpyHostToDevice, s.st));
+    }
+    launch_bucket_generic(dxy, dage, dstr, n, bg, pb, scratch, oxy, oage, ostr, dn, s.st);
+    int m = 0;
+    CU(cudaMemcpyAsync(&m, dn, sizeof(int), cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    if (m > 0) {
+        CU(cudaMemcpy(xy, oxy, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(ages, oage, sizeof(int) * m, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(strengths, ostr, sizeof(int) * m, cudaMemcpyDeviceToHost));
+    }
+    return m;
+}
+
+// device pyramid built with the generic pyrdown kernel
+namespace {
+struct DevPyr {
+    PyrGeom pg;
+    uint8_t* base = nullptr;
+    LkPyramid lk() const {
+        LkPyramid p;
+        for (int l = 0; l < SVO_MAX_LEVELS; ++l) {
+            p.lv[l].img = base + pg.off[l];
+            p.lv[l].w = pg.w[l];
+            p.lv[l].h = pg.h[l];
+            p.lv[l].pitch = pg.pitch[l];
+        }
+        return p;
+    }
+};
+int build_dev_pyr(Scratch& s, DevPyr& out, const uint8_t* img, int w, int h, int stride, int max_level, int win) {
+    out.pg = make_pyr_geom(w, h, max_level, win);
+    CU(s.alloc(&out.base, (size_t)out.pg.image_bytes));
+    CU(cudaMemcpy2DAsync(out.base, out.pg.pitch[0], img, stride, w, h, cudaMemcpyHostToDevice, s.st));
+    for (int l = 1; l < out.pg.nlevels; ++l)
+        launch_pyrdown(out.base + out.pg.off[l - 1], 0, out.pg.w[l - 1], out.pg.h[l - 1], out.pg.pitch[l - 1],
+                       out.base + out.pg.off[l], 0, out.pg.w[l], out.pg.h[l], out.pg.pitch[l], 1, s.st);
+    return SVO_OK;
+}
+}  // namespace
+
+extern "C" int svo_build_pyramid(const uint8_t* img, int width, int height, int stride, int max_level, int win_size,
+                                 uint8_t* out, long long out_cap) {
+    if (!img || width < 1 || height < 1 || stride < width || max_level < 0 || max_level >= SVO_MAX_LEVELS)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    DevPyr p;
+    rc = build_dev_pyr(s, p, img, width, height, stride, max_level, win_size);
+    if (rc != SVO_OK) return rc;
+    long long need = 0;
+    for (int l = 1; l < p.pg.nlevels; ++l) need += (long long)p.pg.w[l] * p.pg.h[l];
+    if (need > out_cap) return fail(SVO_ERR_CAPACITY, "pyramid output buffer too small");
+    long long o = 0;
+    for (int l = 1; l < p.pg.nlevels; ++l) {
+        CU(cudaMemcpy2DAsync(out + o, p.pg.w[l], p.base + p.pg.off[l], p.pg.pitch[l], p.pg.w[l], p.pg.h[l],
+                             cudaMemcpyDeviceToHost, s.st));
+        o += (long long)p.pg.w[l] * p.pg.h[l];
+    }
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    return p.pg.nlevels;
+}
+
+extern "C" int svo_lk_track(const svo_params* p, const uint8_t* prev_img, const uint8_t* next_img, int stride,
+                            const float* pts_in, int n, float* pts_out, uint8_t* status_out) {
+    int rc = validate_params(p);
+    if (rc != SVO_OK) return rc;
+    if (!prev_img || !next_img || n < 0 || (n > 0 && (!pts_in || !pts_out || !status_out)) || stride < p->width)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    rc = need_device();
+    if (rc != SVO_OK) return rc;
+    if (n == 0) return 0;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    DevPyr I, J;
+    rc = build_dev_pyr(s, I, prev_img, p->width, p->height, stride, p->max_level, p->win_size);
+    if (rc != SVO_OK) return rc;
+    rc = build_dev_pyr(s, J, next_img, p->width, p->height, stride, p->max_level, p->win_size);
+    if (rc != SVO_OK) return rc;
+    float2 *din, *dout;
+    uint8_t* dst;
+    CU(s.alloc(&din, (size_t)n));
+    CU(s.alloc(&dout, (size_t)n));
+    CU(s.alloc(&dst, (size_t)n));
+    CU(cudaMemcpyAsync(din, pts_in, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+    launch_lk_single(I.lk(), J.lk(), make_lk_config(*p, I.pg.nlevels), din, n, dout, dst, s.st);
+    CU(cudaMemcpyAsync(pts_out, dout, sizeof(float2) * n, cudaMemcpyDeviceToHost, s.st));
+    CU(cudaMemcpyAsync(status_out, dst, n, cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    int ok = 0;
+    for (int i = 0; i < n; ++i) ok += status_out[i] ? 1 : 0;
+    return ok;
+}
+
+// Stateless circular matching / matchingFeatures on top of a private one-sequence context.
+static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R0, const uint8_t* L1,
+                        const uint8_t* R1, int stride, bool detect, bool check_bounds, float* fs_xy, int* fs_age,
+                        int* fs_str, int* n_fs_io, int fs_cap, const float* pL0_in, int n_in, float* pL0, float* pR0,
+                        float* pL1, float* pR1, uint8_t* keep_out) {
+    svo_params q = *p;
+    q.n_seq = 1;
+    q.features_per_bucket = 1;
+    svo_ctx* c = ctx_create(&q, n_in > fs_cap ? n_in : fs_cap);
+    if (!c) return SVO_ERR_CUDA;
+    struct Guard {
+        svo_ctx* c;
+        ~Guard() { svo_destroy(c); }
+    } guard{c};
+    c->pc.check_bounds = check_bounds ? 1 : 0;
+    c->pc.age_increment = 0;
+    const int W = q.width, H = q.height, P0 = c->pg.pitch[0];
+    const long long plane = (long long)P0 * H;
+    DevArrays& d = c->d;
+    cudaStream_t st = c->stream;
+    auto up = [&](const uint8_t* l, const uint8_t* r) -> int {
+        CU(cudaMemcpy2DAsync(c->stage_L, P0, l, stride, W, H, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpy2DAsync(c->stage_R, P0, r, stride, W, H, cudaMemcpyHostToDevice, st));
+        return SVO_OK;
+    };
+    int rc = up(L0, R0);
+    if (rc != SVO_OK) return rc;
+    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 1, 0, st);
+    launch_first_frame(d, st);
+    rc = up(L1, R1);
+    if (rc != SVO_OK) return rc;
+    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 0, 1, st);
+    SeqState s;
+    CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (detect) {
+        const int n0 = *n_fs_io;
+        if (n0 > 0) {
+            CU(cudaMemcpyAsync(d.fs_xy, fs_xy, sizeof(float2) * n0, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(d.fs_age, fs_age, sizeof(int) * n0, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(d.fs_str, fs_str, sizeof(int) * n0, cudaMemcpyHostToDevice, st));
+        }
+        s.n_feat = n0;
+        CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
+        launch_bucket_merge(d, c->bg, c->pc, 0, st);
+    } else {
+        if (n_in > 0) CU(cudaMemcpyAsync(d.bk_xy, pL0_in, sizeof(float2) * n_in, cudaMemcpyHostToDevice, st));
+        s.n_bucketed = n_in;
+        CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
+    }
+    launch_klt(d, c->pg, c->pc, st);
+    launch_select(d, c->pc, st);
+    CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    const int m = s.n_matched;
+    if (m > 0) {
+        if (pL0) CU(cudaMemcpy(pL0, d.m_L0, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        if (pR0) CU(cudaMemcpy(pR0, d.m_R0, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        if (pL1) CU(cudaMemcpy(pL1, d.m_L1, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        if (pR1) CU(cudaMemcpy(pR1, d.m_R1, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+        if (detect && m <= fs_cap) {
+            CU(cudaMemcpy(fs_xy, d.fs_xy, sizeof(float2) * m, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(fs_age, d.fs_age, sizeof(int) * m, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(fs_str, d.fs_str, sizeof(int) * m, cudaMemcpyDeviceToHost));
+        }
+    }
+    if (keep_out && s.n_bucketed > 0) {
+        std::vector<uint8_t> stt(s.n_bucketed);
+        CU(cudaMemcpy(stt.data(), d.lk_status, s.n_bucketed, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < s.n_bucketed; ++i) keep_out[i] = (stt[i] & 16) ? 1 : 0;
+    }
+    if (detect) {
+        if (m > fs_cap) return fail(SVO_ERR_CAPACITY, "feature-set buffer too small");
+        *n_fs_io = m;
+    }
+    return m;
+}
+
+extern "C" int svo_circular_match(const svo_params* p, const uint8_t* L0, const uint8_t* R0, const uint8_t* L1,
+                                  const uint8_t* R1, int stride, float* pL0, int n, float* pR0, float* pL1, float* pR1,
+                                  uint8_t* keep_out) {
+    int rc = validate_params(p);
+    if (rc != SVO_OK) return rc;
+    if (!L0 || !R0 || !L1 || !R1 || n < 0 || (n > 0 && !pL0) || stride < p->width)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    rc = need_device();
+    if (rc != SVO_OK) return rc;
+    if (n == 0) return 0;   // vo.cpp:179-181
+    return run_matching(p, L0, R0, L1, R1, stride, false, false, nullptr, nullptr, nullptr, nullptr, 0, pL0, n, pL0,
+                        pR0, pL1, pR1, keep_out);
+}
+
+extern "C" int svo_matching_features(const svo_params* p, const uint8_t* L0, const uint8_t* R0, const uint8_t* L1,
+                                     const uint8_t* R1, int stride, float* fs_xy, int* fs_age, int* fs_str, int* n_fs,
+                                     int fs_cap, float* pL0, float* pR0, float* pL1, float* pR1) {
+    int rc = validate_params(p);
+    if (rc != SVO_OK) return rc;
+    if (!L0 || !R0 || !L1 || !R1 || !n_fs || *n_fs < 0 || fs_cap < *n_fs || !fs_xy || !fs_age || !fs_str ||
+        stride < p->width)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    rc = need_device();
+    if (rc != SVO_OK) return rc;
+    return run_matching(p, L0, R0, L1, R1, stride, true, true, fs_xy, fs_age, fs_str, n_fs, fs_cap, nullptr, 0, pL0,
+                        pR0, pL1, pR1, nullptr);
+}
+
+extern "C" int svo_find_close_points(const float* p1, const float* p2, int n, float threshold, uint8_t* ok_out) {
+    if (n < 0 || (n > 0 && (!p1 || !p2 || !ok_out))) return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    if (n == 0) return 0;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    float2 *a, *b;
+    uint8_t* ok;
+    CU(s.alloc(&a, (size_t)n));
+    CU(s.alloc(&b, (size_t)n));
+    CU(s.alloc(&ok, (size_t)n));
+    CU(cudaMemcpyAsync(a, p1, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(b, p2, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+    launch_close_points(a, b, n, threshold, ok, s.st);
+    CU(cudaMemcpyAsync(ok_out, ok, n, cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    int k = 0;
+    for (int i = 0; i < n; ++i) k += ok_out[i] ? 1 : 0;
+    return k;
+}
+
+extern "C" int svo_compact(void* data, int elem_bytes, int n, const uint8_t* keep) {
+    if (n < 0 || elem_bytes < 1 || (n > 0 && (!data || !keep))) return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    if (n == 0) return 0;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    uint8_t *src, *dst, *k;
+    int* dn;
+    CU(s.alloc(&src, (size_t)n * elem_bytes));
+    CU(s.alloc(&dst, (size_t)n * elem_bytes));
+    CU(s.alloc(&k, (size_t)n));
+    CU(s.alloc(&dn, 1));
+    CU(cudaMemcpyAsync(src, data, (size_t)n * elem_bytes, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(k, keep, n, cudaMemcpyHostToDevice, s.st));
+    launch_compact_bytes(src, dst, elem_bytes, n, k, dn, s.st);
+    int m = 0;
+    CU(cudaMemcpyAsync(&m, dn, sizeof(int), cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    if (m > 0) CU(cudaMemcpy(data, dst, (size_t)m * elem_bytes, cudaMemcpyDeviceToHost));
+    return m;
+}
+
+extern "C" int svo_triangulate(const float Pl[12], const float Pr[12], const float* pL, const float* pR, int n,
+                               float* X3_out) {
+    if (!Pl || !Pr || n < 0 || (n > 0 && (!pL || !pR || !X3_out))) return fail(SVO_ERR_INVALID, "bad argument");
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    if (n == 0) return 0;
+    Scratch s;
+    CU(cudaStreamCreate(&s.st));
+    float *dPl, *dPr, *dX;
+    float2 *a, *b;
+    CU(s.alloc(&dPl, 12));
+    CU(s.alloc(&dPr, 12));
+    CU(s.alloc(&a, (size_t)n));
+    CU(s.alloc(&b, (size_t)n));
+    CU(s.alloc(&dX, (size_t)n * 3));
+    CU(cudaMemcpyAsync(dPl, Pl, sizeof(float) * 12, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(dPr, Pr, sizeof(float) * 12, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(a, pL, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(b, pR, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
+    launch_triangulate(dPl, dPr, a, b, n, dX, s.st);
+    CU(cudaMemcpyAsync(X3_out, dX, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, s.st));
+    CU(cudaStreamSynchronize(s.st));
+    CU(cudaGetLastError());
+    return n;
+}
+
+extern "C" int svo_camera_to_world(const svo_params* p, const float K[9], const float* cam_pts, const float* world_pts,
+                                   int n, double R[9], double t[3], int* inliers_out, int* success_out) {
+    if (!p || !K || !R || !t || n < 4 || !cam_pts || !world_pts) return fail(SVO_ERR_INVALID, "bad argument (n >= 4 required)");
+    svo_params q = *p;
+    q.n_seq = 1;
+    q.features_per_bucket = 1;
+    q.features_threshold = 0;   // the >15 gate belongs to stereo_callback, not to cameraToWorld
+    if (q.width < 16) q.width = 64;
+    if (q.height < 16) q.height = 64;
+    int rc = validate_params(&q);
+    if (rc != SVO_OK) return rc;
+    rc = need_device();
+    if (rc != SVO_OK) return rc;
+    svo_ctx* c = ctx_create(&q, n);
+    if (!c) return SVO_ERR_CUDA;
+    struct Guard {
+        svo_ctx* c;
+        ~Guard() { svo_destroy(c); }
+    } guard{c};
+    c->pc.K.fx = K[0];
+    c->pc.K.fy = K[4];
+    c->pc.K.cx = K[2];
+    c->pc.K.cy = K[5];
+    c->pc.max_t_norm = INFINITY;   // the motion gates belong to stereo_callback
+    c->pc.max_r_norm = INFINITY;
+    DevArrays& d = c->d;
+    cudaStream_t st = c->stream;
+    SeqState s;
+    CU(cudaMemcpy(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost));
+    memcpy(s.R, R, sizeof(double) * 9);
+    memcpy(s.t, t, sizeof(double) * 3);
+    s.n_matched = n;
+    s.n_feat = n;
+    s.frame_id = 1;
+    CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d.m_L1, cam_pts, sizeof(float2) * n, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d.X3, world_pts, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st));
+    launch_pnp(d, c->pc, st);
+    CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    if (success_out) *success_out = s.pnp_ok;
+    if (s.pnp_ok) {
+        memcpy(R, s.R, sizeof(double) * 9);
+        memcpy(t, s.t, sizeof(double) * 3);
+        if (inliers_out && s.n_inliers > 0)
+            CU(cudaMemcpy(inliers_out, d.inl_idx, sizeof(int) * s.n_inliers, cudaMemcpyDeviceToHost));
+        return s.n_inliers;
+    }
+    return 0;
+}
+
+extern "C" int svo_get_inverse_transform(const double R[9], const double t[3], double T_out[16]) {
+    if (!R || !t || !T_out) return fail(SVO_ERR_INVALID, "NULL argument");
+    // general 4x4 inverse of [R t; 0 0 0 1] by Gauss-Jordan with partial pivoting (cv::Mat::inv, DECOMP_LU)
+    double A[4][8];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 8; ++j) A[i][j] = 0.0;
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) A[i][j] = R[i * 3 + j];
+        A[i][3] = t[i];
+    }
+    A[3][3] = 1.0;
+    for (int i = 0; i < 4; ++i) A[i][4 + i] = 1.0;
+    for (int col = 0; col < 4; ++col) {
+        int piv = col;
+        for (int r = col + 1; r < 4; ++r)
+            if (fabs(A[r][col]) > fabs(A[piv][col])) piv = r;
+        if (fabs(A[piv][col]) < 1e-300) {
+            for (int i = 0; i < 16; ++i) T_out[i] = 0.0;   // cv::Mat::inv of a singular matrix returns zeros
+            return SVO_OK;
+        }
+        if (piv != col)
+            for (int j = 0; j < 8; ++j) {
+                double tmp = A[col][j];
+                A[col][j] = A[piv][j];
+                A[piv][j] = tmp;
+            }
+        const double inv = 1.0 / A[col][col];
+        for (int j = 0; j < 8; ++j) A[col][j] *= inv;
+        for (int r = 0; r < 4; ++r)
+            if (r != col) {
+                const double f = A[r][col];
+                if (f != 0.0)
+                    for (int j = 0; j < 8; ++j) A[r][j] -= f * A[col][j];
+            }
+    }
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) T_out[i * 4 + j] = A[i][4 + j];
+    return SVO_OK;
+}

@@ -1,0 +1,669 @@
+// svo_core.cuh -- arithmetic cores of the stereo-VO front end, written once as
+// host+device inline functions.  The CUDA kernels (svo_kernels.cu) call them
+// with LANES = 32 (one warp per feature); tests/host_cores.cpp compiles the same
+// header with g++ and LANES = 1 so the arithmetic can be unit-tested on a box
+// without a GPU.  Nothing here is a CPU fallback: the shipped library only
+// instantiates the device side.
+//
+// Behavioural spec: SURVEY.md Appendix B (OpenCV calls made by the reference at
+// src/feature_set.cpp:61, src/vo.cpp:50-53, 90-94, 200-215, 301-304).
+#pragma once
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define SVO_HD __host__ __device__ __forceinline__
+#else
+#define SVO_HD inline
+#endif
+
+namespace svo {
+
+// ---------------------------------------------------------------------------
+// Border handling (cv::BORDER_REFLECT_101), clamped for degenerate sizes.
+SVO_HD int reflect101(int i, int n) {
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * n - 2 - i;
+    if (i < 0) i = 0;
+    if (i >= n) i = n - 1;
+    return i;
+}
+
+SVO_HD int imin(int a, int b) { return a < b ? a : b; }
+SVO_HD int imax(int a, int b) { return a > b ? a : b; }
+
+// ---------------------------------------------------------------------------
+// FAST-9/16 (cv::FAST, TYPE_9_16) -- featureDetectionFast, feature_set.cpp:55-68.
+// Ring offsets k = 0..15 (dx, dy), SURVEY Appendix B.1.
+#define SVO_FAST_RING_DX {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1}
+#define SVO_FAST_RING_DY {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3}
+
+// s = the largest t such that 9 contiguous ring pixels are all >= t darker, or
+// all >= t brighter, than the centre.  Corner <=> s > threshold; KeyPoint
+// response = s - 1 (threshold independent).
+SVO_HD int fast9_arc_score(int v, const int* r) {
+    int d[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = v - r[k];
+    int lo2[16], hi2[16], lo4[16], hi4[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo2[k] = imin(d[k], d[(k + 1) & 15]);
+        hi2[k] = imax(d[k], d[(k + 1) & 15]);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo4[k] = imin(lo2[k], lo2[(k + 2) & 15]);
+        hi4[k] = imax(hi2[k], hi2[(k + 2) & 15]);
+    }
+    int a = -256, b = 256;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        int lo9 = imin(imin(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
+        int hi9 = imax(imax(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
+        a = imax(a, lo9);
+        b = imin(b, hi9);
+    }
+    return imax(a, -b);
+}
+
+// ---------------------------------------------------------------------------
+// Bucketing, FeatureSet::filterByBucketLocationInternal, feature_set.cpp:95-147.
+// C integer division (truncation toward zero) as in Bucket::compute_score,
+// feature_set.cpp:16-18.
+SVO_HD int bucket_score(int age, int strength, int fast_threshold) {
+    return age + (strength - fast_threshold) / 20;
+}
+
+// 64-bit selection key for the one-feature-per-bucket production path:
+// max key == highest score, ties -> earliest position in the reference's
+// feature order.  [63:48] score + 0x8000 | [47:16] ~order | [15:0] strength.
+SVO_HD unsigned long long bucket_key(int score, unsigned order, int strength) {
+    return ((unsigned long long)(unsigned)(score + 0x8000) << 48) |
+           ((unsigned long long)(0xFFFFFFFFu - order) << 16) | (unsigned long long)(strength & 0xFFFF);
+}
+SVO_HD int bucket_key_score(unsigned long long k) { return (int)(k >> 48) - 0x8000; }
+SVO_HD unsigned bucket_key_order(unsigned long long k) {
+    return 0xFFFFFFFFu - (unsigned)((k >> 16) & 0xFFFFFFFFull);
+}
+SVO_HD int bucket_key_strength(unsigned long long k) { return (int)(k & 0xFFFF); }
+// order values >= SVO_FAST_ORDER_BASE denote a FAST pixel (order - base = y*W + x)
+#define SVO_FAST_ORDER_BASE (1u << 24)
+
+// ---------------------------------------------------------------------------
+// pyrDown (cv::pyrDown u8, 5x5 binomial, BORDER_REFLECT_101): SURVEY B.2.
+template <class Img>
+SVO_HD int pyrdown_pixel(const Img& src, int sw, int sh, int x, int y) {
+    int acc = 0;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int yy = reflect101(2 * y + j - 2, sh);
+        const int kj = (j == 0 || j == 4) ? 1 : (j == 2 ? 6 : 4);
+        int row = 0;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const int xx = reflect101(2 * x + i - 2, sw);
+            const int ki = (i == 0 || i == 4) ? 1 : (i == 2 ? 6 : 4);
+            row += ki * (int)src(xx, yy);
+        }
+        acc += kj * row;
+    }
+    return (acc + 128) >> 8;
+}
+
+// ---------------------------------------------------------------------------
+// Pyramidal Lucas-Kanade (cv::calcOpticalFlowPyrLK CPU path), SURVEY B.3.
+struct LkLevel {
+    const uint8_t* img;
+    int w, h, pitch;
+    SVO_HD int at(int x, int y) const { return img[(size_t)y * pitch + x]; }
+    SVO_HD int at_r(int x, int y) const { return img[(size_t)reflect101(y, h) * pitch + reflect101(x, w)]; }
+};
+
+#define SVO_MAX_LEVELS 4
+struct LkPyramid {
+    LkLevel lv[SVO_MAX_LEVELS];
+};
+
+struct LkConfig {
+    int nlevels;      // maxLevel + 1 actually available
+    int max_iters;    // criteria.maxCount
+    double eps_sq;    // criteria.epsilon^2
+    float min_eig;    // minEigThreshold
+};
+
+// Reduction policy for LANES == 1 (host unit tests).
+struct SerialRed {
+    static SVO_HD int sum(int v) { return v; }
+    static SVO_HD long long sum64(long long v) { return v; }
+    static SVO_HD void sync() {}
+};
+
+// cvRound(float): round half to even.
+SVO_HD int round_half_even(float v) {
+#if defined(__CUDA_ARCH__)
+    return __float2int_rn(v);
+#else
+    return (int)lrintf(v);
+#endif
+}
+SVO_HD int floor_int(float v) {
+#if defined(__CUDA_ARCH__)
+    return __float2int_rd(v);
+#else
+    return (int)floorf(v);
+#endif
+}
+
+// Explicitly unfused float ops: OpenCV's x86 build does not contract these and the
+// decision quantities (minEig, D, delta) must not depend on FMA contraction.
+SVO_HD float fmul(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fmul_rn(a, b);
+#else
+    volatile float r = a * b;
+    return r;
+#endif
+}
+SVO_HD float fadd(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fadd_rn(a, b);
+#else
+    volatile float r = a + b;
+    return r;
+#endif
+}
+SVO_HD float fsub(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fsub_rn(a, b);
+#else
+    volatile float r = a - b;
+    return r;
+#endif
+}
+
+#define SVO_LK_WIN 10
+#define SVO_LK_PATCH (SVO_LK_WIN + 3)     // 13: window + 1 (bilinear) + 2 (Scharr halo)
+#define SVO_LK_PATCH_PITCH 16
+#define SVO_LK_NPIX (SVO_LK_WIN * SVO_LK_WIN)
+
+SVO_HD void lk_weights(float a, float b, int& iw00, int& iw01, int& iw10, int& iw11) {
+    const float W = 16384.f;   // 1 << W_BITS
+    iw00 = round_half_even(fmul(fmul(fsub(1.f, a), fsub(1.f, b)), W));
+    iw01 = round_half_even(fmul(fmul(a, fsub(1.f, b)), W));
+    iw10 = round_half_even(fmul(fmul(fsub(1.f, a), b), W));
+    iw11 = 16384 - iw00 - iw01 - iw10;
+}
+
+// Track ONE feature through all pyramid levels.  Executed by LANES cooperating
+// lanes (every lane runs the same scalar control flow; window pixels are
+// distributed lane-cyclically; Red sums across lanes).  `patch` is scratch of
+// SVO_LK_PATCH * SVO_LK_PATCH_PITCH bytes shared by the lanes.
+// Returns status (1 = tracked) and writes the output position.
+template <int LANES, class Red>
+SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const LkConfig& cfg,
+                            float ptx, float pty, int lane, uint8_t* patch, float& outx,
+                            float& outy, int& iters_out) {
+    constexpr int SLOTS = (SVO_LK_NPIX + LANES - 1) / LANES;
+    const float half_win = 4.5f;   // (winSize - 1) * 0.5f
+    const float FLT_SCALE = 1.f / (1 << 20);
+    int status = 1;
+    float nx = 0.f, ny = 0.f;      // nextPts[ptidx]
+    int iters = 0;
+
+    for (int level = cfg.nlevels - 1; level >= 0; --level) {
+        const LkLevel I = Ipyr.lv[level];
+        const LkLevel J = Jpyr.lv[level];
+        const float scale = 1.f / (float)(1 << level);
+        float prx = fmul(ptx, scale), pry = fmul(pty, scale);
+        float nxt_x, nxt_y;
+        if (level == cfg.nlevels - 1) {
+            nxt_x = prx;
+            nxt_y = pry;
+        } else {
+            nxt_x = fmul(nx, 2.f);
+            nxt_y = fmul(ny, 2.f);
+        }
+        nx = nxt_x;
+        ny = nxt_y;
+
+        prx = fsub(prx, half_win);
+        pry = fsub(pry, half_win);
+        const int ipx = floor_int(prx), ipy = floor_int(pry);
+        if (ipx < -SVO_LK_WIN || ipx >= I.w || ipy < -SVO_LK_WIN || ipy >= I.h) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        int iw00, iw01, iw10, iw11;
+        lk_weights(fsub(prx, (float)ipx), fsub(pry, (float)ipy), iw00, iw01, iw10, iw11);
+
+        // ---- stage the 13x13 neighbourhood of the template window
+        Red::sync();
+        for (int idx = lane; idx < SVO_LK_PATCH * SVO_LK_PATCH; idx += LANES) {
+            const int py = idx / SVO_LK_PATCH, px = idx - py * SVO_LK_PATCH;
+            patch[py * SVO_LK_PATCH_PITCH + px] = (uint8_t)I.at_r(ipx - 1 + px, ipy - 1 + py);
+        }
+        Red::sync();
+
+        // ---- template window: Ival (x32), Ix, Iy (Scharr, bilinear), structure tensor
+        short Iv[SLOTS], Ixv[SLOTS], Iyv[SLOTS];
+        int sA11 = 0, sA12 = 0, sA22 = 0;
+#pragma unroll
+        for (int s = 0; s < SLOTS; ++s) {
+            const int idx = lane + s * LANES;
+            Iv[s] = 0; Ixv[s] = 0; Iyv[s] = 0;
+            if (idx < SVO_LK_NPIX) {
+                const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
+                // 4x4 block of the patch whose inner 2x2 are the bilinear taps
+                int P[4][4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) P[r][c] = patch[(wy + r) * SVO_LK_PATCH_PITCH + wx + c];
+                int dx[2][2], dy[2][2];
+#pragma unroll
+                for (int r = 0; r < 2; ++r)
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        // Scharr at patch (c+1, r+1); zero outside the level (derivBorder = CONSTANT)
+                        const int ax = ipx + wx + c, ay = ipy + wy + r;
+                        const bool inside = (ax >= 0) & (ax < I.w) & (ay >= 0) & (ay < I.h);
+                        const int t0m = 3 * (P[r][c] + P[r + 2][c]) + 10 * P[r + 1][c];
+                        const int t0p = 3 * (P[r][c + 2] + P[r + 2][c + 2]) + 10 * P[r + 1][c + 2];
+                        const int t1m = P[r + 2][c] - P[r][c];
+                        const int t1c = P[r + 2][c + 1] - P[r][c + 1];
+                        const int t1p = P[r + 2][c + 2] - P[r][c + 2];
+                        dx[r][c] = inside ? (t0p - t0m) : 0;
+                        dy[r][c] = inside ? (3 * (t1m + t1p) + 10 * t1c) : 0;
+                    }
+                const int iv = (P[1][1] * iw00 + P[1][2] * iw01 + P[2][1] * iw10 + P[2][2] * iw11 + (1 << 8)) >> 9;
+                const int ix = (dx[0][0] * iw00 + dx[0][1] * iw01 + dx[1][0] * iw10 + dx[1][1] * iw11 + (1 << 13)) >> 14;
+                const int iy = (dy[0][0] * iw00 + dy[0][1] * iw01 + dy[1][0] * iw10 + dy[1][1] * iw11 + (1 << 13)) >> 14;
+                Iv[s] = (short)iv; Ixv[s] = (short)ix; Iyv[s] = (short)iy;
+                sA11 += ix * ix; sA12 += ix * iy; sA22 += iy * iy;
+            }
+        }
+        sA11 = Red::sum(sA11); sA12 = Red::sum(sA12); sA22 = Red::sum(sA22);
+        const float A11 = fmul((float)sA11, FLT_SCALE);
+        const float A12 = fmul((float)sA12, FLT_SCALE);
+        const float A22 = fmul((float)sA22, FLT_SCALE);
+        float D = fsub(fmul(A11, A22), fmul(A12, A12));
+        const float dA = fsub(A11, A22);
+        const float disc = fadd(fmul(dA, dA), fmul(fmul(4.f, A12), A12));
+        const float min_eig = fsub(fadd(A22, A11), sqrtf(disc)) / (float)(2 * SVO_LK_NPIX);
+        if (min_eig < cfg.min_eig || D < FLT_EPSILON) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        D = 1.f / D;
+
+        float cx = fsub(nxt_x, half_win), cy = fsub(nxt_y, half_win);   // nextPt -= halfWin
+        float pdx = 0.f, pdy = 0.f;
+        for (int j = 0; j < cfg.max_iters; ++j) {
+            const int inx = floor_int(cx), iny = floor_int(cy);
+            if (inx < -SVO_LK_WIN || inx >= J.w || iny < -SVO_LK_WIN || iny >= J.h) {
+                if (level == 0) status = 0;
+                break;
+            }
+            ++iters;
+            lk_weights(fsub(cx, (float)inx), fsub(cy, (float)iny), iw00, iw01, iw10, iw11);
+            const bool interior = (inx >= 0) & (inx + SVO_LK_WIN < J.w) & (iny >= 0) & (iny + SVO_LK_WIN < J.h);
+            long long sb1 = 0, sb2 = 0;
+#pragma unroll
+            for (int s = 0; s < SLOTS; ++s) {
+                const int idx = lane + s * LANES;
+                if (idx < SVO_LK_NPIX) {
+                    const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
+                    int j00, j01, j10, j11;
+                    if (interior) {
+                        const uint8_t* p = J.img + (size_t)(iny + wy) * J.pitch + inx + wx;
+                        j00 = p[0]; j01 = p[1]; j10 = p[J.pitch]; j11 = p[J.pitch + 1];
+                    } else {
+                        j00 = J.at_r(inx + wx, iny + wy);     j01 = J.at_r(inx + wx + 1, iny + wy);
+                        j10 = J.at_r(inx + wx, iny + wy + 1); j11 = J.at_r(inx + wx + 1, iny + wy + 1);
+                    }
+                    const int diff = ((j00 * iw00 + j01 * iw01 + j10 * iw10 + j11 * iw11 + (1 << 8)) >> 9) - (int)Iv[s];
+                    sb1 += diff * (int)Ixv[s];
+                    sb2 += diff * (int)Iyv[s];
+                }
+            }
+            sb1 = Red::sum64(sb1);
+            sb2 = Red::sum64(sb2);
+            const float b1 = fmul((float)sb1, FLT_SCALE);
+            const float b2 = fmul((float)sb2, FLT_SCALE);
+            const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);
+            const float ddy = fmul(fsub(fmul(A12, b1), fmul(A11, b2)), D);
+            cx = fadd(cx, ddx);
+            cy = fadd(cy, ddy);
+            nx = fadd(cx, half_win);
+            ny = fadd(cy, half_win);
+            if ((double)ddx * (double)ddx + (double)ddy * (double)ddy <= cfg.eps_sq) break;
+            if (j > 0 && (double)fabsf(fadd(ddx, pdx)) < 0.01 && (double)fabsf(fadd(ddy, pdy)) < 0.01) {
+                nx = fsub(nx, fmul(ddx, 0.5f));
+                ny = fsub(ny, fmul(ddy, 0.5f));
+                break;
+            }
+            pdx = ddx;
+            pdy = ddy;
+        }
+    }
+    // err is requested by the reference (vo.cpp:203-215) without
+    // OPTFLOW_LK_GET_MIN_EIGENVALS: OpenCV re-checks the final window position.
+    if (status) {
+        const int fx = floor_int(fsub(nx, half_win)), fy = floor_int(fsub(ny, half_win));
+        const LkLevel J0 = Jpyr.lv[0];
+        if (fx < -SVO_LK_WIN || fx >= J0.w || fy < -SVO_LK_WIN || fy >= J0.h) status = 0;
+    }
+    outx = nx;
+    outy = ny;
+    iters_out = iters;
+    return status;
+}
+
+// ---------------------------------------------------------------------------
+// findClosePoints, vo.cpp:265-280 (NaN => kept, like `offset > threshold`).
+SVO_HD bool close_points(float x1, float y1, float x2, float y2, float thr) {
+    const float off = fmaxf(fabsf(x1 - x2), fabsf(y1 - y2));
+    return !(off > thr);
+}
+// in-bounds test of matchingFeatures, vo.cpp:341-359
+SVO_HD bool in_bounds(float x, float y, int w, int h) {
+    return !((x < 0) || (y < 0) || (y >= (float)h) || (x >= (float)w));
+}
+
+// ---------------------------------------------------------------------------
+// DLT triangulation (cv::triangulatePoints + convertPointsFromHomogeneous as at
+// vo.cpp:89-94), SURVEY B.4.  One-sided (Hestenes) Jacobi SVD of the 4x4 system
+// in FP64; the right singular vector of the smallest singular value is stored as
+// float32 and dehomogenised in float32.
+SVO_HD void triangulate_dlt(const float* Pl, const float* Pr, float xl, float yl, float xr, float yr,
+                            float* X3) {
+    double A[4][4], V[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        A[0][k] = (double)xl * (double)Pl[8 + k] - (double)Pl[k];
+        A[1][k] = (double)yl * (double)Pl[8 + k] - (double)Pl[4 + k];
+        A[2][k] = (double)xr * (double)Pr[8 + k] - (double)Pr[k];
+        A[3][k] = (double)yr * (double)Pr[8 + k] - (double)Pr[4 + k];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) V[r][k] = (r == k) ? 1.0 : 0.0;
+    }
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        bool changed = false;
+#pragma unroll
+        for (int p = 0; p < 3; ++p)
+#pragma unroll
+            for (int q = p + 1; q < 4; ++q) {
+                double a = 0, b = 0, c = 0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    a += A[r][p] * A[r][p];
+                    b += A[r][q] * A[r][q];
+                    c += A[r][p] * A[r][q];
+                }
+                if (fabs(c) <= DBL_EPSILON * sqrt(a * b)) continue;
+                changed = true;
+                const double zeta = (b - a) / (2.0 * c);
+                const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const double ap = A[r][p], aq = A[r][q];
+                    A[r][p] = cs * ap - sn * aq;
+                    A[r][q] = sn * ap + cs * aq;
+                    const double vp = V[r][p], vq = V[r][q];
+                    V[r][p] = cs * vp - sn * vq;
+                    V[r][q] = sn * vp + cs * vq;
+                }
+            }
+        if (!changed) break;
+    }
+    int best = 0;
+    double bestn = DBL_MAX;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        double n = 0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) n += A[r][k] * A[r][k];
+        if (n < bestn) { bestn = n; best = k; }
+    }
+    float h[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        double v = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v = (k == best) ? V[r][k] : v;
+        h[r] = (float)v;
+    }
+    const float sc = (h[3] != 0.f) ? 1.f / h[3] : 1.f;
+    X3[0] = h[0] * sc;
+    X3[1] = h[1] * sc;
+    X3[2] = h[2] * sc;
+}
+
+// ---------------------------------------------------------------------------
+// PnP (cv::solvePnPRansac with SOLVEPNP_ITERATIVE as at vo.cpp:287-304),
+// SURVEY B.5.  Pose = (R row-major 3x3, t) in FP64.
+struct Pose {
+    double R[9];
+    double t[3];
+};
+struct Intrinsics {
+    double fx, fy, cx, cy;
+};
+
+// exp([w]x) * R  (Rodrigues formula)
+SVO_HD void rotate_left(const double* w, const double* R, double* out) {
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+    const double th = sqrt(th2);
+    double a, b;   // exp = I + a [w]x + b [w]x^2
+    if (th < 1e-8) {
+        a = 1.0 - th2 / 6.0;
+        b = 0.5 - th2 / 24.0;
+    } else {
+        a = sin(th) / th;
+        b = (1.0 - cos(th)) / th2;
+    }
+    double E[9];
+    const double wx = w[0], wy = w[1], wz = w[2];
+    E[0] = 1.0 - b * (wy * wy + wz * wz); E[1] = -a * wz + b * wx * wy;        E[2] = a * wy + b * wx * wz;
+    E[3] = a * wz + b * wx * wy;          E[4] = 1.0 - b * (wx * wx + wz * wz); E[5] = -a * wx + b * wy * wz;
+    E[6] = -a * wy + b * wx * wz;         E[7] = a * wx + b * wy * wz;         E[8] = 1.0 - b * (wx * wx + wy * wy);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            out[i * 3 + j] = E[i * 3] * R[j] + E[i * 3 + 1] * R[3 + j] + E[i * 3 + 2] * R[6 + j];
+}
+
+// rotation angle of R = || cv::Rodrigues(R) ||
+SVO_HD double rotation_angle(const double* R) {
+    double c = (R[0] + R[4] + R[8] - 1.0) * 0.5;
+    c = c > 1.0 ? 1.0 : (c < -1.0 ? -1.0 : c);
+    const double sx = R[7] - R[5], sy = R[2] - R[6], sz = R[3] - R[1];
+    const double s = 0.5 * sqrt(sx * sx + sy * sy + sz * sz);
+    return atan2(s, c);
+}
+
+// cv::projectPoints (no distortion), FP64.
+SVO_HD void project_point(const Pose& P, const Intrinsics& K, double X, double Y, double Z, double& u,
+                          double& v) {
+    const double x = P.R[0] * X + P.R[1] * Y + P.R[2] * Z + P.t[0];
+    const double y = P.R[3] * X + P.R[4] * Y + P.R[5] * Z + P.t[1];
+    const double z = P.R[6] * X + P.R[7] * Y + P.R[8] * Z + P.t[2];
+    const double iz = z != 0.0 ? 1.0 / z : 1.0;
+    u = K.fx * (x * iz) + K.cx;
+    v = K.fy * (y * iz) + K.cy;
+}
+
+// Squared reprojection error exactly as PnPRansacCallback::computeError sees it:
+// projection rounded to float32, difference in float32, squares summed.
+SVO_HD float reproj_err_sq(const Pose& P, const Intrinsics& K, const float* X3, const float* uv) {
+    double u, v;
+    project_point(P, K, (double)X3[0], (double)X3[1], (double)X3[2], u, v);
+    const float du = uv[0] - (float)u, dv = uv[1] - (float)v;
+    return (float)((double)du * (double)du + (double)dv * (double)dv);
+}
+
+// Normal-equation accumulator for Gauss-Newton / LM on (dw, dt), left-multiplied
+// rotation increment.  acc[0..20] = upper triangle of J^T J (row-major), acc[21..26]
+// = J^T e, acc[27] = e^T e.
+#define SVO_PNP_ACC 28
+SVO_HD void pnp_accumulate(const Pose& P, const Intrinsics& K, const float* X3, const float* uv,
+                           double* acc, bool with_jacobian) {
+    const double X = X3[0], Y = X3[1], Z = X3[2];
+    const double rx = P.R[0] * X + P.R[1] * Y + P.R[2] * Z;
+    const double ry = P.R[3] * X + P.R[4] * Y + P.R[5] * Z;
+    const double rz = P.R[6] * X + P.R[7] * Y + P.R[8] * Z;
+    const double x = rx + P.t[0], y = ry + P.t[1], z = rz + P.t[2];
+    const double iz = z != 0.0 ? 1.0 / z : 1.0;
+    const double eu = K.fx * (x * iz) + K.cx - (double)uv[0];
+    const double ev = K.fy * (y * iz) + K.cy - (double)uv[1];
+    acc[27] += eu * eu + ev * ev;
+    if (!with_jacobian) return;
+    // d(u,v)/d(xc)
+    const double a0 = K.fx * iz, a2 = -K.fx * x * iz * iz;
+    const double b1 = K.fy * iz, b2 = -K.fy * y * iz * iz;
+    // d(xc)/d(w) = -[r]x ; d(xc)/d(t) = I
+    double Ju[6], Jv[6];
+    Ju[0] = a2 * ry;              // a . (-[r]x col 0) = a . (0, -rz... ) see below
+    Ju[1] = a0 * rz - a2 * rx;
+    Ju[2] = -a0 * ry;
+    Jv[0] = -b1 * rz + b2 * ry;
+    Jv[1] = -b2 * rx;
+    Jv[2] = b1 * rx;
+    Ju[3] = a0; Ju[4] = 0.0; Ju[5] = a2;
+    Jv[3] = 0.0; Jv[4] = b1; Jv[5] = b2;
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+        for (int j = i; j < 6; ++j) acc[k++] += Ju[i] * Ju[j] + Jv[i] * Jv[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc[21 + i] += Ju[i] * eu + Jv[i] * ev;
+}
+
+// Solve (JtJ with diag * (1 + lambda)) d = Jte by Cholesky.  Returns false when
+// the damped matrix is not positive definite.
+SVO_HD bool pnp_solve_step(const double* acc, double lambda, double* d) {
+    double M[6][6];
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = i; j < 6; ++j) {
+            M[i][j] = acc[k];
+            M[j][i] = acc[k];
+            ++k;
+        }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) M[i][i] *= (1.0 + lambda);
+    // Cholesky M = L L^T (in place, lower)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        double s = M[j][j];
+#pragma unroll
+        for (int q = 0; q < 6; ++q)
+            if (q < j) s -= M[j][q] * M[j][q];
+        if (!(s > 0.0)) return false;
+        const double l = sqrt(s);
+        M[j][j] = l;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i > j) {
+                double v = M[i][j];
+#pragma unroll
+                for (int q = 0; q < 6; ++q)
+                    if (q < j) v -= M[i][q] * M[j][q];
+                M[i][j] = v / l;
+            }
+    }
+    double yv[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        double v = acc[21 + i];
+#pragma unroll
+        for (int q = 0; q < 6; ++q)
+            if (q < i) v -= M[i][q] * yv[q];
+        yv[i] = v / M[i][i];
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; --i) {
+        double v = yv[i];
+#pragma unroll
+        for (int q = 0; q < 6; ++q)
+            if (q > i) v -= M[q][i] * d[q];
+        d[i] = v / M[i][i];
+    }
+    return true;
+}
+
+// param = prevParam - delta (CvLevMarq::step): R' = exp(-dw) R, t' = t - dt
+SVO_HD void pnp_apply_step(const Pose& P, const double* d, Pose& out) {
+    const double w[3] = {-d[0], -d[1], -d[2]};
+    rotate_left(w, P.R, out.R);
+    out.t[0] = P.t[0] - d[3];
+    out.t[1] = P.t[1] - d[4];
+    out.t[2] = P.t[2] - d[5];
+}
+
+// Levenberg-Marquardt control flow of CvLevMarq (OpenCV calib3d compat_ptsetreg.cpp)
+// as used by cvFindExtrinsicCameraParams2: lambda = 10^lg, lg starts at -3, a
+// worse step raises lg (up to 16) and retries, a better one lowers it; stops after
+// 20 accepted steps or when the relative parameter change drops below FLT_EPSILON.
+// `Eval` computes the 28 accumulators for a pose: eval(pose, acc, with_jacobian).
+template <class Eval>
+SVO_HD void pnp_refine_lm(Pose& P, Eval& eval, int max_iter) {
+    double acc[SVO_PNP_ACC], cand_acc[SVO_PNP_ACC];
+    eval(P, acc, true);
+    double prev_err = acc[27];
+    int lg = -3;
+    int iters = 0;
+    for (int guard = 0; guard < 64; ++guard) {
+        double d[6];
+        Pose cand;
+        bool solved = pnp_solve_step(acc, pow(10.0, (double)lg), d);
+        if (solved) {
+            pnp_apply_step(P, d, cand);
+            eval(cand, cand_acc, true);
+        }
+        if (!solved || !(cand_acc[27] <= prev_err)) {
+            if (++lg <= 16) continue;   // retry with more damping from the same linearisation
+            if (!solved) return;
+        }
+        lg = lg - 1 < -16 ? -16 : lg - 1;
+        // accepted
+        const double ang = rotation_angle(P.R);
+        const double pn = sqrt(ang * ang + P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
+        const double dn = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + d[3] * d[3] + d[4] * d[4] + d[5] * d[5]);
+        P = cand;
+        ++iters;
+        if (iters >= max_iter || dn < (double)FLT_EPSILON * pn) return;
+        prev_err = cand_acc[27];
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = cand_acc[i];
+    }
+}
+
+// Counter-based RNG for hypothesis sampling (splitmix64).
+SVO_HD uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// 5 distinct indices in [0, n), n >= 5
+SVO_HD void sample5(uint64_t seed, uint64_t stream, int n, int* idx) {
+    uint64_t ctr = 0;
+    for (int i = 0; i < 5;) {
+        const uint64_t r = splitmix64(seed ^ splitmix64(stream * 0x100000001B3ull + (ctr++)));
+        const int v = (int)((r >> 11) % (uint64_t)n);
+        bool dup = false;
+        for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
+        if (!dup) idx[i++] = v;
+    }
+}
+
+}  // namespace svo

@@ -1,0 +1,96 @@
+// svo_device.cuh -- device-side data layout shared by the kernels (svo_kernels.cu)
+// and the C-ABI host layer (svo_capi.cu).
+//
+// HBM layout (one context = n_seq independent sequences, all arrays SoA per sequence):
+//   pyramids  [seq][slot 0/1][cam L/R][level 0..3]  u8, row pitch 128-B aligned
+//   fastkeys  [parity 0/1][A|B][seq][bucket]        u64 per-bucket FAST winners of one left image
+//   trackkeys [seq][bucket]                         u64 scratch for the tracked-feature winners
+//   feature set / bucketed list / LK legs / matched set / 3-D points: [seq][cap]
+//   hypotheses [seq][H] pose (12 f64) + inlier count
+//   SeqState [seq], svo_frame_result [seq]
+#pragma once
+#include <stdint.h>
+
+#include "../../include/svo.h"
+#include "svo_core.cuh"
+
+namespace svo {
+
+struct PyrGeom {
+    int nlevels;
+    int w[SVO_MAX_LEVELS], h[SVO_MAX_LEVELS], pitch[SVO_MAX_LEVELS];
+    long long off[SVO_MAX_LEVELS];   // byte offset of each level inside one image pyramid
+    long long image_bytes;           // bytes of one image pyramid (all levels)
+    // pyramid of (seq, slot, cam)
+    __host__ __device__ long long base(int seq, int slot, int cam) const {
+        return ((long long)(seq * 2 + slot) * 2 + cam) * image_bytes;
+    }
+};
+
+struct BucketGeom {
+    int n_bh, n_bw;      // buckets along height / width
+    int bh, bw;          // bucket size in pixels (ceil division, feature_set.cpp:103-104)
+    int start_row;
+    int age_threshold;
+    int fast_threshold;  // the constant inside Bucket::compute_score
+    int nb;              // n_bh * n_bw
+};
+
+struct SeqState {
+    int slot;            // pyramid slot holding lastLeftPyramid / lastRightPyramid (vo.h:257-258)
+    int n_feat;          // currentVOFeatures.size()
+    int n_bucketed;
+    int n_matched;
+    int n_inliers;
+    int retry;
+    int pnp_ok;
+    int lk_iters;
+    int frame_id;
+    int pad_;
+    double R[9];         // rotation      (vo.h:262)
+    double t[3];         // translation   (vo.h:263)
+    double last_T[16];   // last_transform (vo.h:264)
+};
+
+// All device pointers of a context, passed by value to the kernels.
+struct DevArrays {
+    uint8_t* pyr;                     // pyramids
+    unsigned long long* fastkeys;     // [2][2][n_seq][nb]
+    unsigned long long* trackkeys;    // [n_seq][nb]
+    SeqState* state;                  // [n_seq]
+    svo_frame_result* result;         // [n_seq]
+    // tracked feature set (currentVOFeatures)
+    float2* fs_xy; int* fs_age; int* fs_str;
+    // bucketed list == pointsLeftT0 entering circular matching
+    float2* bk_xy; int* bk_age; int* bk_str;
+    // LK leg outputs + status bits (bit l = status of leg l)
+    float2* lk_L1; float2* lk_R1; float2* lk_R0; float2* lk_C; uint8_t* lk_status;
+    // matched (compacted) sets
+    float2* m_L0; float2* m_L1; float2* m_R0; float2* m_R1; int* m_age; int* m_str;
+    float* X3;                        // [cap][3]
+    // RANSAC hypotheses
+    double* hyp_pose;                 // [n_seq][H][12]
+    int* hyp_count;                   // [n_seq][H]
+    int* inl_idx;                     // [n_seq][cap] ascending inlier indices
+    int cap;                          // per-sequence feature capacity
+    int n_seq;
+    int n_hyp;
+};
+
+struct PipeConfig {
+    int width, height;
+    int features_threshold;      // 15
+    int pre_matching_threshold;  // 100
+    int thr_hi, thr_lo;          // FAST_THRESHOLD, FAST_THRESHOLD / 4
+    float circular_threshold;
+    float reproj_thr_sq;         // (float)(8*8)
+    double max_t_norm, max_r_norm;
+    uint64_t seed;
+    int check_bounds;            // in-bounds test of matchingFeatures (vo.cpp:341-359)
+    int age_increment;           // ages++ of stereo_callback (vo.cpp:70-72)
+    LkConfig lk;
+    Intrinsics K;
+    float Pl[12], Pr[12];
+};
+
+}  // namespace svo

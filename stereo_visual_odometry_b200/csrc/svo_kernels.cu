@@ -1,0 +1,928 @@
+// svo_kernels.cu -- hand-written sm_100a kernels of the stereo-VO front end.
+//
+// Stage map (reference call stack):
+//   fast_kernel            cv::FAST + NMS (feature_set.cpp:55-68) and the age-0 half of
+//                          filterByBucketLocation (feature_set.cpp:95-147): per-bucket winners
+//   pyrdown / ctx_* ingest cv::buildOpticalFlowPyramid image levels (vo.cpp:50-53, 200-201)
+//   bucket_merge_kernel    appendFeaturesFromImage + bucketing + low-threshold retry (vo.cpp:325-332)
+//   klt_kernel             the 4 calcOpticalFlowPyrLK legs L0->L1->R1->R0->L0 (vo.cpp:203-215)
+//   select_kernel          findClosePoints + status AND + bounds + compaction (vo.cpp:217-238,
+//                          341-364), ages++ (vo.cpp:70-72), triangulation (vo.cpp:89-94)
+//   pnp_hyp_kernel / pnp_final_kernel   cameraToWorld (vo.cpp:282-313) + the failure gates of
+//                          stereo_callback (vo.cpp:106-136)
+#include <stdio.h>
+
+#include "svo_kernels.cuh"
+
+namespace svo {
+
+// ============================================================================
+// helpers
+struct WarpRed {
+    static __device__ __forceinline__ int sum(int v) { return __reduce_add_sync(0xffffffffu, v); }
+    // |v| < 2^27 per lane (4 window pixels x 8160 x 4080)
+    static __device__ __forceinline__ long long sum64(long long v) {
+        const unsigned u = (unsigned)((int)v + (1 << 27));
+        const unsigned lo = __reduce_add_sync(0xffffffffu, u & 0xFFFFu);
+        const unsigned hi = __reduce_add_sync(0xffffffffu, u >> 16);
+        return ((long long)hi << 16) + (long long)lo - (32ll << 27);
+    }
+    static __device__ __forceinline__ void sync() { __syncwarp(); }
+};
+
+// exclusive scan of one int per thread over the block; returns the offset, *total = sum
+template <int NT>
+__device__ __forceinline__ int block_excl_scan(int v, int* total, int* smem /* NT/32 + 1 ints */) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    __syncthreads();   // protect smem reuse across calls
+    if (lane == 31) smem[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int w = (lane < NT / 32) ? smem[lane] : 0;
+        int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += n;
+        }
+        if (lane < NT / 32) smem[lane] = wi - w;
+        if (lane == 31) smem[NT / 32] = wi;
+    }
+    __syncthreads();
+    *total = smem[NT / 32];
+    return smem[wid] + incl - v;
+}
+
+__device__ __forceinline__ unsigned long long ld_key(const unsigned long long* p) {
+    return __ldcg(p);   // keys are produced by L2 atomics: bypass L1
+}
+
+// ============================================================================
+// FAST-9/16 + 3x3 NMS.  One block = 64x16 output pixels; the 72x24 u8 tile and the
+// 66x18 score tile live in shared memory.
+constexpr int FT_W = 64, FT_H = 16, FT_THREADS = 256;
+constexpr int FT_TP = FT_W + 8 + 8;    // tile pitch (80)
+constexpr int FT_SP = FT_W + 2 + 2;    // score pitch (68)
+
+__device__ __forceinline__ bool has_arc9(unsigned m) {
+    // any 9 contiguous (circular) set bits among 16
+    unsigned x = m | (m << 16);
+    x &= x >> 1;
+    x &= x >> 2;
+    x &= x >> 4;    // runs of 8
+    x &= x >> 1;    // runs of 9
+    return (x & 0xFFFFu) != 0;
+}
+
+__global__ void __launch_bounds__(FT_THREADS)
+fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h, int pitch, int thr_lo,
+            int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
+            unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
+            BucketGeom bg) {
+    __shared__ __align__(16) uint8_t tile[(FT_H + 8) * FT_TP];
+    __shared__ uint8_t score[(FT_H + 2) * FT_SP];
+    const int z = blockIdx.z;
+    const uint8_t* src = img + (long long)z * img_stride;
+    const int x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H;
+    const int tid = threadIdx.x;
+
+    // ---- load tile rows [y0-4, y0+FT_H+4) x cols [x0-4, x0+FT_W+4), clamped (clamped
+    // values are only ever read for pixels whose score is forced to 0)
+    for (int i = tid; i < (FT_H + 8) * (FT_W + 8); i += FT_THREADS) {
+        const int ty = i / (FT_W + 8), tx = i - ty * (FT_W + 8);
+        const int gy = min(max(y0 - 4 + ty, 0), h - 1), gx = min(max(x0 - 4 + tx, 0), w - 1);
+        tile[ty * FT_TP + tx] = __ldg(src + (long long)gy * pitch + gx);
+    }
+    __syncthreads();
+
+    // ---- scores on the (FT_W+2) x (FT_H+2) region
+    constexpr int RDX[16] = SVO_FAST_RING_DX;
+    constexpr int RDY[16] = SVO_FAST_RING_DY;
+    for (int i = tid; i < (FT_H + 2) * (FT_W + 2); i += FT_THREADS) {
+        const int sy = i / (FT_W + 2), sx = i - sy * (FT_W + 2);
+        const int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
+        int resp = 0;
+        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3) {
+            const uint8_t* c = tile + (sy + 3) * FT_TP + (sx + 3);
+            const int v = c[0];
+            int r[16];
+            unsigned mb = 0, md = 0;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                r[k] = c[RDY[k] * FT_TP + RDX[k]];
+                mb |= (r[k] > v + thr_lo) ? (1u << k) : 0u;
+                md |= (r[k] < v - thr_lo) ? (1u << k) : 0u;
+            }
+            if (has_arc9(mb) || has_arc9(md)) resp = fast9_arc_score(v, r) - 1;
+        }
+        score[sy * FT_SP + sx] = (uint8_t)resp;
+    }
+    __syncthreads();
+
+    // ---- NMS (strict maximum over the 8 neighbours) + outputs
+    for (int i = tid; i < FT_H * FT_W; i += FT_THREADS) {
+        const int oy = i / FT_W, ox = i - oy * FT_W;
+        const int gx = x0 + ox, gy = y0 + oy;
+        if (gx >= w || gy >= h) continue;
+        const uint8_t* s = score + (oy + 1) * FT_SP + (ox + 1);
+        const int v = s[0];
+        const bool keep = v > 0 && v > s[-1] && v > s[1] && v > s[-FT_SP - 1] && v > s[-FT_SP] &&
+                          v > s[-FT_SP + 1] && v > s[FT_SP - 1] && v > s[FT_SP] && v > s[FT_SP + 1];
+        if (resp_map) resp_map[(long long)z * map_stride + (long long)gy * map_pitch + gx] = keep ? (uint8_t)v : 0;
+        if (keep && keysB) {
+            const int br = gy / bg.bh, bc = gx / bg.bw;
+            if (br >= bg.start_row && 0 < bg.age_threshold) {
+                const unsigned long long key =
+                    bucket_key(bucket_score(0, v, bg.fast_threshold), SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
+                const long long b = (long long)z * bg.nb + br * bg.n_bw + bc;
+                atomicMax(keysB + b, key);
+                if (v >= thr_hi) atomicMax(keysA + b, key);
+            }
+        }
+    }
+}
+
+void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
+                 int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
+                 unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st) {
+    dim3 grid((w + FT_W - 1) / FT_W, (h + FT_H - 1) / FT_H, n_img);
+    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map,
+                                             map_stride, map_pitch, keysA, keysB, bg);
+}
+
+// ---- ordered compaction of the response map (row-major == cv::FAST output order)
+__global__ void kp_rowcount_kernel(const uint8_t* __restrict__ map, int w, int h, int pitch, int thr,
+                                   int* __restrict__ row_count) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= h) return;
+    int c = 0;
+    for (int x = lane; x < w; x += 32) c += (map[(long long)row * pitch + x] >= thr) ? 1 : 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) row_count[row] = c;
+}
+__global__ void __launch_bounds__(1024) scan_kernel(int* __restrict__ v, int n, int* __restrict__ total_out) {
+    __shared__ int sm[33];
+    const int chunk = (n + 1023) / 1024;
+    const int b0 = min(n, (int)threadIdx.x * chunk), b1 = min(n, b0 + chunk);
+    int s = 0;
+    for (int i = b0; i < b1; ++i) s += v[i];
+    int total;
+    int off = block_excl_scan<1024>(s, &total, sm);
+    for (int i = b0; i < b1; ++i) {
+        const int c = v[i];
+        v[i] = off;
+        off += c;
+    }
+    if (threadIdx.x == 0 && total_out) *total_out = total;
+}
+__global__ void kp_write_kernel(const uint8_t* __restrict__ map, int w, int h, int pitch, int thr,
+                                const int* __restrict__ row_off, float2* __restrict__ xy,
+                                float* __restrict__ resp, int cap) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= h) return;
+    int base = row_off[row];
+    for (int x0 = 0; x0 < w; x0 += 32) {
+        const int x = x0 + lane;
+        const int v = (x < w) ? map[(long long)row * pitch + x] : 0;
+        const bool k = v >= thr && v > 0;
+        const unsigned m = __ballot_sync(0xffffffffu, k);
+        if (k) {
+            const int o = base + __popc(m & ((1u << lane) - 1));
+            if (o < cap) {
+                xy[o] = make_float2((float)x, (float)row);
+                resp[o] = (float)v;
+            }
+        }
+        base += __popc(m);
+    }
+}
+void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pitch, int thr, int* row_count,
+                              float2* xy_out, float* resp_out, int cap, int* n_out, cudaStream_t st) {
+    const int wpb = 8;
+    kp_rowcount_kernel<<<(h + wpb - 1) / wpb, wpb * 32, 0, st>>>(resp_map, w, h, map_pitch, thr, row_count);
+    scan_kernel<<<1, 1024, 0, st>>>(row_count, h, n_out);
+    kp_write_kernel<<<(h + wpb - 1) / wpb, wpb * 32, 0, st>>>(resp_map, w, h, map_pitch, thr, row_count, xy_out,
+                                                              resp_out, cap);
+}
+
+// ============================================================================
+// pyrDown
+struct GlobalImg {
+    const uint8_t* p;
+    int pitch;
+    __device__ __forceinline__ int operator()(int x, int y) const { return __ldg(p + (long long)y * pitch + x); }
+};
+__global__ void __launch_bounds__(256)
+pyrdown_kernel(const uint8_t* __restrict__ src, long long src_stride, int sw, int sh, int spitch,
+               uint8_t* __restrict__ dst, long long dst_stride, int dw, int dh, int dpitch) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= dw || y >= dh) return;
+    GlobalImg g{src + (long long)blockIdx.z * src_stride, spitch};
+    dst[(long long)blockIdx.z * dst_stride + (long long)y * dpitch + x] = (uint8_t)pyrdown_pixel(g, sw, sh, x, y);
+}
+void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch, uint8_t* dst,
+                    long long dst_stride, int dw, int dh, int dpitch, int n_img, cudaStream_t st) {
+    dim3 grid((dw + 31) / 32, (dh + 7) / 8, n_img);
+    pyrdown_kernel<<<grid, 256, 0, st>>>(src, src_stride, sw, sh, spitch, dst, dst_stride, dw, dh, dpitch);
+}
+
+// ---- context ingest: slot chosen on the device from SeqState
+__device__ __forceinline__ int ingest_slot(const SeqState* s, int first_frame) {
+    return first_frame ? 0 : (s->slot ^ 1);
+}
+// z = seq * 2 + cam
+__global__ void __launch_bounds__(256)
+ctx_copy_level0_kernel(DevArrays d, PyrGeom pg, const uint8_t* __restrict__ left,
+                       const uint8_t* __restrict__ right, int stride, long long seq_stride, int first_frame) {
+    const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
+    const int slot = ingest_slot(d.state + seq, first_frame);
+    const uint8_t* src = (cam ? right : left) + (long long)seq * seq_stride;
+    uint8_t* dst = d.pyr + pg.base(seq, slot, cam) + pg.off[0];
+    const int y = blockIdx.y;
+    const int w = pg.w[0];
+    const uint8_t* srow = src + (long long)y * stride;
+    uint8_t* drow = dst + (long long)y * pg.pitch[0];
+    const bool vec = ((((unsigned long long)src) | (unsigned long long)stride) & 15ull) == 0;
+    if (vec) {
+        const int nv = w >> 4;
+        for (int i = blockIdx.x * 256 + threadIdx.x; i < nv; i += gridDim.x * 256)
+            reinterpret_cast<uint4*>(drow)[i] = __ldg(reinterpret_cast<const uint4*>(srow) + i);
+        for (int x = (nv << 4) + blockIdx.x * 256 + threadIdx.x; x < w; x += gridDim.x * 256) drow[x] = srow[x];
+    } else {
+        for (int x = blockIdx.x * 256 + threadIdx.x; x < w; x += gridDim.x * 256) drow[x] = srow[x];
+    }
+}
+__global__ void __launch_bounds__(256)
+ctx_pyrdown_kernel(DevArrays d, PyrGeom pg, int level /* destination level >= 1 */, int first_frame) {
+    const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
+    const int slot = ingest_slot(d.state + seq, first_frame);
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= pg.w[level] || y >= pg.h[level]) return;
+    uint8_t* base = d.pyr + pg.base(seq, slot, cam);
+    GlobalImg g{base + pg.off[level - 1], pg.pitch[level - 1]};
+    // plain loads: the source level was written by the previous launch
+    base[pg.off[level] + (long long)y * pg.pitch[level] + x] =
+        (uint8_t)pyrdown_pixel(g, pg.w[level - 1], pg.h[level - 1], x, y);
+}
+
+void launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int first_frame,
+                   int parity, cudaStream_t st) {
+    {
+        dim3 grid(1, pg.h[0], d.n_seq * 2);
+        ctx_copy_level0_kernel<<<grid, 256, 0, st>>>(d, pg, left, right, stride, seq_stride, first_frame);
+    }
+    for (int l = 1; l < pg.nlevels; ++l) {
+        dim3 grid((pg.w[l] + 31) / 32, (pg.h[l] + 7) / 8, d.n_seq * 2);
+        ctx_pyrdown_kernel<<<grid, 256, 0, st>>>(d, pg, l, first_frame);
+    }
+    unsigned long long* keysA = d.fastkeys + ((long long)(parity * 2 + 0) * d.n_seq) * bg.nb;
+    unsigned long long* keysB = d.fastkeys + ((long long)(parity * 2 + 1) * d.n_seq) * bg.nb;
+    launch_fast(left, seq_stride, pc.width, pc.height, stride, d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, keysA,
+                keysB, bg, st);
+}
+
+// ============================================================================
+// first frame (vo.cpp:47-56): nothing but a "fail" result carrying last_transform
+__global__ void first_frame_kernel(DevArrays d) {
+    const int seq = blockIdx.x * blockDim.x + threadIdx.x;
+    if (seq >= d.n_seq) return;
+    SeqState* s = d.state + seq;
+    s->slot = 0;
+    s->frame_id = 1;
+    svo_frame_result* r = d.result + seq;
+    r->success = 0;
+    r->reason = SVO_REASON_FIRST_FRAME;
+    r->n_bucketed = r->n_matched = r->n_inliers = r->retry = r->pnp_ok = r->lk_iters = 0;
+    for (int i = 0; i < 9; ++i) r->R[i] = s->R[i];
+    for (int i = 0; i < 3; ++i) r->t[i] = s->t[i];
+    for (int i = 0; i < 16; ++i) r->transform[i] = s->last_T[i];
+}
+void launch_first_frame(const DevArrays& d, cudaStream_t st) {
+    first_frame_kernel<<<(d.n_seq + 127) / 128, 128, 0, st>>>(d);
+}
+
+// ============================================================================
+// bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry
+__global__ void __launch_bounds__(1024)
+bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
+    __shared__ int sm[33];
+    const int seq = blockIdx.x, tid = threadIdx.x;
+    SeqState* s = d.state + seq;
+    const long long fo = (long long)seq * d.cap;
+    unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
+    unsigned long long* keyA = d.fastkeys + ((long long)(parity * 2 + 0) * d.n_seq + seq) * bg.nb;
+    unsigned long long* keyB = d.fastkeys + ((long long)(parity * 2 + 1) * d.n_seq + seq) * bg.nb;
+    const int n = s->n_feat;
+
+    for (int i = tid; i < n; i += 1024) {
+        const float2 p = d.fs_xy[fo + i];
+        const int age = d.fs_age[fo + i], str = d.fs_str[fo + i];
+        const int br = (int)__fdiv_rn(p.y, (float)bg.bh), bc = (int)__fdiv_rn(p.x, (float)bg.bw);
+        if (br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw && age < bg.age_threshold)
+            atomicMax(keyT + br * bg.n_bw + bc, bucket_key(bucket_score(age, str, bg.fast_threshold), (unsigned)i, str));
+    }
+    __threadfence();
+    __syncthreads();
+
+    const int chunk = (bg.nb + 1023) / 1024;
+    const int b0 = min(bg.nb, tid * chunk), b1 = min(bg.nb, b0 + chunk);
+    int c1 = 0;
+    for (int b = b0; b < b1; ++b) {
+        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
+        c1 += ((kt > ka ? kt : ka) != 0ull) ? 1 : 0;
+    }
+    int n1;
+    block_excl_scan<1024>(c1, &n1, sm);
+    const bool retry = n1 < pc.pre_matching_threshold;
+
+    int c2 = 0;
+    for (int b = b0; b < b1; ++b) {
+        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
+        unsigned long long wv = kt > ka ? kt : ka;
+        if (retry) {
+            const unsigned long long kb = ld_key(keyB + b);
+            if (kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) wv = kb;
+        }
+        c2 += (wv != 0ull) ? 1 : 0;
+    }
+    int total;
+    int off = block_excl_scan<1024>(c2, &total, sm);
+    for (int b = b0; b < b1; ++b) {
+        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
+        unsigned long long wv = kt > ka ? kt : ka;
+        const unsigned long long kb = ld_key(keyB + b);
+        if (retry && kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) wv = kb;
+        if (wv != 0ull) {
+            const unsigned order = bucket_key_order(wv);
+            float2 p;
+            int age, str;
+            if (order >= SVO_FAST_ORDER_BASE) {
+                const int pix = (int)(order - SVO_FAST_ORDER_BASE);
+                const int y = pix / pc.width;
+                p = make_float2((float)(pix - y * pc.width), (float)y);
+                age = 0;
+                str = bucket_key_strength(wv);
+            } else {
+                p = d.fs_xy[fo + order];
+                age = d.fs_age[fo + order];
+                str = d.fs_str[fo + order];
+            }
+            if (off < d.cap) {
+                d.bk_xy[fo + off] = p;
+                d.bk_age[fo + off] = age;
+                d.bk_str[fo + off] = str;
+            }
+            ++off;
+        }
+        keyT[b] = 0ull;
+        keyA[b] = 0ull;
+        keyB[b] = 0ull;
+    }
+    if (tid == 0) {
+        s->n_bucketed = min(total, d.cap);
+        s->retry = retry ? 1 : 0;
+        s->lk_iters = 0;
+        s->frame_id += 1;
+    }
+}
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
+                         cudaStream_t st) {
+    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, parity);
+}
+
+// ============================================================================
+// KLT: one warp per feature, the whole circular chain L0->L1->R1->R0->L0 in one launch
+constexpr int KLT_WARPS = 8;
+__device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom& pg) {
+    LkPyramid p;
+#pragma unroll
+    for (int l = 0; l < SVO_MAX_LEVELS; ++l) {
+        p.lv[l].img = base + pg.off[l];
+        p.lv[l].w = pg.w[l];
+        p.lv[l].h = pg.h[l];
+        p.lv[l].pitch = pg.pitch[l];
+    }
+    return p;
+}
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc) {
+    __shared__ uint8_t patch[KLT_WARPS][SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    const int seq = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f = blockIdx.x * KLT_WARPS + wid;
+    SeqState* s = d.state + seq;
+    if (f >= s->n_bucketed) return;
+    const int slot = s->slot;
+    const LkPyramid L0 = make_pyr(d.pyr + pg.base(seq, slot, 0), pg);
+    const LkPyramid R0 = make_pyr(d.pyr + pg.base(seq, slot, 1), pg);
+    const LkPyramid L1 = make_pyr(d.pyr + pg.base(seq, slot ^ 1, 0), pg);
+    const LkPyramid R1 = make_pyr(d.pyr + pg.base(seq, slot ^ 1, 1), pg);
+    const long long o = (long long)seq * d.cap + f;
+    const float2 p0 = d.bk_xy[o];
+    float2 a, b, c, e;
+    int it, iters = 0;
+    unsigned st = 0;
+    st |= lk_track_feature<32, WarpRed>(L0, L1, pc.lk, p0.x, p0.y, lane, patch[wid], a.x, a.y, it) ? 1u : 0u;
+    iters += it;
+    st |= lk_track_feature<32, WarpRed>(L1, R1, pc.lk, a.x, a.y, lane, patch[wid], b.x, b.y, it) ? 2u : 0u;
+    iters += it;
+    st |= lk_track_feature<32, WarpRed>(R1, R0, pc.lk, b.x, b.y, lane, patch[wid], c.x, c.y, it) ? 4u : 0u;
+    iters += it;
+    st |= lk_track_feature<32, WarpRed>(R0, L0, pc.lk, c.x, c.y, lane, patch[wid], e.x, e.y, it) ? 8u : 0u;
+    iters += it;
+    if (lane == 0) {
+        d.lk_L1[o] = a;
+        d.lk_R1[o] = b;
+        d.lk_R0[o] = c;
+        d.lk_C[o] = e;
+        d.lk_status[o] = (uint8_t)st;
+        atomicAdd(&s->lk_iters, iters);
+    }
+}
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, cudaStream_t st) {
+    dim3 grid((d.cap + KLT_WARPS - 1) / KLT_WARPS, d.n_seq);
+    klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc);
+}
+
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+lk_single_kernel(LkPyramid I, LkPyramid J, LkConfig cfg, const float2* __restrict__ pts, int n,
+                 float2* __restrict__ out, uint8_t* __restrict__ status) {
+    __shared__ uint8_t patch[KLT_WARPS][SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f = blockIdx.x * KLT_WARPS + wid;
+    if (f >= n) return;
+    const float2 p = pts[f];
+    float2 q;
+    int it;
+    const int ok = lk_track_feature<32, WarpRed>(I, J, cfg, p.x, p.y, lane, patch[wid], q.x, q.y, it);
+    if (lane == 0) {
+        out[f] = q;
+        status[f] = (uint8_t)ok;
+    }
+}
+void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, const float2* pts, int n, float2* out,
+                      uint8_t* status, cudaStream_t st) {
+    if (n <= 0) return;
+    lk_single_kernel<<<(n + KLT_WARPS - 1) / KLT_WARPS, KLT_WARPS * 32, 0, st>>>(I, J, cfg, pts, n, out, status);
+}
+
+// ============================================================================
+// select: circular check + status AND + bounds, stable compaction, ages++, triangulation
+__global__ void __launch_bounds__(1024) select_kernel(DevArrays d, PipeConfig pc) {
+    __shared__ int sm[33];
+    const int seq = blockIdx.x, tid = threadIdx.x;
+    SeqState* s = d.state + seq;
+    const long long fo = (long long)seq * d.cap;
+    const int n = s->n_bucketed;
+    const int chunk = (n + 1023) / 1024;
+    const int i0 = min(n, tid * chunk), i1 = min(n, i0 + chunk);
+    const int W = pc.width, H = pc.height;
+    int cnt = 0;
+    for (int i = i0; i < i1; ++i) {
+        const float2 p0 = d.bk_xy[fo + i], l1 = d.lk_L1[fo + i], r1 = d.lk_R1[fo + i], r0 = d.lk_R0[fo + i],
+                     c = d.lk_C[fo + i];
+        bool ok = (d.lk_status[fo + i] & 15) == 15 && close_points(p0.x, p0.y, c.x, c.y, pc.circular_threshold);
+        if (pc.check_bounds)
+            ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(l1.x, l1.y, W, H) && in_bounds(r0.x, r0.y, W, H) &&
+                 in_bounds(r1.x, r1.y, W, H);
+        cnt += ok ? 1 : 0;
+    }
+    int total;
+    int off = block_excl_scan<1024>(cnt, &total, sm);
+    for (int i = i0; i < i1; ++i) {
+        const float2 p0 = d.bk_xy[fo + i], l1 = d.lk_L1[fo + i], r1 = d.lk_R1[fo + i], r0 = d.lk_R0[fo + i],
+                     c = d.lk_C[fo + i];
+        bool ok = (d.lk_status[fo + i] & 15) == 15 && close_points(p0.x, p0.y, c.x, c.y, pc.circular_threshold);
+        if (pc.check_bounds)
+            ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(l1.x, l1.y, W, H) && in_bounds(r0.x, r0.y, W, H) &&
+                 in_bounds(r1.x, r1.y, W, H);
+        if (ok) d.lk_status[fo + i] |= 16;   // is_ok mask over the inputs (parity tap)
+        if (ok) {
+            const int age = d.bk_age[fo + i] + pc.age_increment, str = d.bk_str[fo + i];   // ages++ (vo.cpp:70-72)
+            d.m_L0[fo + off] = p0;
+            d.m_L1[fo + off] = l1;
+            d.m_R0[fo + off] = r0;
+            d.m_R1[fo + off] = r1;
+            d.m_age[fo + off] = age;
+            d.m_str[fo + off] = str;
+            // currentVOFeatures after matchingFeatures: t0 coordinates (vo.cpp:360)
+            d.fs_xy[fo + off] = p0;
+            d.fs_age[fo + off] = age;
+            d.fs_str[fo + off] = str;
+            ++off;
+        }
+    }
+    __syncthreads();
+    // triangulation (only consumed when enough features survive; cheap enough to always run)
+    for (int i = tid; i < total; i += 1024) {
+        const float2 a = d.m_L0[fo + i], b = d.m_R0[fo + i];
+        triangulate_dlt(pc.Pl, pc.Pr, a.x, a.y, b.x, b.y, d.X3 + (fo + i) * 3);
+    }
+    if (tid == 0) {
+        s->n_matched = total;
+        s->n_feat = total;
+        s->n_inliers = 0;
+        s->pnp_ok = 0;
+        if (n > 0) s->slot ^= 1;   // lastLeft/RightPyramid = pyramid(l1/r1) (vo.cpp:231-232); not when n == 0 (179-181)
+    }
+}
+void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+    select_kernel<<<d.n_seq, 1024, 0, st>>>(d, pc);
+}
+
+// ============================================================================
+// PnP-RANSAC: parallel 5-point hypotheses (LM from the extrinsic guess, like
+// solvePnP(ITERATIVE, useExtrinsicGuess) inside OpenCV's RANSAC loop), inlier counting
+// by warp reduction, then an FP64 LM refit on the inliers of the best hypothesis.
+constexpr int HYP_WARPS = 4;
+
+struct FivePointEval {
+    const float* X;   // 5 x 3
+    const float* U;   // 5 x 2
+    Intrinsics K;
+    __device__ void operator()(const Pose& P, double* acc, bool jac) const {
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = 0.0;
+        for (int i = 0; i < 5; ++i) pnp_accumulate(P, K, X + 3 * i, U + 2 * i, acc, jac);
+    }
+};
+
+__global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, PipeConfig pc) {
+    const int seq = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int hyp = blockIdx.x * HYP_WARPS + wid;
+    SeqState* s = d.state + seq;
+    const int n = s->n_matched;
+    const int min_n = max(4, pc.features_threshold);
+    if (hyp >= d.n_hyp || n <= min_n) return;   // vo.cpp:82-84
+    const long long fo = (long long)seq * d.cap;
+    const float* X3 = d.X3 + fo * 3;
+    const float2* uv = d.m_L1 + fo;
+
+    Pose P;
+    if (lane == 0) {
+        int idx[5];
+        sample5(pc.seed, ((uint64_t)(unsigned)s->frame_id << 24) ^ ((uint64_t)seq << 48) ^ (uint64_t)hyp, n, idx);
+        float X[15], U[10];
+        for (int i = 0; i < 5; ++i) {
+            X[3 * i] = X3[3 * idx[i]];
+            X[3 * i + 1] = X3[3 * idx[i] + 1];
+            X[3 * i + 2] = X3[3 * idx[i] + 2];
+            const float2 q = uv[idx[i]];
+            U[2 * i] = q.x;
+            U[2 * i + 1] = q.y;
+        }
+        for (int i = 0; i < 9; ++i) P.R[i] = s->R[i];
+        for (int i = 0; i < 3; ++i) P.t[i] = s->t[i];
+        FivePointEval ev{X, U, pc.K};
+        pnp_refine_lm(P, ev, 20);
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) P.R[i] = __shfl_sync(0xffffffffu, P.R[i], 0);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) P.t[i] = __shfl_sync(0xffffffffu, P.t[i], 0);
+    int cnt = 0;
+    for (int i = lane; i < n; i += 32) {
+        const float2 q = uv[i];
+        const float uvf[2] = {q.x, q.y};
+        const float e = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf);
+        cnt += (e <= pc.reproj_thr_sq) ? 1 : 0;
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0) {
+        double* hp = d.hyp_pose + ((long long)seq * d.n_hyp + hyp) * 12;
+        for (int i = 0; i < 9; ++i) hp[i] = P.R[i];
+        for (int i = 0; i < 3; ++i) hp[9 + i] = P.t[i];
+        // a diverged LM (NaN pose) must never win
+        bool finite = true;
+        for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
+        for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
+        d.hyp_count[(long long)seq * d.n_hyp + hyp] = finite ? cnt : 0;
+    }
+}
+
+constexpr int FIN_THREADS = 512;
+struct BlockInlierEval {
+    const float* X3;
+    const float2* uv;
+    const int* idx;
+    int n;
+    Intrinsics K;
+    double* sm;   // [FIN_THREADS/32][SVO_PNP_ACC]
+    __device__ void operator()(const Pose& P, double* acc, bool jac) const {
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = 0.0;
+        for (int i = threadIdx.x; i < n; i += FIN_THREADS) {
+            const int k = idx[i];
+            const float2 q = uv[k];
+            const float uvf[2] = {q.x, q.y};
+            pnp_accumulate(P, K, X3 + 3 * k, uvf, acc, jac);
+        }
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) {
+            double v = acc[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            acc[i] = v;
+        }
+        __syncthreads();
+        if (lane == 0) {
+#pragma unroll
+            for (int i = 0; i < SVO_PNP_ACC; ++i) sm[wid * SVO_PNP_ACC + i] = acc[i];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) {
+            double v = 0.0;
+            for (int w = 0; w < FIN_THREADS / 32; ++w) v += sm[w * SVO_PNP_ACC + i];
+            acc[i] = v;
+        }
+    }
+};
+
+__device__ void write_result(const DevArrays& d, int seq, int success, int reason, const double* T) {
+    SeqState* s = d.state + seq;
+    svo_frame_result* r = d.result + seq;
+    r->success = success;
+    r->reason = reason;
+    r->n_bucketed = s->n_bucketed;
+    r->n_matched = s->n_matched;
+    r->n_inliers = s->n_inliers;
+    r->retry = s->retry;
+    r->pnp_ok = s->pnp_ok;
+    r->lk_iters = s->lk_iters;
+    for (int i = 0; i < 9; ++i) r->R[i] = s->R[i];
+    for (int i = 0; i < 3; ++i) r->t[i] = s->t[i];
+    for (int i = 0; i < 16; ++i) r->transform[i] = T[i];
+}
+
+__global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, PipeConfig pc) {
+    __shared__ int sm_i[33];
+    __shared__ unsigned sm_best[FIN_THREADS / 32];
+    __shared__ double sm_acc[(FIN_THREADS / 32) * SVO_PNP_ACC];
+    const int seq = blockIdx.x, tid = threadIdx.x;
+    const int lane = tid & 31, wid = tid >> 5;
+    SeqState* s = d.state + seq;
+    const long long fo = (long long)seq * d.cap;
+    const int n = s->n_matched;
+    const int min_n = max(4, pc.features_threshold);
+    if (n <= min_n) {   // vo.cpp:82-84
+        if (tid == 0) write_result(d, seq, 0, SVO_REASON_FEW_FEATURES, s->last_T);
+        return;
+    }
+    // ---- best hypothesis: max inlier count, ties -> lowest index
+    unsigned best = 0;
+    for (int h = tid; h < d.n_hyp; h += FIN_THREADS) {
+        const unsigned c = (unsigned)d.hyp_count[(long long)seq * d.n_hyp + h];
+        const unsigned key = (c << 12) | (unsigned)(4095 - h);
+        best = max(best, key);
+    }
+    best = __reduce_max_sync(0xffffffffu, best);
+    if (lane == 0) sm_best[wid] = best;
+    __syncthreads();
+    best = 0;
+    for (int w = 0; w < FIN_THREADS / 32; ++w) best = max(best, sm_best[w]);
+    const int best_cnt = (int)(best >> 12), best_h = 4095 - (int)(best & 4095u);
+    if (best_cnt < 5) {   // no model: solvePnPRansac returns false, translation restored (vo.cpp:309-311)
+        if (tid == 0) {
+            s->pnp_ok = 0;
+            s->n_inliers = 0;
+            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
+        }
+        return;
+    }
+    Pose P;
+    {
+        const double* hp = d.hyp_pose + ((long long)seq * d.n_hyp + best_h) * 12;
+        for (int i = 0; i < 9; ++i) P.R[i] = hp[i];
+        for (int i = 0; i < 3; ++i) P.t[i] = hp[9 + i];
+    }
+    // ---- inlier mask of the best model -> ascending index list
+    const float* X3 = d.X3 + fo * 3;
+    const float2* uv = d.m_L1 + fo;
+    int* idx = d.inl_idx + fo;
+    const int chunk = (n + FIN_THREADS - 1) / FIN_THREADS;
+    const int i0 = min(n, tid * chunk), i1 = min(n, i0 + chunk);
+    int cnt = 0;
+    for (int i = i0; i < i1; ++i) {
+        const float2 q = uv[i];
+        const float uvf[2] = {q.x, q.y};
+        cnt += (reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq) ? 1 : 0;
+    }
+    int n_in;
+    int off = block_excl_scan<FIN_THREADS>(cnt, &n_in, sm_i);
+    for (int i = i0; i < i1; ++i) {
+        const float2 q = uv[i];
+        const float uvf[2] = {q.x, q.y};
+        if (reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq) idx[off++] = i;
+    }
+    __syncthreads();
+    // ---- LM refit on all inliers (uniform control flow across the block)
+    BlockInlierEval ev{X3, uv, idx, n_in, pc.K, sm_acc};
+    pnp_refine_lm(P, ev, 20);
+    bool finite = true;
+    for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
+    for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
+    if (!finite) {
+        if (tid == 0) {
+            s->pnp_ok = 0;
+            s->n_inliers = 0;
+            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
+        }
+        return;
+    }
+    const bool enough = n_in >= pc.features_threshold;
+    if (enough) {
+        // currentVOFeatures.points = pointsLeftT1; keep inliers (vo.cpp:115-121).  fs_* currently
+        // holds the matched set at t0 coordinates; idx[i] >= i so the in-order rewrite is safe
+        // per element only after a barrier: stage through registers.
+        for (int base = 0; base < n_in; base += FIN_THREADS) {
+            const int i = base + tid;
+            float2 p = make_float2(0.f, 0.f);
+            int age = 0, str = 0;
+            if (i < n_in) {
+                const int k = idx[i];
+                p = d.m_L1[fo + k];
+                age = d.m_age[fo + k];
+                str = d.m_str[fo + k];
+            }
+            if (i < n_in) {
+                d.fs_xy[fo + i] = p;
+                d.fs_age[fo + i] = age;
+                d.fs_str[fo + i] = str;
+            }
+        }
+    }
+    if (tid == 0) {
+        s->pnp_ok = 1;
+        s->n_inliers = n_in;
+        for (int i = 0; i < 9; ++i) s->R[i] = P.R[i];   // rotation / translation overwritten on PnP success
+        for (int i = 0; i < 3; ++i) s->t[i] = P.t[i];
+        if (!enough) {   // vo.cpp:106-113
+            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
+            return;
+        }
+        s->n_feat = n_in;
+        const double tn = sqrt(P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
+        const double ang = rotation_angle(P.R);
+        if (tn > pc.max_t_norm || ang > pc.max_r_norm) {   // vo.cpp:123-132
+            write_result(d, seq, 0, SVO_REASON_TOO_BIG, s->last_T);
+            return;
+        }
+        // getInverseTransform (vo.cpp:246-258): inverse of the rigid [R|t]
+        double T[16];
+        for (int i = 0; i < 3; ++i) {
+            for (int j = 0; j < 3; ++j) T[i * 4 + j] = P.R[j * 3 + i];
+            T[i * 4 + 3] = -(P.R[0 * 3 + i] * P.t[0] + P.R[1 * 3 + i] * P.t[1] + P.R[2 * 3 + i] * P.t[2]);
+        }
+        T[12] = T[13] = T[14] = 0.0;
+        T[15] = 1.0;
+        for (int i = 0; i < 16; ++i) s->last_T[i] = T[i];
+        write_result(d, seq, 1, SVO_REASON_OK, T);
+    }
+}
+void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+    dim3 grid((d.n_hyp + HYP_WARPS - 1) / HYP_WARPS, d.n_seq);
+    pnp_hyp_kernel<<<grid, HYP_WARPS * 32, 0, st>>>(d, pc);
+    pnp_final_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);
+}
+
+// ============================================================================
+// stage-level helpers for the stateless API
+__global__ void triangulate_kernel(const float* __restrict__ Pl, const float* __restrict__ Pr,
+                                   const float2* __restrict__ pL, const float2* __restrict__ pR, int n,
+                                   float* __restrict__ X3) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float l[12], r[12];
+    for (int k = 0; k < 12; ++k) {
+        l[k] = Pl[k];
+        r[k] = Pr[k];
+    }
+    triangulate_dlt(l, r, pL[i].x, pL[i].y, pR[i].x, pR[i].y, X3 + 3 * (long long)i);
+}
+void launch_triangulate(const float* Pl_dev, const float* Pr_dev, const float2* pL, const float2* pR, int n,
+                        float* X3, cudaStream_t st) {
+    if (n <= 0) return;
+    triangulate_kernel<<<(n + 127) / 128, 128, 0, st>>>(Pl_dev, Pr_dev, pL, pR, n, X3);
+}
+
+__global__ void __launch_bounds__(1024)
+compact_bytes_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int elem, int n,
+                     const uint8_t* __restrict__ keep, int* __restrict__ n_out) {
+    __shared__ int sm[33];
+    const int chunk = (n + 1023) / 1024;
+    const int i0 = min(n, (int)threadIdx.x * chunk), i1 = min(n, i0 + chunk);
+    int c = 0;
+    for (int i = i0; i < i1; ++i) c += keep[i] ? 1 : 0;
+    int total;
+    int off = block_excl_scan<1024>(c, &total, sm);
+    for (int i = i0; i < i1; ++i)
+        if (keep[i]) {
+            for (int b = 0; b < elem; ++b) dst[(long long)off * elem + b] = src[(long long)i * elem + b];
+            ++off;
+        }
+    if (threadIdx.x == 0) *n_out = total;
+}
+void launch_compact_bytes(const uint8_t* src, uint8_t* dst, int elem_bytes, int n, const uint8_t* keep, int* n_out,
+                          cudaStream_t st) {
+    compact_bytes_kernel<<<1, 1024, 0, st>>>(src, dst, elem_bytes, n, keep, n_out);
+}
+
+__global__ void close_points_kernel(const float2* __restrict__ a, const float2* __restrict__ b, int n, float thr,
+                                    uint8_t* __restrict__ ok) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) ok[i] = close_points(a[i].x, a[i].y, b[i].x, b[i].y, thr) ? 1 : 0;
+}
+void launch_close_points(const float2* a, const float2* b, int n, float thr, uint8_t* ok, cudaStream_t st) {
+    if (n <= 0) return;
+    close_points_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, n, thr, ok);
+}
+
+// ---- generic bucketing (any features_per_bucket): exact Bucket::add_feature semantics.
+// scratch layout (ints): bidx[n] | cnt[nb] | kept[nb + 1] | slots[nb * per_bucket]
+__global__ void bucket_index_kernel(const float2* __restrict__ xy, int n, BucketGeom bg, int* __restrict__ bidx,
+                                    int* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int br = (int)__fdiv_rn(xy[i].y, (float)bg.bh), bc = (int)__fdiv_rn(xy[i].x, (float)bg.bw);
+    int b = -1;
+    if (br >= 0 && br < bg.n_bh && bc >= 0 && bc < bg.n_bw) {
+        b = br * bg.n_bw + bc;
+        atomicAdd(cnt + b, 1);
+    }
+    bidx[i] = b;
+}
+__global__ void bucket_fill_kernel(const int* __restrict__ ages, const int* __restrict__ strengths, int n,
+                                   BucketGeom bg, int per_bucket, const int* __restrict__ bidx,
+                                   const int* __restrict__ cnt, int* __restrict__ kept, int* __restrict__ slots) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bg.nb) return;
+    int size = 0;
+    const int max_size = (b / bg.n_bw >= bg.start_row) ? per_bucket : 0;   // feature_set.cpp:112-116
+    if (cnt[b] > 0 && max_size > 0) {
+        int* sl = slots + (long long)b * per_bucket;
+        int seen = 0;
+        for (int i = 0; i < n && seen < cnt[b]; ++i) {
+            if (bidx[i] != b) continue;
+            ++seen;
+            const int age = ages[i], str = strengths[i];
+            if (age >= bg.age_threshold) continue;
+            if (size < max_size) {
+                sl[size++] = i;
+            } else {
+                const int score = bucket_score(age, str, bg.fast_threshold);
+                int smin = bucket_score(ages[sl[0]], strengths[sl[0]], bg.fast_threshold), imin_ = 0;
+                for (int k = 1; k < size; ++k) {
+                    const int sc = bucket_score(ages[sl[k]], strengths[sl[k]], bg.fast_threshold);
+                    if (sc < smin) {
+                        smin = sc;
+                        imin_ = k;
+                    }
+                }
+                if (score > smin) sl[imin_] = i;
+            }
+        }
+    }
+    kept[b] = size;
+}
+__global__ void bucket_emit_kernel(const float2* __restrict__ xy, const int* __restrict__ ages,
+                                   const int* __restrict__ strengths, BucketGeom bg, int per_bucket,
+                                   const int* __restrict__ kept_off, const int* __restrict__ slots,
+                                   float2* __restrict__ xy_out, int* __restrict__ age_out, int* __restrict__ str_out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bg.nb) return;
+    const int o0 = kept_off[b], o1 = kept_off[b + 1];
+    for (int k = 0; k < o1 - o0; ++k) {
+        const int i = slots[(long long)b * per_bucket + k];
+        xy_out[o0 + k] = xy[i];
+        age_out[o0 + k] = ages[i];
+        str_out[o0 + k] = strengths[i];
+    }
+}
+void launch_bucket_generic(float2* xy, int* ages, int* strengths, int n, BucketGeom bg, int per_bucket, int* scratch,
+                           float2* xy_out, int* age_out, int* str_out, int* n_out, cudaStream_t st) {
+    int* bidx = scratch;
+    int* cnt = bidx + n;
+    int* kept = cnt + bg.nb;
+    int* slots = kept + bg.nb + 1;
+    cudaMemsetAsync(cnt, 0, sizeof(int) * (2 * (size_t)bg.nb + 1), st);
+    if (n > 0) bucket_index_kernel<<<(n + 255) / 256, 256, 0, st>>>(xy, n, bg, bidx, cnt);
+    bucket_fill_kernel<<<(bg.nb + 127) / 128, 128, 0, st>>>(ages, strengths, n, bg, per_bucket, bidx, cnt, kept, slots);
+    scan_kernel<<<1, 1024, 0, st>>>(kept, bg.nb + 1, nullptr);
+    bucket_emit_kernel<<<(bg.nb + 127) / 128, 128, 0, st>>>(xy, ages, strengths, bg, per_bucket, kept, slots, xy_out,
+                                                            age_out, str_out);
+    cudaMemcpyAsync(n_out, kept + bg.nb, sizeof(int), cudaMemcpyDeviceToDevice, st);
+}
+
+}  // namespace svo

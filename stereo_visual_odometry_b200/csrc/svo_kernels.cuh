@@ -1,0 +1,53 @@
+// svo_kernels.cuh -- launch wrappers of the sm_100a kernels (definitions in svo_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "svo_device.cuh"
+
+namespace svo {
+
+// ---- ingest: level-0 copy, FAST-9/16 + NMS (+ per-bucket winners), pyrDown ----
+// FAST over `n_img` images (image i at img + i * img_stride).  Any of resp_map /
+// keysA / keysB may be null.  resp_map: dense u8 (pitch = map_pitch) holding the
+// keypoint response at NMS survivors with response >= thr_lo, 0 elsewhere.
+void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
+                 int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
+                 unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg,
+                 cudaStream_t st);
+// ordered (row-major) compaction of a dense response map into a keypoint list
+void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pitch, int thr,
+                              int* row_count /*[h+1] scratch*/, float2* xy_out, float* resp_out,
+                              int cap, int* n_out, cudaStream_t st);
+// generic pyrDown: n_img images, src/dst strides in bytes
+void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch,
+                    uint8_t* dst, long long dst_stride, int dw, int dh, int dpitch, int n_img,
+                    cudaStream_t st);
+// context ingest: copies the new frame (left/right planes, n_seq each) into level 0 of
+// slot (state.slot ^ 1) (slot 0 on the first frame), builds levels 1.., runs FAST on the
+// new LEFT image into fastkeys[parity].
+void launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
+                   int first_frame, int parity, cudaStream_t st);
+
+// ---- per-frame pipeline stages (all sequences of the context per launch) ----
+void launch_first_frame(const DevArrays& d, cudaStream_t st);
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
+                         cudaStream_t st);
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, cudaStream_t st);
+void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+
+// ---- stage-level helpers used by the stateless API ----
+void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, const float2* pts, int n,
+                      float2* out, uint8_t* status, cudaStream_t st);
+void launch_bucket_generic(float2* xy, int* ages, int* strengths, int n, BucketGeom bg,
+                           int per_bucket, int* scratch /* see svo_capi.cu */, float2* xy_out,
+                           int* age_out, int* str_out, int* n_out, cudaStream_t st);
+void launch_triangulate(const float* Pl_dev, const float* Pr_dev, const float2* pL, const float2* pR,
+                        int n, float* X3, cudaStream_t st);
+void launch_compact_bytes(const uint8_t* src, uint8_t* dst, int elem_bytes, int n, const uint8_t* keep,
+                          int* n_out, cudaStream_t st);
+void launch_close_points(const float2* a, const float2* b, int n, float thr, uint8_t* ok,
+                         cudaStream_t st);
+
+}  // namespace svo
