@@ -56,7 +56,7 @@ typedef struct svo_params {
     float circular_threshold;     /* .15  vo.h CIRCULAR_MATCHING_SUCCESS_THRESHOLD */
     float ransac_reproj_error;    /* 8    vo.h RANSAC_REPROJECTION_ERROR         */
     int ransac_iterations;        /* 100  vo.h RANSAC_ITERATIONS (reference's sequential cap) */
-    int ransac_hypotheses;        /* parallel hypotheses scored per frame (B200 design, default 256) */
+    int ransac_hypotheses;        /* hypotheses scored in parallel per frame (default 100 = the cap above) */
     float ransac_confidence;      /* .98  vo.cpp:295 (kept for the record)       */
     double max_translation_norm;  /* .1   vo.h MAX_TRANSLATION_NORM              */
     double max_rotation_norm;     /* .5   vo.h MAX_ROTATION_NORM                 */

@@ -67,7 +67,7 @@ extern "C" void svo_default_params(svo_params* p, int width, int height) {
     p->circular_threshold = 0.15f;
     p->ransac_reproj_error = 8.f;
     p->ransac_iterations = 100;
-    p->ransac_hypotheses = 256;
+    p->ransac_hypotheses = 100;
     p->ransac_confidence = 0.98f;
     p->max_translation_norm = 0.1;
     p->max_rotation_norm = 0.5;
@@ -198,6 +198,8 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     pc.max_t_norm = p->max_translation_norm;
     pc.max_r_norm = p->max_rotation_norm;
     pc.seed = p->ransac_seed;
+    pc.ransac_iterations = p->ransac_iterations;
+    pc.ransac_confidence = (double)p->ransac_confidence;
     pc.lk = make_lk_config(*p, c->pg.nlevels);
     pc.check_bounds = 1;
     pc.age_increment = 1;
@@ -225,6 +227,15 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.hyp_pose, S * d.n_hyp * 12));
     CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
     CU(dev_alloc(c, &d.inl_idx, C));
+    CU(dev_alloc(c, &d.hyp_samples, S * d.n_hyp * 5));
+    CU(dev_alloc(c, &d.rng_raw, (size_t)SVO_RNG_TABLE));
+    {
+        std::vector<unsigned> raw(SVO_RNG_TABLE);
+        uint64_t state = 0xFFFFFFFFFFFFFFFFull;   // RNG rng((uint64)-1) in RANSACPointSetRegistrator::run
+        for (int i = 0; i < SVO_RNG_TABLE; ++i) raw[i] = cv_rng_next(state);
+        CU(cudaMemcpyAsync(d.rng_raw, raw.data(), sizeof(unsigned) * SVO_RNG_TABLE, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
     CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S, false));
     CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S, false));
     CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S));
@@ -869,6 +880,7 @@ extern "C" int svo_camera_to_world(const svo_params* p, const float K[9], const 
     CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d.m_L1, cam_pts, sizeof(float2) * n, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d.X3, world_pts, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st));
+    launch_pnp_samples(d, st);
     launch_pnp(d, c->pc, st);
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

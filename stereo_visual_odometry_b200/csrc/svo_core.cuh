@@ -647,6 +647,72 @@ SVO_HD void pnp_refine_lm(Pose& P, Eval& eval, int max_iter) {
     }
 }
 
+// ---- RANSAC control flow of cv::solvePnPRansac (RANSACPointSetRegistrator::run) -------
+// OpenCV seeds a local RNG with (uint64)-1 on every call, so the sample sequence depends
+// only on the number of points: it can be replayed exactly.  cv::RNG is a multiply-with-
+// carry generator; uniform(0, n) = next() % n.
+#define SVO_RNG_TABLE 1024
+SVO_HD unsigned cv_rng_next(uint64_t& state) {
+    state = (uint64_t)(unsigned)state * 4164903690u + (unsigned)(state >> 32);
+    return (unsigned)state;
+}
+// getSubset(): 5 distinct indices per hypothesis, redrawing on duplicates.  mod_at(pos) is
+// the pos-th RNG output modulo the point count.  A hypothesis that would run past the table
+// is marked invalid (-1); unreachable in practice (needs > 1024 draws for <= 100 samples).
+template <class ModAt>
+SVO_HD void ransac_build_samples(ModAt mod_at, int n_hyp, int* samples) {
+    int pos = 0;
+    for (int h = 0; h < n_hyp; ++h) {
+        int idx[5] = {-1, -1, -1, -1, -1};
+        bool ok = true;
+        for (int i = 0; i < 5 && ok; ++i) {
+            for (;;) {
+                if (pos >= SVO_RNG_TABLE) { ok = false; break; }
+                const int v = mod_at(pos++);
+                bool dup = false;
+                for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
+                if (!dup) { idx[i] = v; break; }
+            }
+        }
+        for (int i = 0; i < 5; ++i) samples[h * 5 + i] = ok ? idx[i] : -1;
+    }
+}
+// cv::RANSACUpdateNumIters
+SVO_HD int ransac_update_num_iters(double p, double ep, int model_points, int max_iters) {
+    p = p < 0. ? 0. : (p > 1. ? 1. : p);
+    ep = ep < 0. ? 0. : (ep > 1. ? 1. : ep);
+    double num = 1. - p;
+    if (num < DBL_MIN) num = DBL_MIN;
+    double denom = 1. - pow(1. - ep, (double)model_points);
+    if (denom < DBL_MIN) return 0;
+    num = log(num);
+    denom = log(denom);
+    if (denom >= 0 || -num >= max_iters * (-denom)) return max_iters;
+#if defined(__CUDA_ARCH__)
+    return __double2int_rn(num / denom);
+#else
+    return (int)lrint(num / denom);
+#endif
+}
+// Replays the sequential loop over per-hypothesis inlier counts: a model replaces the best
+// iff count > max(best, 4); the iteration budget shrinks adaptively.  Returns the index of
+// the winning hypothesis or -1.
+SVO_HD int ransac_replay(const int* counts, int n_hyp, int n_points, int max_iters, double confidence,
+                         int& best_count) {
+    int niters = max_iters < 1 ? 1 : max_iters;
+    int best = -1, max_good = 0;
+    for (int k = 0; k < niters && k < n_hyp; ++k) {
+        const int c = counts[k];
+        if (c > (max_good > 4 ? max_good : 4)) {
+            max_good = c;
+            best = k;
+            niters = ransac_update_num_iters(confidence, (double)(n_points - c) / n_points, 5, niters);
+        }
+    }
+    best_count = max_good;
+    return best;
+}
+
 // Counter-based RNG for hypothesis sampling (splitmix64).
 SVO_HD uint64_t splitmix64(uint64_t x) {
     x += 0x9E3779B97F4A7C15ull;

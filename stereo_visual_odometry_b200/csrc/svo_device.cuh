@@ -71,6 +71,8 @@ struct DevArrays {
     // RANSAC hypotheses
     double* hyp_pose;                 // [n_seq][H][12]
     int* hyp_count;                   // [n_seq][H]
+    int* hyp_samples;                 // [n_seq][H][5] OpenCV-order sample indices (-1 = invalid)
+    unsigned* rng_raw;                // [SVO_RNG_TABLE] cv::RNG((uint64)-1) output stream
     int* inl_idx;                     // [n_seq][cap] ascending inlier indices
     int cap;                          // per-sequence feature capacity
     int n_seq;
@@ -86,6 +88,8 @@ struct PipeConfig {
     float reproj_thr_sq;         // (float)(8*8)
     double max_t_norm, max_r_norm;
     uint64_t seed;
+    int ransac_iterations;       // RANSAC_ITERATIONS (vo.h) = OpenCV's iteration cap
+    double ransac_confidence;    // (double)(float)0.98 (vo.cpp:295)
     int check_bounds;            // in-bounds test of matchingFeatures (vo.cpp:341-359)
     int age_increment;           // ages++ of stereo_callback (vo.cpp:70-72)
     LkConfig lk;

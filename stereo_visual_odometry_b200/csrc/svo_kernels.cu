@@ -477,8 +477,25 @@ void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, cons
 
 // ============================================================================
 // select: circular check + status AND + bounds, stable compaction, ages++, triangulation
+// one full warp: RNG outputs modulo n in parallel, then lane 0 replays getSubset()
+__device__ __forceinline__ void warp_build_samples(const unsigned* __restrict__ raw, int n, int n_hyp,
+                                                   int* __restrict__ samples, int* mods /* smem [SVO_RNG_TABLE] */) {
+    const int lane = threadIdx.x & 31;
+    for (int i = lane; i < SVO_RNG_TABLE; i += 32) mods[i] = (int)(raw[i] % (unsigned)n);
+    __syncwarp();
+    if (lane == 0) ransac_build_samples([&](int pos) { return mods[pos]; }, n_hyp, samples);
+}
+__global__ void pnp_samples_kernel(DevArrays d) {
+    __shared__ int mods[SVO_RNG_TABLE];
+    const int seq = blockIdx.x;
+    const int n = d.state[seq].n_matched;
+    if (n >= 5) warp_build_samples(d.rng_raw, n, d.n_hyp, d.hyp_samples + (long long)seq * d.n_hyp * 5, mods);
+}
+void launch_pnp_samples(const DevArrays& d, cudaStream_t st) { pnp_samples_kernel<<<d.n_seq, 32, 0, st>>>(d); }
+
 __global__ void __launch_bounds__(1024) select_kernel(DevArrays d, PipeConfig pc) {
     __shared__ int sm[33];
+    __shared__ int mods[SVO_RNG_TABLE];
     const int seq = blockIdx.x, tid = threadIdx.x;
     SeqState* s = d.state + seq;
     const long long fo = (long long)seq * d.cap;
@@ -522,6 +539,8 @@ __global__ void __launch_bounds__(1024) select_kernel(DevArrays d, PipeConfig pc
         }
     }
     __syncthreads();
+    // RANSAC sample indices in OpenCV's order (depends only on the survivor count)
+    if (tid < 32 && total >= 5) warp_build_samples(d.rng_raw, total, d.n_hyp, d.hyp_samples + (long long)seq * d.n_hyp * 5, mods);
     // triangulation (only consumed when enough features survive; cheap enough to always run)
     for (int i = tid; i < total; i += 1024) {
         const float2 a = d.m_L0[fo + i], b = d.m_R0[fo + i];
@@ -569,9 +588,14 @@ __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, Pi
     const float2* uv = d.m_L1 + fo;
 
     Pose P;
+    bool valid = true;
     if (lane == 0) {
         int idx[5];
-        sample5(pc.seed, ((uint64_t)(unsigned)s->frame_id << 24) ^ ((uint64_t)seq << 48) ^ (uint64_t)hyp, n, idx);
+        const int* smp = d.hyp_samples + ((long long)seq * d.n_hyp + hyp) * 5;
+        for (int i = 0; i < 5; ++i) idx[i] = smp[i];
+        valid = idx[0] >= 0 && idx[4] < n;
+        if (!valid)
+            for (int i = 0; i < 5; ++i) idx[i] = i;
         float X[15], U[10];
         for (int i = 0; i < 5; ++i) {
             X[3 * i] = X3[3 * idx[i]];
@@ -606,7 +630,7 @@ __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, Pi
         bool finite = true;
         for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
         for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
-        d.hyp_count[(long long)seq * d.n_hyp + hyp] = finite ? cnt : 0;
+        d.hyp_count[(long long)seq * d.n_hyp + hyp] = (finite && valid) ? cnt : 0;
     }
 }
 
@@ -668,7 +692,6 @@ __device__ void write_result(const DevArrays& d, int seq, int success, int reaso
 
 __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, PipeConfig pc) {
     __shared__ int sm_i[33];
-    __shared__ unsigned sm_best[FIN_THREADS / 32];
     __shared__ double sm_acc[(FIN_THREADS / 32) * SVO_PNP_ACC];
     const int seq = blockIdx.x, tid = threadIdx.x;
     const int lane = tid & 31, wid = tid >> 5;
@@ -680,20 +703,17 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         if (tid == 0) write_result(d, seq, 0, SVO_REASON_FEW_FEATURES, s->last_T);
         return;
     }
-    // ---- best hypothesis: max inlier count, ties -> lowest index
-    unsigned best = 0;
-    for (int h = tid; h < d.n_hyp; h += FIN_THREADS) {
-        const unsigned c = (unsigned)d.hyp_count[(long long)seq * d.n_hyp + h];
-        const unsigned key = (c << 12) | (unsigned)(4095 - h);
-        best = max(best, key);
+    // ---- winning hypothesis: replay of OpenCV's sequential adaptive RANSAC loop over the counts
+    if (tid == 0) {
+        int bc = 0;
+        sm_i[0] = ransac_replay(d.hyp_count + (long long)seq * d.n_hyp, d.n_hyp, n, pc.ransac_iterations,
+                                pc.ransac_confidence, bc);
+        sm_i[1] = bc;
     }
-    best = __reduce_max_sync(0xffffffffu, best);
-    if (lane == 0) sm_best[wid] = best;
     __syncthreads();
-    best = 0;
-    for (int w = 0; w < FIN_THREADS / 32; ++w) best = max(best, sm_best[w]);
-    const int best_cnt = (int)(best >> 12), best_h = 4095 - (int)(best & 4095u);
-    if (best_cnt < 5) {   // no model: solvePnPRansac returns false, translation restored (vo.cpp:309-311)
+    const int best_h = sm_i[0], best_cnt = sm_i[1];
+    __syncthreads();
+    if (best_h < 0 || best_cnt < 5) {   // no model: solvePnPRansac returns false, translation restored (vo.cpp:309-311)
         if (tid == 0) {
             s->pnp_ok = 0;
             s->n_inliers = 0;

@@ -36,6 +36,7 @@ void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeCon
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, cudaStream_t st);
 void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_pnp_samples(const DevArrays& d, cudaStream_t st);   // standalone (select_kernel fuses it)
 
 // ---- stage-level helpers used by the stateless API ----
 void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, const float2* pts, int n,

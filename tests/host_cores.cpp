@@ -1,0 +1,191 @@
+// tests/host_cores.cpp -- TEST HARNESS, not product code and not a fallback.
+//
+// Compiles the arithmetic cores of stereo_visual_odometry_b200/csrc/svo_core.cuh for the
+// host (g++, LANES = 1) so that the exact integer / fixed-point / FP64 arithmetic the CUDA
+// kernels execute can be checked against the cv2 oracle on a box without a GPU.  The
+// shipped library (libsvo_b200.so) never contains or calls any of this.
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../stereo_visual_odometry_b200/csrc/svo_core.cuh"
+
+using namespace svo;
+
+struct HostImg {
+    const uint8_t* p;
+    int pitch;
+    int operator()(int x, int y) const { return p[(size_t)y * pitch + x]; }
+};
+
+extern "C" {
+
+// dense response map (0 = not a keypoint), same semantics as fast_kernel
+int hc_fast_map(const uint8_t* img, int w, int h, int stride, int thr, uint8_t* resp_map) {
+    static const int RDX[16] = SVO_FAST_RING_DX;
+    static const int RDY[16] = SVO_FAST_RING_DY;
+    std::vector<uint8_t> score((size_t)w * h, 0);
+    for (int y = 3; y < h - 3; ++y)
+        for (int x = 3; x < w - 3; ++x) {
+            const int v = img[(size_t)y * stride + x];
+            int r[16];
+            for (int k = 0; k < 16; ++k) r[k] = img[(size_t)(y + RDY[k]) * stride + x + RDX[k]];
+            const int s = fast9_arc_score(v, r);
+            score[(size_t)y * w + x] = (uint8_t)(s > thr ? s - 1 : 0);
+        }
+    int n = 0;
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const int v = score[(size_t)y * w + x];
+            bool keep = v > 0;
+            for (int dy = -1; dy <= 1 && keep; ++dy)
+                for (int dx = -1; dx <= 1; ++dx) {
+                    if (!dx && !dy) continue;
+                    const int xx = x + dx, yy = y + dy;
+                    const int nv = (xx >= 0 && xx < w && yy >= 0 && yy < h) ? score[(size_t)yy * w + xx] : 0;
+                    if (!(v > nv)) { keep = false; break; }
+                }
+            resp_map[(size_t)y * w + x] = keep ? (uint8_t)v : 0;
+            n += keep;
+        }
+    return n;
+}
+
+void hc_pyrdown(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dpitch) {
+    const int dw = (sw + 1) / 2, dh = (sh + 1) / 2;
+    HostImg g{src, spitch};
+    for (int y = 0; y < dh; ++y)
+        for (int x = 0; x < dw; ++x) dst[(size_t)y * dpitch + x] = (uint8_t)pyrdown_pixel(g, sw, sh, x, y);
+}
+
+struct HostPyr {
+    std::vector<std::vector<uint8_t>> lv;
+    LkPyramid p;
+    int nlevels;
+};
+static void build_pyr(HostPyr& hp, const uint8_t* img, int w, int h, int stride, int max_level, int win) {
+    hp.lv.clear();
+    hp.lv.emplace_back((size_t)w * h);
+    for (int y = 0; y < h; ++y) memcpy(&hp.lv[0][(size_t)y * w], img + (size_t)y * stride, w);
+    int lw = w, lh = h;
+    hp.p.lv[0] = LkLevel{hp.lv[0].data(), w, h, w};
+    int l = 1;
+    for (; l <= max_level && l < SVO_MAX_LEVELS; ++l) {
+        const int nw = (lw + 1) / 2, nh = (lh + 1) / 2;
+        if (nw <= win || nh <= win) break;
+        hp.lv.emplace_back((size_t)nw * nh);
+        hc_pyrdown(hp.lv[l - 1].data(), lw, lh, lw, hp.lv[l].data(), nw);
+        lw = nw;
+        lh = nh;
+    }
+    hp.nlevels = l;
+    for (int k = 0; k < SVO_MAX_LEVELS; ++k) {
+        const int q = k < l ? k : l - 1;
+        int qw = w, qh = h;
+        for (int i = 0; i < q; ++i) { qw = (qw + 1) / 2; qh = (qh + 1) / 2; }
+        hp.p.lv[k] = LkLevel{hp.lv[q].data(), qw, qh, qw};
+    }
+}
+
+int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, int max_level, int max_iters,
+          double eps, float min_eig, const float* pts, int n, float* out, uint8_t* status) {
+    HostPyr I, J;
+    build_pyr(I, prev, w, h, stride, max_level, SVO_LK_WIN);
+    build_pyr(J, next, w, h, stride, max_level, SVO_LK_WIN);
+    LkConfig cfg;
+    cfg.nlevels = I.nlevels;
+    cfg.max_iters = max_iters;
+    cfg.eps_sq = eps * eps;
+    cfg.min_eig = min_eig;
+    uint8_t patch[SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    int total_iters = 0;
+    for (int i = 0; i < n; ++i) {
+        float ox, oy;
+        int it;
+        status[i] = (uint8_t)lk_track_feature<1, SerialRed>(I.p, J.p, cfg, pts[2 * i], pts[2 * i + 1], 0, patch, ox,
+                                                            oy, it);
+        out[2 * i] = ox;
+        out[2 * i + 1] = oy;
+        total_iters += it;
+    }
+    return total_iters;
+}
+
+void hc_triangulate(const float* Pl, const float* Pr, const float* pL, const float* pR, int n, float* X3) {
+    for (int i = 0; i < n; ++i)
+        triangulate_dlt(Pl, Pr, pL[2 * i], pL[2 * i + 1], pR[2 * i], pR[2 * i + 1], X3 + 3 * i);
+}
+
+struct SetEval {
+    const float* X3;
+    const float* uv;
+    const int* idx;
+    int n;
+    Intrinsics K;
+    void operator()(const Pose& P, double* acc, bool jac) const {
+        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = 0.0;
+        for (int i = 0; i < n; ++i) {
+            const int k = idx ? idx[i] : i;
+            pnp_accumulate(P, K, X3 + 3 * k, uv + 2 * k, acc, jac);
+        }
+    }
+};
+
+// serial emulation of select_kernel's sampling + pnp_hyp_kernel + pnp_final_kernel (same cores)
+int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, double* R, double* t, int n_hyp,
+                  int max_iters, double confidence, float reproj_thr_sq, int* inliers, int* success) {
+    Intrinsics K{K9[0], K9[4], K9[2], K9[5]};
+    *success = 0;
+    if (n < 5) return 0;
+    std::vector<unsigned> raw(SVO_RNG_TABLE);
+    uint64_t state = 0xFFFFFFFFFFFFFFFFull;
+    for (int i = 0; i < SVO_RNG_TABLE; ++i) raw[i] = cv_rng_next(state);
+    std::vector<int> samples((size_t)n_hyp * 5), counts(n_hyp, 0);
+    ransac_build_samples([&](int pos) { return (int)(raw[pos] % (unsigned)n); }, n_hyp, samples.data());
+    std::vector<Pose> poses(n_hyp);
+    for (int hyp = 0; hyp < n_hyp; ++hyp) {
+        const int* idx = samples.data() + 5 * hyp;
+        if (idx[0] < 0) continue;
+        Pose P;
+        memcpy(P.R, R, sizeof(double) * 9);
+        memcpy(P.t, t, sizeof(double) * 3);
+        SetEval ev{X3, uv, idx, 5, K};
+        pnp_refine_lm(P, ev, 20);
+        bool finite = true;
+        for (int i = 0; i < 9; ++i) finite &= std::isfinite(P.R[i]);
+        for (int i = 0; i < 3; ++i) finite &= std::isfinite(P.t[i]);
+        int cnt = 0;
+        for (int i = 0; i < n; ++i) cnt += reproj_err_sq(P, K, X3 + 3 * i, uv + 2 * i) <= reproj_thr_sq;
+        counts[hyp] = finite ? cnt : 0;
+        poses[hyp] = P;
+    }
+    int best_cnt = 0;
+    const int bh = ransac_replay(counts.data(), n_hyp, n, max_iters, confidence, best_cnt);
+    if (bh < 0 || best_cnt < 5) return 0;
+    Pose best = poses[bh];
+    int n_in = 0;
+    for (int i = 0; i < n; ++i)
+        if (reproj_err_sq(best, K, X3 + 3 * i, uv + 2 * i) <= reproj_thr_sq) inliers[n_in++] = i;
+    SetEval ev{X3, uv, inliers, n_in, K};
+    pnp_refine_lm(best, ev, 20);
+    memcpy(R, best.R, sizeof(double) * 9);
+    memcpy(t, best.t, sizeof(double) * 3);
+    *success = 1;
+    return n_in;
+}
+
+double hc_rotation_angle(const double* R) { return rotation_angle(R); }
+
+int hc_bucket_score(int age, int strength, int fast_threshold) { return bucket_score(age, strength, fast_threshold); }
+
+// key round trip + ordering property used by bucket_merge_kernel
+int hc_bucket_key_roundtrip(int score, unsigned order, int strength) {
+    const unsigned long long k = bucket_key(score, order, strength);
+    return bucket_key_score(k) == score && bucket_key_order(k) == order && bucket_key_strength(k) == strength;
+}
+int hc_bucket_key_less(int s1, unsigned o1, int s2, unsigned o2) {
+    return bucket_key(s1, o1, 0) < bucket_key(s2, o2, 0);
+}
+
+}  // extern "C"
