@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py -- stereo frames/s of the per-frame VO front end at KITTI shape (BASELINE.json).
+
+  python bench.py --gpus N --steps K --warmup W            (torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (config.workload): BASELINE.json configs[1] -- synthetic KITTI-shape stereo 1241x376 uint8,
+kitti00.yaml calibration, ~2000 tracked features per frame, one sequence per GPU.  A "step" is
+FRAMES_PER_STEP consecutive stereo frames through VisualOdometry::stereo_callback.
+  value : frames/s with every frame already resident in HBM (svo_process_frame_batch_dev, stream
+          ordered, no host sync inside the timed region), CUDA events on the context's stream.
+  e2e   : frames/s through the reference-facing call (svo_process_frame: pinned HOST images, H2D copy,
+          kernels, D2H of the 4x4 + flags, one sync per frame -- the API returns the pose).
+  N > 1 : one sequence per rank (weak scaling, no data-path collective), trajectories gathered over NCCL.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 1241, 376
+FRAMES_PER_STEP = 100
+REF_FRAMES_PER_STEP = 8
+METRIC = "stereo frames/s at KITTI 1241x376"
+
+
+def pyramid_bytes(w, h, levels=3):
+    tot, lw, lh = 0, w, h
+    for _ in range(levels):
+        lw, lh = (lw + 1) // 2, (lh + 1) // 2
+        tot += lw * lh
+    return tot
+
+
+# each new u8 pixel read once + pyramid levels 1..3 written once, both images
+B_ALG_FRAME = 2 * W * H + 2 * pyramid_bytes(W, H)
+
+
+def render_frames(n_unique, seed):
+    from oracle import synth
+    seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=n_unique, seed=seed)
+    L = np.empty((n_unique, H, W), np.uint8)
+    R = np.empty((n_unique, H, W), np.uint8)
+    for i in range(n_unique):
+        L[i], R[i] = seq.render(i)
+    return seq, L, R
+
+
+def pingpong(i, n):
+    """Endless physically valid playback of n rendered frames: forward, then backward, ..."""
+    p = i % (2 * n - 2) if n > 1 else 0
+    return p if p < n else 2 * n - 2 - p
+
+
+class ClockSampler:
+    def __init__(self, dev):
+        self.dev, self.rows, self.proc = dev, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.dev), f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for k, nm in enumerate(names):
+                    if r[2 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU path (OpenCV kernels via the cv2 oracle restatement,
+    oracle/ref_cv2.py; the C++ reference cannot be built here: no OpenCV C++ headers/libs)."""
+    if rank != 0:
+        return
+    import cv2
+    from oracle import ref_cv2 as O
+    cores = os.cpu_count() or 1
+    cv2.setNumThreads(cores)
+    n_unique = min(64, 2 + REF_FRAMES_PER_STEP * 2)
+    seq, L, R = render_frames(n_unique, 0)
+    vo = O.RefVO(seq.Pl, seq.Pr)
+    vo.stereo_callback(L[0], R[0])
+    k = 1
+
+    def step():
+        nonlocal k
+        for _ in range(REF_FRAMES_PER_STEP):
+            j = pingpong(k, n_unique)
+            vo.stereo_callback(L[j], R[j])
+            k += 1
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    fps = args.steps * REF_FRAMES_PER_STEP / dt
+    sample = f"{args.steps} steps x {REF_FRAMES_PER_STEP} frames of the same synthetic KITTI-shape sequence"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "synthetic KITTI-shape stereo 1241x376 uint8, kitti00.yaml, ~2000 features (configs[1])",
+                   "frames_per_step": REF_FRAMES_PER_STEP},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample,
+                         "note": "cv2 (OpenCV 4.13) kernels = the same library calls the reference makes"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def cpu_baseline(seq, L, R, budget_s=12.0):
+    import cv2
+    from oracle import ref_cv2 as O
+    out = {}
+    for cores in (1, os.cpu_count() or 1):
+        cv2.setNumThreads(cores)
+        vo = O.RefVO(seq.Pl, seq.Pr)
+        vo.stereo_callback(L[0], R[0])
+        vo.stereo_callback(L[1], R[1])
+        t0 = time.perf_counter()
+        n, k = 0, 2
+        stages = {}
+        while time.perf_counter() - t0 < budget_s / 2 and n < 200:
+            j = pingpong(k, len(L))
+            vo.stereo_callback(L[j], R[j])
+            for kk, v in vo.taps.times.items():
+                stages[kk] = stages.get(kk, 0.0) + v
+            k += 1
+            n += 1
+        dt = time.perf_counter() - t0
+        out[cores] = (n / dt, n, {kk: 1e3 * v / n for kk, v in stages.items()})
+    best = max(out, key=lambda c: out[c][0])
+    return {"value": out[best][0], "unit": "frames/s", "cores": best, "kind": "port",
+            "sample": f"{out[best][1]} frames of the same sequence, cv2 oracle (OpenCV kernels the reference calls)",
+            "single_thread_value": out[1][0], "stage_ms_single_thread": out[1][2]}
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from stereo_visual_odometry_b200 import _lib
+    from stereo_visual_odometry_b200._lib import FrameResult, check, default_params, lib, ptr
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L_ = lib()
+    n_unique = args.frames
+    t_r = time.perf_counter()
+    seq, Lh, Rh = render_frames(n_unique, seed=rank)
+    render_s = time.perf_counter() - t_r
+    Lp, Rp = torch.from_numpy(Lh).pin_memory(), torch.from_numpy(Rh).pin_memory()
+    Ld, Rd = Lp.cuda(non_blocking=True), Rp.cuda(non_blocking=True)
+    torch.cuda.synchronize()
+
+    def make_ctx(n_seq=1):
+        p = default_params(W, H, n_seq=n_seq, device=local_rank)
+        ctx = L_.svo_create(C.byref(p))
+        if not ctx:
+            raise RuntimeError("svo_create: " + L_.svo_last_error().decode())
+        Pl, Pr = np.ascontiguousarray(seq.Pl), np.ascontiguousarray(seq.Pr)
+        check(L_.svo_set_projection(ctx, ptr(Pl, C.c_float), ptr(Pr, C.c_float)))
+        return ctx
+
+    n_total = (args.warmup + args.steps) * FRAMES_PER_STEP + 1
+    res_dev = torch.zeros((n_total, C.sizeof(FrameResult)), dtype=torch.uint8, device="cuda")
+
+    # ---------------- value: frames resident in HBM, stream-ordered, no host sync in the timed region
+    ctx = make_ctx()
+    stream = torch.cuda.ExternalStream(L_.svo_stream(ctx))
+    fsz = C.sizeof(FrameResult)
+    k = 0
+
+    def enqueue(ctx_, i):
+        j = pingpong(i, n_unique)
+        check(L_.svo_process_frame_batch_dev(ctx_, Ld[j].data_ptr(), Rd[j].data_ptr(), W, W * H,
+                                             res_dev.data_ptr() + i * fsz))
+
+    enqueue(ctx, 0)
+    k = 1
+    for _ in range(args.warmup):
+        for _ in range(FRAMES_PER_STEP):
+            enqueue(ctx, k)
+            k += 1
+    check(L_.svo_synchronize(ctx))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = L_.svo_launch_count(ctx)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    k_timed0 = k
+    for _ in range(args.steps):
+        for _ in range(FRAMES_PER_STEP):
+            enqueue(ctx, k)
+            k += 1
+    e1.record(stream)
+    check(L_.svo_synchronize(ctx))
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = L_.svo_launch_count(ctx) - launches0
+    # trajectories: gather over NCCL (the only exchange of the path), inside the step budget
+    traj = res_dev[k_timed0:k].clone()
+    if world > 1:
+        gathered = [torch.empty_like(traj) for _ in range(world)] if rank == 0 else None
+        dist.gather(traj, gathered, dst=0)
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop()
+    res = np.frombuffer(traj.cpu().numpy().tobytes(), dtype=np.dtype([
+        ("i", np.int32, 8), ("R", np.float64, 9), ("t", np.float64, 3), ("T", np.float64, 16)]))
+    n_frames_timed = args.steps * FRAMES_PER_STEP
+    success_rate = float(res["i"][:, 0].mean())
+    mean_matched = float(res["i"][:, 3].mean())
+    mean_bucketed = float(res["i"][:, 2].mean())
+    mean_iters = float(res["i"][:, 7].mean())
+    value = world * n_frames_timed / (ms * 1e-3)
+
+    # accuracy vs ground truth over the timed frames (independent of the oracle)
+    terr = []
+    for q in range(min(n_frames_timed, 300)):
+        i = k_timed0 + q
+        a, b = pingpong(i - 1, n_unique), pingpong(i, n_unique)
+        T0 = np.eye(4); T0[:3, :3], T0[:3, 3] = seq.R_wc[a], seq.C[a]
+        T1 = np.eye(4); T1[:3, :3], T1[:3, 3] = seq.R_wc[b], seq.C[b]
+        G = np.linalg.inv(T0) @ T1
+        if res["i"][q, 0]:
+            terr.append(np.linalg.norm(res["T"][q].reshape(4, 4)[:3, 3] - G[:3, 3]) / max(np.linalg.norm(G[:3, 3]), 1e-9))
+
+    out = None
+    if rank == 0:
+        # ---------------- per-stage device times (separate pass, CUDA events between stages on the ctx stream)
+        check(L_.svo_enable_timers(ctx, 1))
+        check(L_.svo_reset_timers(ctx))
+        n_t = 200
+        for _ in range(n_t):
+            enqueue(ctx, min(k, n_total - 1) if False else k % n_total)
+            k += 1
+        names = ["ingest_fast_pyramid", "bucket", "klt", "select_triangulate", "pnp_ransac"]
+        stages = {}
+        for s_, nm in enumerate(names):
+            msv, ln = C.c_double(0), C.c_longlong(0)
+            L_.svo_get_stage_time(ctx, s_, C.byref(msv), C.byref(ln))
+            stages[nm] = {"us_per_frame": 1e3 * msv.value / n_t, "launches_per_frame": ln.value / n_t}
+        check(L_.svo_enable_timers(ctx, 0))
+    L_.svo_destroy(ctx)
+
+    e2e = None
+    if True:
+        # ---------------- e2e: the reference-facing call with pinned HOST images, sync per frame
+        ctx2 = make_ctx()
+        T = np.zeros(16, np.float64)
+        n_e2e = min(n_frames_timed, 1000)
+        check(L_.svo_process_frame(ctx2, Lp[0].data_ptr(), Rp[0].data_ptr(), W, ptr(T, C.c_double)))
+        kk = 1
+        for _ in range(50):
+            j = pingpong(kk, n_unique)
+            check(L_.svo_process_frame(ctx2, Lp[j].data_ptr(), Rp[j].data_ptr(), W, ptr(T, C.c_double)))
+            kk += 1
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            j = pingpong(kk, n_unique)
+            check(L_.svo_process_frame(ctx2, Lp[j].data_ptr(), Rp[j].data_ptr(), W, ptr(T, C.c_double)))
+            kk += 1
+        dt = time.perf_counter() - t0
+        if world > 1:
+            tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+        e2e = {"value": world * n_e2e / dt, "unit": "frames/s", "h2d_bytes_per_step": 2 * W * H * FRAMES_PER_STEP,
+               "d2h_bytes_per_step": C.sizeof(FrameResult) * FRAMES_PER_STEP, "frames_timed": n_e2e,
+               "timing": "host wall clock around synchronous svo_process_frame calls (each call syncs the stream)"}
+        L_.svo_destroy(ctx2)
+
+    if rank == 0:
+        # ---------------- batched ingest/pipeline (config 5 shape on this rank): 64/N sequences per launch
+        n_b = max(1, 64 // world)
+        batch = None
+        try:
+            nfb = min(40, n_unique)
+            ctxb = make_ctx(n_seq=n_b)
+            idx = torch.tensor([[pingpong(f + 3 * s_, n_unique) for s_ in range(n_b)] for f in range(nfb)], device="cuda")
+            sb = torch.cuda.ExternalStream(L_.svo_stream(ctxb))
+            check(L_.svo_enable_timers(ctxb, 0))
+            bl = torch.empty((n_b, H, W), dtype=torch.uint8, device="cuda")
+            br = torch.empty((n_b, H, W), dtype=torch.uint8, device="cuda")
+            Lb = [Ld[idx[f]] for f in range(nfb)]
+            Rb = [Rd[idx[f]] for f in range(nfb)]
+            torch.cuda.synchronize()
+            for f in range(5):
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+            check(L_.svo_synchronize(ctxb))
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b0.record(sb)
+            for f in range(5, nfb):
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+            b1.record(sb)
+            check(L_.svo_synchronize(ctxb))
+            bms = b0.elapsed_time(b1)
+            check(L_.svo_enable_timers(ctxb, 1))
+            check(L_.svo_reset_timers(ctxb))
+            for f in range(nfb - 1, nfb - 11, -1):
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+            msv, ln = C.c_double(0), C.c_longlong(0)
+            L_.svo_get_stage_time(ctxb, 0, C.byref(msv), C.byref(ln))
+            ing_us = 1e3 * msv.value / 10
+            fr = FrameResult()
+            L_.svo_get_result(ctxb, 0, C.byref(fr))
+            batch = {"sequences_per_launch": n_b, "frames_per_s": n_b * (nfb - 5) / (bms * 1e-3),
+                     "ingest_us_per_launch": ing_us,
+                     "ingest_GBps": B_ALG_FRAME * n_b / (ing_us * 1e-6) / 1e9, "last_matched": fr.n_matched}
+            L_.svo_destroy(ctxb)
+        except Exception as ex:   # keep the headline line alive
+            batch = {"error": str(ex)[:200]}
+
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (of fallback)"
+        ing = stages["ingest_fast_pyramid"]
+        ach = B_ALG_FRAME / (ing["us_per_frame"] * 1e-6) / 1e9
+        roofline = {"bound": "hbm", "kernel": "ingest: level-0 copy + pyrDown x3 + FAST/NMS/bucket-winners (1 frame per launch)",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "peak_source": peak_src, "algorithmic_bytes_per_frame": B_ALG_FRAME,
+                    "note": "a single 0.9 MB frame cannot fill the HBM pipe; see roofline_batch for the n-sequence launch"}
+        if batch and "ingest_GBps" in batch:
+            roofline_batch = {"bound": "hbm", "achieved": batch["ingest_GBps"], "peak": peak, "unit": "GB/s",
+                              "frac": batch["ingest_GBps"] / peak, "frames_per_launch": batch["sequences_per_launch"]}
+        else:
+            roofline_batch = None
+        cpu = cpu_baseline(seq, Lh, Rh) if not args.no_cpu_baseline else None
+        out = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "synthetic KITTI-shape stereo 1241x376 uint8, kitti00.yaml, ~2000 features, "
+                                   "one sequence per GPU (BASELINE.json configs[1])",
+                       "frames_per_step": FRAMES_PER_STEP, "unique_frames": n_unique, "playback": "ping-pong",
+                       "l2": "inputs (%d MB of frames per GPU) exceed nothing: each frame is read once; per-frame working set is L2-resident by nature" % (2 * n_unique * W * H >> 20),
+                       "features_bucketed_mean": mean_bucketed, "features_matched_mean": mean_matched,
+                       "lk_iters_per_frame": mean_iters, "success_rate": success_rate,
+                       "rel_translation_err_vs_gt_median": float(np.median(terr)) if terr else None},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "roofline_batch": roofline_batch, "stages": stages, "batch64": batch, "cpu_baseline": cpu,
+            "render_s": render_s,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=120, help="unique rendered frames (ping-pong playback)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -133,6 +133,8 @@ struct SetEval {
 };
 
 // serial emulation of select_kernel's sampling + pnp_hyp_kernel + pnp_final_kernel (same cores)
+int g_chain = 0;
+void hc_set_chain(int c) { g_chain = c; }
 int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, double* R, double* t, int n_hyp,
                   int max_iters, double confidence, float reproj_thr_sq, int* inliers, int* success) {
     Intrinsics K{K9[0], K9[4], K9[2], K9[5]};
@@ -150,6 +152,7 @@ int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, doub
         Pose P;
         memcpy(P.R, R, sizeof(double) * 9);
         memcpy(P.t, t, sizeof(double) * 3);
+        if (g_chain && hyp > 0) P = poses[hyp - 1];
         SetEval ev{X3, uv, idx, 5, K};
         pnp_refine_lm(P, ev, 20);
         bool finite = true;
@@ -173,6 +176,18 @@ int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, doub
     memcpy(t, best.t, sizeof(double) * 3);
     *success = 1;
     return n_in;
+}
+
+// plain LM refinement on all n points (solvePnP ITERATIVE with useExtrinsicGuess)
+void hc_pnp_refine(const float* K9, const float* uv, const float* X3, int n, double* R, double* t, int max_iter) {
+    Intrinsics K{K9[0], K9[4], K9[2], K9[5]};
+    Pose P;
+    memcpy(P.R, R, sizeof(double) * 9);
+    memcpy(P.t, t, sizeof(double) * 3);
+    SetEval ev{X3, uv, nullptr, n, K};
+    pnp_refine_lm(P, ev, max_iter);
+    memcpy(R, P.R, sizeof(double) * 9);
+    memcpy(t, P.t, sizeof(double) * 3);
 }
 
 double hc_rotation_angle(const double* R) { return rotation_angle(R); }

@@ -1,0 +1,144 @@
+"""-m gpu parity tests of the whole per-frame path (VisualOdometry::stereo_callback, vo.cpp:41-137)
+through the C ABI against the cv2 oracle, frame by frame with stage taps."""
+import numpy as np
+import pytest
+
+from stereo_visual_odometry_b200 import vo as V
+from oracle import ref_cv2 as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def rot_angle(R):
+    return float(np.arccos(np.clip((np.trace(R) - 1) / 2, -1, 1)))
+
+
+def run_both(frames, Pl, Pr, width, height, check_stages=True):
+    vo = V.VisualOdometry(width, height)
+    vo.initalize_projection_matricies(Pl, Pr)
+    ref = O.RefVO(Pl, Pr)
+    stats = dict(frames=0, lk_close=[], status_eq=[], pose_ok=0, pose_n=0, flags_eq=0, inl_symdiff=[])
+    pose_g, pose_r = np.eye(4), np.eye(4)
+    for i, (L, R) in enumerate(frames):
+        ok, T = vo.stereo_callback(L, R)
+        rok, rT = ref.stereo_callback(L, R)
+        res = vo.last_result()
+        tp = ref.taps
+        stats["frames"] += 1
+        stats["flags_eq"] += int(ok == rok)
+        pose_g, pose_r = pose_g @ T, pose_r @ rT
+        if i == 0:
+            assert not ok and res.reason == 1 and np.array_equal(T, np.eye(4))
+            continue
+        if check_stages:
+            # FAST + bucketing (+ retry)
+            b = vo.tap(0)
+            assert res.retry == int(tp.retry)
+            if i == 1:   # identical inputs (FAST on identical pixels, empty tracked set): bit-exact, order included
+                assert np.array_equal(b["points"], tp.bucketed[0]), f"frame {i}: bucketed points differ"
+                assert np.array_equal(b["ages"], tp.bucketed[1]) and np.array_equal(b["strengths"], tp.bucketed[2])
+            # later frames: tracked positions carry LK float noise (<= 1e-3 px), so match features by position
+            from scipy.spatial import cKDTree
+            dist, j = cKDTree(tp.bucketed[0]).query(b["points"], distance_upper_bound=0.05)
+            hit = np.isfinite(dist)
+            stats.setdefault("bucket_match", []).append(min(hit.mean(), hit.sum() / max(1, len(tp.bucketed[0]))))
+            g, r = np.nonzero(hit)[0], j[hit]
+            assert (b["ages"][g] == tp.bucketed[1][r]).mean() >= 0.99 and (b["strengths"][g] == tp.bucketed[2][r]).mean() >= 0.99
+            # KLT legs on the matched features
+            lk = vo.tap(1)
+            st = np.stack([(lk["status"] >> k) & 1 for k in range(4)], 1)[g]
+            rst = np.stack([tp.lk[f"s{k}"] for k in range(4)], 1)[r]
+            stats["status_eq"].append((st == rst).all(1).mean())
+            d = np.max([np.abs(lk[k][g] - tp.lk[k][r]).max(1) for k in ("pL1", "pR1", "pR0", "pC")], 0)
+            stats["lk_close"].append((d <= 0.05).mean())
+            keep = ((lk["status"] & 16) != 0)
+            stats.setdefault("keep_eq", []).append((keep[g] == tp.keep[r]).mean())
+        if ok and rok:
+            stats["pose_n"] += 1
+            dR = rot_angle(T[:3, :3] @ rT[:3, :3].T)
+            dt = np.linalg.norm(T[:3, 3] - rT[:3, 3]) / max(np.linalg.norm(rT[:3, 3]), 1e-9)
+            stats["pose_ok"] += int(dR < 1e-3 and dt < 1e-3)
+            stats.setdefault("dt", []).append(dt)
+            m = vo.tap(2)
+            if len(m["pL0"]) == len(tp.pL0):
+                stats["inl_symdiff"].append(len(set(m["inliers"].tolist()) ^ set(tp.inliers.tolist())))
+    stats["end_gap"] = float(np.linalg.norm(pose_g[:3, 3] - pose_r[:3, 3]))
+    stats["path_len"] = float(np.linalg.norm(pose_r[:3, 3]))
+    vo.close()
+    return stats
+
+
+def check(stats, pose_frac=0.9):
+    assert stats["flags_eq"] == stats["frames"], "success flags differ from the oracle"
+    assert np.mean(stats["bucket_match"]) >= 0.99 and np.min(stats["bucket_match"]) >= 0.98
+    assert np.mean(stats["status_eq"]) >= 0.99 and np.min(stats["status_eq"]) >= 0.98
+    assert np.mean(stats["lk_close"]) >= 0.99 and np.min(stats["lk_close"]) >= 0.98
+    assert np.mean(stats["keep_eq"]) >= 0.99
+    assert stats["pose_n"] > 0 and stats["pose_ok"] >= pose_frac * stats["pose_n"], (stats["pose_ok"], stats["pose_n"], stats.get("dt"))
+    assert stats["end_gap"] <= 0.01 * max(stats["path_len"], 1e-6) + 1e-4, (stats["end_gap"], stats["path_len"])
+
+
+def test_run1_gray(run1):
+    Pl, Pr = O.CLI_P_LEFT, O.CLI_P_RIGHT
+    s = run_both(iter(run1["gray"]), Pl, Pr, 512, 288)
+    check(s)
+
+
+def test_synthetic_kitti():
+    seq = synth.make_sequence(n_frames=12, seed=0)
+    s = run_both(seq.frames(), seq.Pl, seq.Pr, seq.width, seq.height)
+    check(s)
+
+
+def test_synthetic_small_noisy():
+    seq = synth.make_sequence(width=640, height=240, n_frames=10, seed=5, noise=1.0)
+    s = run_both(seq.frames(), seq.Pl, seq.Pr, seq.width, seq.height)
+    check(s)
+
+
+def test_blank_images_retry_and_few_features():
+    """No texture: the low-threshold retry fires, nothing is tracked, every frame fails softly and
+    returns last_transform (identity) -- vo.cpp:82-84, 179-181, 327-332."""
+    z = np.zeros((200, 320), np.uint8)
+    vo = V.VisualOdometry(320, 200)
+    vo.initalize_projection_matricies(*synth.projection_matrices("cli"))
+    ref = O.RefVO(*synth.projection_matrices("cli"))
+    for i in range(3):
+        ok, T = vo.stereo_callback(z, z)
+        rok, rT = ref.stereo_callback(z, z)
+        assert ok == rok is False and np.array_equal(T, np.eye(4))
+        if i:
+            r = vo.last_result()
+            assert r.retry == 1 and r.n_bucketed == 0 and r.reason == 2
+
+
+def test_failure_then_recovery_matches_oracle(run1):
+    """A frame with a huge jump (frames far apart) trips a failure gate; state afterwards must evolve
+    like the reference's."""
+    g = run1["gray"]
+    order = [0, 1, 2, 7, 3, 4, 5]
+    s = run_both(iter([g[i] for i in order]), O.CLI_P_LEFT, O.CLI_P_RIGHT, 512, 288, check_stages=True)
+    assert s["flags_eq"] == s["frames"]
+    assert np.mean(s["keep_eq"]) >= 0.98
+
+
+def test_batched_sequences_equal_single():
+    """n_seq = 3 batched context == three independent single-sequence contexts (config 5 path)."""
+    seqs = [synth.make_sequence(width=640, height=240, n_frames=5, seed=s) for s in (0, 1, 2)]
+    single = []
+    for q in seqs:
+        vo = V.VisualOdometry(640, 240)
+        vo.initalize_projection_matricies(q.Pl, q.Pr)
+        single.append([vo.stereo_callback(*q.render(i)) for i in range(5)])
+        vo.close()
+    vb = V.VisualOdometry(640, 240, n_seq=3)
+    vb.initalize_projection_matricies(seqs[0].Pl, seqs[0].Pr)
+    for i in range(5):
+        fr = [q.render(i) for q in seqs]
+        res = vb.stereo_callback_batch(np.stack([f[0] for f in fr]), np.stack([f[1] for f in fr]))
+        for k in range(3):
+            ok, T = single[k][i]
+            assert bool(res[k].success) == ok
+            assert np.array_equal(np.array(res[k].transform).reshape(4, 4), T)
+    vb.close()

@@ -67,8 +67,7 @@ def test_bucket_generic_matches_reference_policy():
         fs = V.FeatureSet()
         fs.points, fs.ages, fs.strengths = pts, ages, strs
         fs.filterByBucketLocationInternal(np.zeros((H, W), np.uint8), grid[0], grid[1], start, per_bucket)
-        rp, ra, rs = O.bucket_filter(pts, ages, strs, H, W, grid[0], grid[1], start, max(per_bucket, 0) or 0) \
-            if per_bucket != 1 else O.bucket_filter(pts, ages, strs, H, W, grid[0], grid[1], start, 1)
+        rp, ra, rs = O.bucket_filter(pts, ages, strs, H, W, grid[0], grid[1], start, per_bucket)
         if per_bucket == 0:
             assert fs.size() == 0
             continue
@@ -90,7 +89,6 @@ def test_reference_test_bucket_nonempty():   # main.cpp:62-78 through the generi
 def test_reference_test_featureset():   # main.cpp:102-127
     img = featureset_image()
     fs = V.FeatureSet()
-    V.FAST_THRESHOLD_SAVE = None
     pts, resp = V.featureDetectionFast(img, 1)
     fs.points, fs.ages, fs.strengths = pts, np.zeros(len(pts), np.int32), resp.astype(np.int32)
     fs.filterByBucketLocation(img)
