@@ -13,6 +13,7 @@
 #include <stdio.h>
 
 #include "svo_kernels.cuh"
+#include "svo_epnp.cuh"
 
 namespace svo {
 
@@ -564,18 +565,19 @@ void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
 // by warp reduction, then an FP64 LM refit on the inliers of the best hypothesis.
 constexpr int HYP_WARPS = 4;
 
-struct FivePointEval {
-    const float* X;   // 5 x 3
-    const float* U;   // 5 x 2
-    Intrinsics K;
-    __device__ void operator()(const Pose& P, double* acc, bool jac) const {
+struct WarpRedD {
+    static __device__ __forceinline__ void sync() { __syncwarp(); }
+    static __device__ __forceinline__ double sumd(double v) {
 #pragma unroll
-        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = 0.0;
-        for (int i = 0; i < 5; ++i) pnp_accumulate(P, K, X + 3 * i, U + 2 * i, acc, jac);
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
     }
 };
 
+// One warp per RANSAC hypothesis: EPnP on the 5-point sample (what cv::solvePnPRansac runs per
+// iteration), then the inlier count over all matched points by warp reduction.
 __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, PipeConfig pc) {
+    __shared__ EpnpWork work[HYP_WARPS];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int hyp = blockIdx.x * HYP_WARPS + wid;
@@ -587,50 +589,38 @@ __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, Pi
     const float* X3 = d.X3 + fo * 3;
     const float2* uv = d.m_L1 + fo;
 
-    Pose P;
+    const int* smp = d.hyp_samples + ((long long)seq * d.n_hyp + hyp) * 5;
+    float X[15], U[10];
     bool valid = true;
-    if (lane == 0) {
-        int idx[5];
-        const int* smp = d.hyp_samples + ((long long)seq * d.n_hyp + hyp) * 5;
-        for (int i = 0; i < 5; ++i) idx[i] = smp[i];
-        valid = idx[0] >= 0 && idx[4] < n;
-        if (!valid)
-            for (int i = 0; i < 5; ++i) idx[i] = i;
-        float X[15], U[10];
-        for (int i = 0; i < 5; ++i) {
-            X[3 * i] = X3[3 * idx[i]];
-            X[3 * i + 1] = X3[3 * idx[i] + 1];
-            X[3 * i + 2] = X3[3 * idx[i] + 2];
-            const float2 q = uv[idx[i]];
-            U[2 * i] = q.x;
-            U[2 * i + 1] = q.y;
-        }
-        for (int i = 0; i < 9; ++i) P.R[i] = s->R[i];
-        for (int i = 0; i < 3; ++i) P.t[i] = s->t[i];
-        FivePointEval ev{X, U, pc.K};
-        pnp_refine_lm(P, ev, 20);
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        int k = smp[i];
+        valid = valid && k >= 0 && k < n;
+        k = min(max(k, 0), n - 1);
+        X[3 * i] = X3[3 * k];
+        X[3 * i + 1] = X3[3 * k + 1];
+        X[3 * i + 2] = X3[3 * k + 2];
+        const float2 q = uv[k];
+        U[2 * i] = q.x;
+        U[2 * i + 1] = q.y;
     }
-#pragma unroll
-    for (int i = 0; i < 9; ++i) P.R[i] = __shfl_sync(0xffffffffu, P.R[i], 0);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) P.t[i] = __shfl_sync(0xffffffffu, P.t[i], 0);
+    Pose P;
+    const bool solved = epnp5_solve<32, WarpRedD>(work[wid], pc.K, X, U, lane, P);
     int cnt = 0;
-    for (int i = lane; i < n; i += 32) {
-        const float2 q = uv[i];
-        const float uvf[2] = {q.x, q.y};
-        const float e = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf);
-        cnt += (e <= pc.reproj_thr_sq) ? 1 : 0;
+    if (solved && valid) {
+        for (int i = lane; i < n; i += 32) {
+            const float2 q = uv[i];
+            const float uvf[2] = {q.x, q.y};
+            const float e = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf);
+            cnt += (e <= pc.reproj_thr_sq) ? 1 : 0;
+        }
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if (lane == 0) {
         double* hp = d.hyp_pose + ((long long)seq * d.n_hyp + hyp) * 12;
         for (int i = 0; i < 9; ++i) hp[i] = P.R[i];
         for (int i = 0; i < 3; ++i) hp[9 + i] = P.t[i];
-        // a diverged LM (NaN pose) must never win
-        bool finite = true;
-        for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
-        for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
-        d.hyp_count[(long long)seq * d.n_hyp + hyp] = (finite && valid) ? cnt : 0;
+        d.hyp_count[(long long)seq * d.n_hyp + hyp] = (solved && valid) ? cnt : 0;
     }
 }
 

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../stereo_visual_odometry_b200/csrc/svo_core.cuh"
+#include "../stereo_visual_odometry_b200/csrc/svo_epnp.cuh"
 
 using namespace svo;
 
@@ -133,7 +134,7 @@ struct SetEval {
 };
 
 // serial emulation of select_kernel's sampling + pnp_hyp_kernel + pnp_final_kernel (same cores)
-int g_chain = 0;
+int g_chain = 2;   // 2 = EPnP hypotheses (what the kernels run); 0/1 = LM hypotheses (experiments)
 void hc_set_chain(int c) { g_chain = c; }
 int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, double* R, double* t, int n_hyp,
                   int max_iters, double confidence, float reproj_thr_sq, int* inliers, int* success) {
@@ -153,8 +154,19 @@ int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, doub
         memcpy(P.R, R, sizeof(double) * 9);
         memcpy(P.t, t, sizeof(double) * 3);
         if (g_chain && hyp > 0) P = poses[hyp - 1];
-        SetEval ev{X3, uv, idx, 5, K};
-        pnp_refine_lm(P, ev, 20);
+        if (g_chain == 2) {
+            float Xs[15], Us[10];
+            for (int i = 0; i < 5; ++i) {
+                for (int j = 0; j < 3; ++j) Xs[3 * i + j] = X3[3 * idx[i] + j];
+                Us[2 * i] = uv[2 * idx[i]];
+                Us[2 * i + 1] = uv[2 * idx[i] + 1];
+            }
+            static EpnpWork w;
+            if (!epnp5_solve<1, SerialRedD>(w, K, Xs, Us, 0, P)) P.t[0] = NAN;
+        } else {
+            SetEval ev{X3, uv, idx, 5, K};
+            pnp_refine_lm(P, ev, 20);
+        }
         bool finite = true;
         for (int i = 0; i < 9; ++i) finite &= std::isfinite(P.R[i]);
         for (int i = 0; i < 3; ++i) finite &= std::isfinite(P.t[i]);
@@ -188,6 +200,17 @@ void hc_pnp_refine(const float* K9, const float* uv, const float* X3, int n, dou
     pnp_refine_lm(P, ev, max_iter);
     memcpy(R, P.R, sizeof(double) * 9);
     memcpy(t, P.t, sizeof(double) * 3);
+}
+
+// EPnP on exactly 5 points (the RANSAC hypothesis generator)
+int hc_epnp5(const float* K9, const float* uv, const float* X3, double* R, double* t) {
+    Intrinsics K{K9[0], K9[4], K9[2], K9[5]};
+    static EpnpWork w;
+    Pose P;
+    const bool ok = epnp5_solve<1, SerialRedD>(w, K, X3, uv, 0, P);
+    memcpy(R, P.R, sizeof(double) * 9);
+    memcpy(t, P.t, sizeof(double) * 3);
+    return ok ? 1 : 0;
 }
 
 double hc_rotation_angle(const double* R) { return rotation_angle(R); }
