@@ -90,6 +90,7 @@ struct svo_ctx {
     long long frames = 0;
     long long launches = 0;
     bool have_projection = false;
+    int klt_blocks = 148;   // persistent KLT blocks per sequence
     // timers
     bool timers = false;
     cudaEvent_t ev[6];
@@ -224,9 +225,11 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.m_L0, C));   CU(dev_alloc(c, &d.m_L1, C));    CU(dev_alloc(c, &d.m_R0, C));
     CU(dev_alloc(c, &d.m_R1, C));   CU(dev_alloc(c, &d.m_age, C));   CU(dev_alloc(c, &d.m_str, C));
     CU(dev_alloc(c, &d.X3, C * 3));
+    CU(dev_alloc(c, &d.X3u, C * 3));
     CU(dev_alloc(c, &d.hyp_pose, S * d.n_hyp * 12));
     CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
     CU(dev_alloc(c, &d.inl_idx, C));
+    CU(dev_alloc(c, &d.klt_next, S));
     CU(dev_alloc(c, &d.hyp_samples, S * d.n_hyp * 5));
     CU(dev_alloc(c, &d.rng_raw, (size_t)SVO_RNG_TABLE));
     {
@@ -248,6 +251,13 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     }
     CU(cudaMemcpyAsync(d.state, init.data(), sizeof(SeqState) * S, cudaMemcpyHostToDevice, c->stream));
     for (int i = 0; i < 6; ++i) CU(cudaEventCreate(&c->ev[i]));
+    {
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, p->device));
+        // 3 resident blocks of 8 warps per SM (register bound); split the machine between the sequences
+        int per_seq = (prop.multiProcessorCount * 3 + p->n_seq - 1) / p->n_seq;
+        c->klt_blocks = per_seq < 1 ? 1 : per_seq;
+    }
     CU(cudaStreamSynchronize(c->stream));
     return SVO_OK;
 }
@@ -269,6 +279,10 @@ static svo_ctx* ctx_create(const svo_params* p, int cap_override) {
 }
 
 extern "C" svo_ctx* svo_create(const svo_params* p) {
+    if (p && (long long)p->buckets_along_height * p->buckets_along_width > 16384) {
+        fail(SVO_ERR_INVALID, "the pipeline context supports at most 16384 buckets (reference: 92 x 160 = 14720)");
+        return nullptr;
+    }
     if (p && p->features_per_bucket != 1) {
         fail(SVO_ERR_INVALID, "the pipeline context is built for FEATURES_PER_BUCKET == 1 (vo.h); use svo_bucket_filter for other values");
         return nullptr;
@@ -344,7 +358,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     } else {
         launch_bucket_merge(c->d, c->bg, c->pc, parity ^ 1, st);   // FAST winners of the PREVIOUS left image
         if (tm) cudaEventRecord(c->ev[2], st);
-        launch_klt(c->d, c->pg, c->pc, st);
+        launch_klt(c->d, c->pg, c->pc, c->klt_blocks, st);
         if (tm) cudaEventRecord(c->ev[3], st);
         launch_select(c->d, c->pc, st);
         if (tm) cudaEventRecord(c->ev[4], st);
@@ -713,7 +727,8 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
         s.n_bucketed = n_in;
         CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
     }
-    launch_klt(d, c->pg, c->pc, st);
+    CU(cudaMemsetAsync(d.klt_next, 0, sizeof(int), st));
+    launch_klt(d, c->pg, c->pc, c->klt_blocks, st);
     launch_select(d, c->pc, st);
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

@@ -374,68 +374,91 @@ SVO_HD bool in_bounds(float x, float y, int w, int h) {
 
 // ---------------------------------------------------------------------------
 // DLT triangulation (cv::triangulatePoints + convertPointsFromHomogeneous as at
-// vo.cpp:89-94), SURVEY B.4.  One-sided (Hestenes) Jacobi SVD of the 4x4 system
-// in FP64; the right singular vector of the smallest singular value is stored as
-// float32 and dehomogenised in float32.
+// vo.cpp:89-94), SURVEY B.4.  FP64; the right singular vector of the smallest singular
+// value is stored as float32 and dehomogenised in float32.
 SVO_HD void triangulate_dlt(const float* Pl, const float* Pr, float xl, float yl, float xr, float yr,
                             float* X3) {
-    double A[4][4], V[4][4];
+    // Right singular vector of the smallest singular value of the 4x4 DLT system A == eigenvector of
+    // the smallest eigenvalue of G = A^T A.  Inverse iteration on G + eps*I (same eigenvectors, safely
+    // positive definite) with one LDL^T factorisation: ~10x cheaper than a Jacobi SVD per point and
+    // accurate far below float32 resolution for any point with a usable depth.
+    double A[4][4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         A[0][k] = (double)xl * (double)Pl[8 + k] - (double)Pl[k];
         A[1][k] = (double)yl * (double)Pl[8 + k] - (double)Pl[4 + k];
         A[2][k] = (double)xr * (double)Pr[8 + k] - (double)Pr[k];
         A[3][k] = (double)yr * (double)Pr[8 + k] - (double)Pr[4 + k];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) V[r][k] = (r == k) ? 1.0 : 0.0;
     }
-    for (int sweep = 0; sweep < 30; ++sweep) {
-        bool changed = false;
+    double G[4][4];
 #pragma unroll
-        for (int p = 0; p < 3; ++p)
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int q = p + 1; q < 4; ++q) {
-                double a = 0, b = 0, c = 0;
+        for (int j = 0; j < 4; ++j) {
+            G[i][j] = 0.0;
+            if (j >= i) {
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    a += A[r][p] * A[r][p];
-                    b += A[r][q] * A[r][q];
-                    c += A[r][p] * A[r][q];
-                }
-                if (fabs(c) <= DBL_EPSILON * sqrt(a * b)) continue;
-                changed = true;
-                const double zeta = (b - a) / (2.0 * c);
-                const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const double ap = A[r][p], aq = A[r][q];
-                    A[r][p] = cs * ap - sn * aq;
-                    A[r][q] = sn * ap + cs * aq;
-                    const double vp = V[r][p], vq = V[r][q];
-                    V[r][p] = cs * vp - sn * vq;
-                    V[r][q] = sn * vp + cs * vq;
-                }
+                for (int r = 0; r < 4; ++r) G[i][j] += A[r][i] * A[r][j];
             }
-        if (!changed) break;
+        }
+    const double tr = G[0][0] + G[1][1] + G[2][2] + G[3][3];
+    const double eps = 1e-13 * tr + 1e-300;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) G[i][i] += eps;
+    // LDL^T (upper part of G holds the input): L unit lower in Lm, D in Dv
+    double Lm[4][4], Dinv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        double dj = G[j][j];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (k < j) dj -= Lm[j][k] * Lm[j][k] / Dinv[k];
+        if (!(dj > 1e-300)) dj = 1e-300;
+        Dinv[j] = 1.0 / dj;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (i > j) {
+                double v = G[j][i];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (k < j) v -= Lm[i][k] * Lm[j][k] / Dinv[k];
+                Lm[i][j] = v * Dinv[j];
+            }
     }
-    int best = 0;
-    double bestn = DBL_MAX;
+    double x[4] = {0.3, 0.2, 0.7, 0.6};
+    for (int it = 0; it < 12; ++it) {
+        double y[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        double n = 0;
+        for (int i = 0; i < 4; ++i) {   // L z = x
+            double v = x[i];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) n += A[r][k] * A[r][k];
-        if (n < bestn) { bestn = n; best = k; }
+            for (int k = 0; k < 4; ++k)
+                if (k < i) v -= Lm[i][k] * y[k];
+            y[i] = v;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) y[i] *= Dinv[i];
+#pragma unroll
+        for (int i = 3; i >= 0; --i) {   // L^T y = z
+            double v = y[i];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (k > i) v -= Lm[k][i] * y[k];
+            y[i] = v;
+        }
+        const double inv = 1.0 / sqrt(y[0] * y[0] + y[1] * y[1] + y[2] * y[2] + y[3] * y[3]);
+        double diff = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const double v = y[i] * inv;
+            diff += fabs(v - x[i]);
+            x[i] = v;
+        }
+        if (diff < 1e-15) break;
     }
     float h[4];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        double v = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) v = (k == best) ? V[r][k] : v;
-        h[r] = (float)v;
-    }
+    for (int r = 0; r < 4; ++r) h[r] = (float)x[r];
     const float sc = (h[3] != 0.f) ? 1.f / h[3] : 1.f;
     X3[0] = h[0] * sc;
     X3[1] = h[1] * sc;

@@ -67,13 +67,15 @@ struct DevArrays {
     float2* lk_L1; float2* lk_R1; float2* lk_R0; float2* lk_C; uint8_t* lk_status;
     // matched (compacted) sets
     float2* m_L0; float2* m_L1; float2* m_R0; float2* m_R1; int* m_age; int* m_str;
-    float* X3;                        // [cap][3]
+    float* X3;                        // [cap][3] matched (compacted)
+    float* X3u;                       // [cap][3] per bucketed feature (written by the KLT kernel)
     // RANSAC hypotheses
     double* hyp_pose;                 // [n_seq][H][12]
     int* hyp_count;                   // [n_seq][H]
     int* hyp_samples;                 // [n_seq][H][5] OpenCV-order sample indices (-1 = invalid)
     unsigned* rng_raw;                // [SVO_RNG_TABLE] cv::RNG((uint64)-1) output stream
     int* inl_idx;                     // [n_seq][cap] ascending inlier indices
+    int* klt_next;                    // [n_seq] next feature index for the persistent KLT warps
     int cap;                          // per-sequence feature capacity
     int n_seq;
     int n_hyp;

@@ -312,11 +312,16 @@ void launch_first_frame(const DevArrays& d, cudaStream_t st) {
 }
 
 // ============================================================================
-// bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry
+// bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry.
+// One block per sequence.  Buckets are visited in coalesced tiles of 1024 (bucket = tile * 1024 + tid);
+// every key is read once into registers, the ordered compaction uses one ballot per tile and a single
+// block scan over the (tile, warp) popcounts.
+constexpr int BM_TILES = 16;   // nb <= 16384 (checked in svo_create)
 __global__ void __launch_bounds__(1024)
 bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
     __shared__ int sm[33];
-    const int seq = blockIdx.x, tid = threadIdx.x;
+    __shared__ int wcount[BM_TILES * 32];
+    const int seq = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     SeqState* s = d.state + seq;
     const long long fo = (long long)seq * d.cap;
     unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
@@ -334,35 +339,51 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
     __threadfence();
     __syncthreads();
 
-    const int chunk = (bg.nb + 1023) / 1024;
-    const int b0 = min(bg.nb, tid * chunk), b1 = min(bg.nb, b0 + chunk);
+    const int ntiles = (bg.nb + 1023) >> 10;
+    unsigned long long w1[BM_TILES], kbv[BM_TILES];
     int c1 = 0;
-    for (int b = b0; b < b1; ++b) {
-        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
-        c1 += ((kt > ka ? kt : ka) != 0ull) ? 1 : 0;
+#pragma unroll
+    for (int j = 0; j < BM_TILES; ++j) {
+        w1[j] = 0ull;
+        kbv[j] = 0ull;
+        const int b = (j << 10) + tid;
+        if (j < ntiles && b < bg.nb) {
+            const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
+            kbv[j] = ld_key(keyB + b);
+            w1[j] = kt > ka ? kt : ka;
+            c1 += (w1[j] != 0ull) ? 1 : 0;
+            keyT[b] = 0ull;   // consumed: ready for the next frame / the next FAST pass of this parity
+            keyA[b] = 0ull;
+            keyB[b] = 0ull;
+        }
     }
     int n1;
     block_excl_scan<1024>(c1, &n1, sm);
-    const bool retry = n1 < pc.pre_matching_threshold;
+    const bool retry = n1 < pc.pre_matching_threshold;   // vo.cpp:327-332
 
-    int c2 = 0;
-    for (int b = b0; b < b1; ++b) {
-        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
-        unsigned long long wv = kt > ka ? kt : ka;
-        if (retry) {
-            const unsigned long long kb = ld_key(keyB + b);
-            if (kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) wv = kb;
-        }
-        c2 += (wv != 0ull) ? 1 : 0;
-    }
-    int total;
-    int off = block_excl_scan<1024>(c2, &total, sm);
-    for (int b = b0; b < b1; ++b) {
-        const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
-        unsigned long long wv = kt > ka ? kt : ka;
-        const unsigned long long kb = ld_key(keyB + b);
+    unsigned ballots[BM_TILES];
+#pragma unroll
+    for (int j = 0; j < BM_TILES; ++j) {
+        unsigned long long wv = w1[j];
+        const unsigned long long kb = kbv[j];
+        // second append: the survivors come first in the feature order, so a thr/4 FAST feature only wins
+        // with a strictly greater score
         if (retry && kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) wv = kb;
+        w1[j] = wv;
+        ballots[j] = __ballot_sync(0xffffffffu, wv != 0ull);
+        if (lane == 0) wcount[j * 32 + wid] = __popc(ballots[j]);
+    }
+    __syncthreads();
+    int total;
+    const int my = (tid < BM_TILES * 32) ? wcount[tid] : 0;
+    const int pre = block_excl_scan<1024>(my, &total, sm);
+    if (tid < BM_TILES * 32) wcount[tid] = pre;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < BM_TILES; ++j) {
+        const unsigned long long wv = w1[j];
         if (wv != 0ull) {
+            const int off = wcount[j * 32 + wid] + __popc(ballots[j] & ((1u << lane) - 1u));
             const unsigned order = bucket_key_order(wv);
             float2 p;
             int age, str;
@@ -382,17 +403,14 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
                 d.bk_age[fo + off] = age;
                 d.bk_str[fo + off] = str;
             }
-            ++off;
         }
-        keyT[b] = 0ull;
-        keyA[b] = 0ull;
-        keyB[b] = 0ull;
     }
     if (tid == 0) {
         s->n_bucketed = min(total, d.cap);
         s->retry = retry ? 1 : 0;
         s->lk_iters = 0;
         s->frame_id += 1;
+        d.klt_next[seq] = 0;
     }
 }
 void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
@@ -414,43 +432,68 @@ __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom
     }
     return p;
 }
+// Persistent warps: every warp pulls the next feature index from a per-sequence counter, so warps that
+// finish a quickly converging feature immediately start another one (the per-feature cost varies 10x).
+// The four legs L0->L1->R1->R0->L0 (vo.cpp:203-215) run in ONE loop body to keep the code I-cache sized.
 __global__ void __launch_bounds__(KLT_WARPS * 32)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc) {
     __shared__ uint8_t patch[KLT_WARPS][SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int f = blockIdx.x * KLT_WARPS + wid;
     SeqState* s = d.state + seq;
-    if (f >= s->n_bucketed) return;
+    const int n = s->n_bucketed;
     const int slot = s->slot;
-    const LkPyramid L0 = make_pyr(d.pyr + pg.base(seq, slot, 0), pg);
-    const LkPyramid R0 = make_pyr(d.pyr + pg.base(seq, slot, 1), pg);
-    const LkPyramid L1 = make_pyr(d.pyr + pg.base(seq, slot ^ 1, 0), pg);
-    const LkPyramid R1 = make_pyr(d.pyr + pg.base(seq, slot ^ 1, 1), pg);
-    const long long o = (long long)seq * d.cap + f;
-    const float2 p0 = d.bk_xy[o];
-    float2 a, b, c, e;
-    int it, iters = 0;
-    unsigned st = 0;
-    st |= lk_track_feature<32, WarpRed>(L0, L1, pc.lk, p0.x, p0.y, lane, patch[wid], a.x, a.y, it) ? 1u : 0u;
-    iters += it;
-    st |= lk_track_feature<32, WarpRed>(L1, R1, pc.lk, a.x, a.y, lane, patch[wid], b.x, b.y, it) ? 2u : 0u;
-    iters += it;
-    st |= lk_track_feature<32, WarpRed>(R1, R0, pc.lk, b.x, b.y, lane, patch[wid], c.x, c.y, it) ? 4u : 0u;
-    iters += it;
-    st |= lk_track_feature<32, WarpRed>(R0, L0, pc.lk, c.x, c.y, lane, patch[wid], e.x, e.y, it) ? 8u : 0u;
-    iters += it;
-    if (lane == 0) {
-        d.lk_L1[o] = a;
-        d.lk_R1[o] = b;
-        d.lk_R0[o] = c;
-        d.lk_C[o] = e;
-        d.lk_status[o] = (uint8_t)st;
-        atomicAdd(&s->lk_iters, iters);
+    // pyramid k: 0 = L0, 1 = L1, 2 = R1, 3 = R0 ; leg l tracks from pyramid l to pyramid (l + 1) & 3
+    const long long base[4] = {pg.base(seq, slot, 0), pg.base(seq, slot ^ 1, 0), pg.base(seq, slot ^ 1, 1),
+                               pg.base(seq, slot, 1)};
+    int* counter = d.klt_next + seq;
+    for (;;) {
+        int f = 0;
+        if (lane == 0) f = atomicAdd(counter, 1);
+        f = __shfl_sync(0xffffffffu, f, 0);
+        if (f >= n) break;
+        const long long o = (long long)seq * d.cap + f;
+        const float2 p0 = d.bk_xy[o];
+        float2 pts[5];
+        pts[0] = p0;
+        int iters = 0;
+        unsigned st = 0;
+#pragma unroll 1
+        for (int leg = 0; leg < 4; ++leg) {
+            const LkPyramid I = make_pyr(d.pyr + base[leg], pg);
+            const LkPyramid J = make_pyr(d.pyr + base[(leg + 1) & 3], pg);
+            int it;
+            float ox, oy;
+            const float ix = leg == 0 ? pts[0].x : (leg == 1 ? pts[1].x : (leg == 2 ? pts[2].x : pts[3].x));
+            const float iy = leg == 0 ? pts[0].y : (leg == 1 ? pts[1].y : (leg == 2 ? pts[2].y : pts[3].y));
+            const int ok = lk_track_feature<32, WarpRed>(I, J, pc.lk, ix, iy, lane, patch[wid], ox, oy, it);
+            st |= ok ? (1u << leg) : 0u;
+            iters += it;
+            if (leg == 0) pts[1] = make_float2(ox, oy);
+            else if (leg == 1) pts[2] = make_float2(ox, oy);
+            else if (leg == 2) pts[3] = make_float2(ox, oy);
+            else pts[4] = make_float2(ox, oy);
+        }
+        if (lane == 0) {
+            const float2 a = pts[1], b = pts[2], c = pts[3], e = pts[4];
+            // findClosePoints + status AND (vo.cpp:217-230) + in-bounds test (vo.cpp:341-359): the is_ok bit
+            bool ok = st == 15u && close_points(p0.x, p0.y, e.x, e.y, pc.circular_threshold);
+            if (pc.check_bounds) {
+                const int W = pc.width, H = pc.height;
+                ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(a.x, a.y, W, H) && in_bounds(c.x, c.y, W, H) &&
+                     in_bounds(b.x, b.y, W, H);
+            }
+            d.lk_L1[o] = a;
+            d.lk_R1[o] = b;
+            d.lk_R0[o] = c;
+            d.lk_C[o] = e;
+            d.lk_status[o] = (uint8_t)(st | (ok ? 16u : 0u));
+            atomicAdd(&s->lk_iters, iters);
+        }
     }
 }
-void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, cudaStream_t st) {
-    dim3 grid((d.cap + KLT_WARPS - 1) / KLT_WARPS, d.n_seq);
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, cudaStream_t st) {
+    dim3 grid(blocks_per_seq, d.n_seq);
     klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc);
 }
 
@@ -501,52 +544,33 @@ __global__ void __launch_bounds__(1024) select_kernel(DevArrays d, PipeConfig pc
     SeqState* s = d.state + seq;
     const long long fo = (long long)seq * d.cap;
     const int n = s->n_bucketed;
-    const int chunk = (n + 1023) / 1024;
-    const int i0 = min(n, tid * chunk), i1 = min(n, i0 + chunk);
-    const int W = pc.width, H = pc.height;
-    int cnt = 0;
-    for (int i = i0; i < i1; ++i) {
-        const float2 p0 = d.bk_xy[fo + i], l1 = d.lk_L1[fo + i], r1 = d.lk_R1[fo + i], r0 = d.lk_R0[fo + i],
-                     c = d.lk_C[fo + i];
-        bool ok = (d.lk_status[fo + i] & 15) == 15 && close_points(p0.x, p0.y, c.x, c.y, pc.circular_threshold);
-        if (pc.check_bounds)
-            ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(l1.x, l1.y, W, H) && in_bounds(r0.x, r0.y, W, H) &&
-                 in_bounds(r1.x, r1.y, W, H);
-        cnt += ok ? 1 : 0;
-    }
-    int total;
-    int off = block_excl_scan<1024>(cnt, &total, sm);
-    for (int i = i0; i < i1; ++i) {
-        const float2 p0 = d.bk_xy[fo + i], l1 = d.lk_L1[fo + i], r1 = d.lk_R1[fo + i], r0 = d.lk_R0[fo + i],
-                     c = d.lk_C[fo + i];
-        bool ok = (d.lk_status[fo + i] & 15) == 15 && close_points(p0.x, p0.y, c.x, c.y, pc.circular_threshold);
-        if (pc.check_bounds)
-            ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(l1.x, l1.y, W, H) && in_bounds(r0.x, r0.y, W, H) &&
-                 in_bounds(r1.x, r1.y, W, H);
-        if (ok) d.lk_status[fo + i] |= 16;   // is_ok mask over the inputs (parity tap)
+    int base = 0;
+    for (int t0 = 0; t0 < n; t0 += 1024) {   // coalesced tiles, stable order
+        const int i = t0 + tid;
+        const bool ok = i < n && (d.lk_status[fo + i] & 16) != 0;
+        int tile_total;
+        const int off = base + block_excl_scan<1024>(ok ? 1 : 0, &tile_total, sm);
         if (ok) {
+            const float2 p0 = d.bk_xy[fo + i];
             const int age = d.bk_age[fo + i] + pc.age_increment, str = d.bk_str[fo + i];   // ages++ (vo.cpp:70-72)
             d.m_L0[fo + off] = p0;
-            d.m_L1[fo + off] = l1;
-            d.m_R0[fo + off] = r0;
-            d.m_R1[fo + off] = r1;
+            d.m_L1[fo + off] = d.lk_L1[fo + i];
+            d.m_R1[fo + off] = d.lk_R1[fo + i];
             d.m_age[fo + off] = age;
             d.m_str[fo + off] = str;
             // currentVOFeatures after matchingFeatures: t0 coordinates (vo.cpp:360)
             d.fs_xy[fo + off] = p0;
             d.fs_age[fo + off] = age;
             d.fs_str[fo + off] = str;
-            ++off;
+            const float2 r0 = d.lk_R0[fo + i];
+            d.m_R0[fo + off] = r0;
+            triangulate_dlt(pc.Pl, pc.Pr, p0.x, p0.y, r0.x, r0.y, d.X3 + (fo + off) * 3);   // vo.cpp:89-94
         }
+        base += tile_total;
     }
-    __syncthreads();
+    const int total = base;
     // RANSAC sample indices in OpenCV's order (depends only on the survivor count)
     if (tid < 32 && total >= 5) warp_build_samples(d.rng_raw, total, d.n_hyp, d.hyp_samples + (long long)seq * d.n_hyp * 5, mods);
-    // triangulation (only consumed when enough features survive; cheap enough to always run)
-    for (int i = tid; i < total; i += 1024) {
-        const float2 a = d.m_L0[fo + i], b = d.m_R0[fo + i];
-        triangulate_dlt(pc.Pl, pc.Pr, a.x, a.y, b.x, b.y, d.X3 + (fo + i) * 3);
-    }
     if (tid == 0) {
         s->n_matched = total;
         s->n_feat = total;
@@ -655,12 +679,14 @@ struct BlockInlierEval {
             for (int i = 0; i < SVO_PNP_ACC; ++i) sm[wid * SVO_PNP_ACC + i] = acc[i];
         }
         __syncthreads();
-#pragma unroll
-        for (int i = 0; i < SVO_PNP_ACC; ++i) {
+        if (threadIdx.x < SVO_PNP_ACC) {   // fixed summation order -> every thread sees identical totals
             double v = 0.0;
-            for (int w = 0; w < FIN_THREADS / 32; ++w) v += sm[w * SVO_PNP_ACC + i];
-            acc[i] = v;
+            for (int w = 0; w < FIN_THREADS / 32; ++w) v += sm[w * SVO_PNP_ACC + threadIdx.x];
+            sm[(FIN_THREADS / 32) * SVO_PNP_ACC + threadIdx.x] = v;
         }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = sm[(FIN_THREADS / 32) * SVO_PNP_ACC + i];
     }
 };
 
@@ -682,7 +708,7 @@ __device__ void write_result(const DevArrays& d, int seq, int success, int reaso
 
 __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, PipeConfig pc) {
     __shared__ int sm_i[33];
-    __shared__ double sm_acc[(FIN_THREADS / 32) * SVO_PNP_ACC];
+    __shared__ double sm_acc[(FIN_THREADS / 32 + 1) * SVO_PNP_ACC];
     const int seq = blockIdx.x, tid = threadIdx.x;
     const int lane = tid & 31, wid = tid >> 5;
     SeqState* s = d.state + seq;
@@ -721,20 +747,19 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
     const float* X3 = d.X3 + fo * 3;
     const float2* uv = d.m_L1 + fo;
     int* idx = d.inl_idx + fo;
-    const int chunk = (n + FIN_THREADS - 1) / FIN_THREADS;
-    const int i0 = min(n, tid * chunk), i1 = min(n, i0 + chunk);
-    int cnt = 0;
-    for (int i = i0; i < i1; ++i) {
-        const float2 q = uv[i];
-        const float uvf[2] = {q.x, q.y};
-        cnt += (reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq) ? 1 : 0;
-    }
-    int n_in;
-    int off = block_excl_scan<FIN_THREADS>(cnt, &n_in, sm_i);
-    for (int i = i0; i < i1; ++i) {
-        const float2 q = uv[i];
-        const float uvf[2] = {q.x, q.y};
-        if (reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq) idx[off++] = i;
+    int n_in = 0;
+    for (int t0 = 0; t0 < n; t0 += FIN_THREADS) {   // coalesced tiles, ascending order
+        const int i = t0 + tid;
+        bool in = false;
+        if (i < n) {
+            const float2 q = uv[i];
+            const float uvf[2] = {q.x, q.y};
+            in = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq;
+        }
+        int tile_total;
+        const int off = n_in + block_excl_scan<FIN_THREADS>(in ? 1 : 0, &tile_total, sm_i);
+        if (in) idx[off] = i;
+        n_in += tile_total;
     }
     __syncthreads();
     // ---- LM refit on all inliers (uniform control flow across the block)

@@ -33,7 +33,7 @@ void launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, 
 void launch_first_frame(const DevArrays& d, cudaStream_t st);
 void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
                          cudaStream_t st);
-void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, cudaStream_t st);
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, cudaStream_t st);
 void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_samples(const DevArrays& d, cudaStream_t st);   // standalone (select_kernel fuses it)
