@@ -273,7 +273,7 @@ def run_gpu(args, rank, world, local_rank):
         for _ in range(n_t):
             enqueue(ctx, min(k, n_total - 1) if False else k % n_total)
             k += 1
-        names = ["ingest_fast_pyramid", "bucket", "klt", "select_triangulate", "pnp_ransac"]
+        names = ["ingest_fast_pyramid", "bucket", "klt", "select_triangulate", "pnp_hypotheses", "pnp_refit"]
         stages = {}
         for s_, nm in enumerate(names):
             msv, ln = C.c_double(0), C.c_longlong(0)

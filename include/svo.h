@@ -133,7 +133,7 @@ void* svo_stream(svo_ctx* ctx);
 long long svo_launch_count(svo_ctx* ctx);
 /* Accumulated CUDA-event time (ms) and launch count of one stage since the last
  * svo_reset_timers(); only measured when svo_enable_timers(ctx,1) was called.
- * stage: 0 ingest(FAST+pyramid) 1 bucket 2 klt 3 select+triangulate 4 pnp */
+ * stage: 0 ingest(FAST+pyramid) 1 bucket 2 klt 3 select+triangulate 4 pnp hypotheses 5 pnp refit */
 int svo_enable_timers(svo_ctx* ctx, int on);
 int svo_get_stage_time(svo_ctx* ctx, int stage, double* ms_out, long long* launches_out);
 int svo_reset_timers(svo_ctx* ctx);

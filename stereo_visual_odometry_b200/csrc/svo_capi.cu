@@ -93,9 +93,9 @@ struct svo_ctx {
     int klt_blocks = 148;   // persistent KLT blocks per sequence
     // timers
     bool timers = false;
-    cudaEvent_t ev[6];
-    double stage_ms[5] = {0, 0, 0, 0, 0};
-    long long stage_launches[5] = {0, 0, 0, 0, 0};
+    cudaEvent_t ev[7];
+    double stage_ms[6] = {0, 0, 0, 0, 0, 0};
+    long long stage_launches[6] = {0, 0, 0, 0, 0, 0};
 };
 
 static BucketGeom make_bucket_geom(int height, int width, int n_bh, int n_bw, int start_row, int age_thr,
@@ -226,6 +226,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.m_R1, C));   CU(dev_alloc(c, &d.m_age, C));   CU(dev_alloc(c, &d.m_str, C));
     CU(dev_alloc(c, &d.X3, C * 3));
     CU(dev_alloc(c, &d.X3u, C * 3));
+    CU(dev_alloc(c, &d.in_uv, C));
     CU(dev_alloc(c, &d.hyp_pose, S * d.n_hyp * 12));
     CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
     CU(dev_alloc(c, &d.inl_idx, C));
@@ -250,7 +251,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         init[s].last_T[0] = init[s].last_T[5] = init[s].last_T[10] = init[s].last_T[15] = 1.0;
     }
     CU(cudaMemcpyAsync(d.state, init.data(), sizeof(SeqState) * S, cudaMemcpyHostToDevice, c->stream));
-    for (int i = 0; i < 6; ++i) CU(cudaEventCreate(&c->ev[i]));
+    for (int i = 0; i < 7; ++i) CU(cudaEventCreate(&c->ev[i]));
     {
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, p->device));
@@ -297,7 +298,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
     for (void* q : c->allocs) cudaFree(q);
     if (c->host_result) cudaFreeHost(c->host_result);
     if (c->stream) {
-        for (int i = 0; i < 6; ++i)
+        for (int i = 0; i < 7; ++i)
             if (c->ev[i]) cudaEventDestroy(c->ev[i]);
         cudaStreamDestroy(c->stream);
     }
@@ -327,14 +328,14 @@ extern "C" int svo_enable_timers(svo_ctx* c, int on) {
 }
 extern "C" int svo_reset_timers(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
-    for (int i = 0; i < 5; ++i) {
+    for (int i = 0; i < 6; ++i) {
         c->stage_ms[i] = 0;
         c->stage_launches[i] = 0;
     }
     return SVO_OK;
 }
 extern "C" int svo_get_stage_time(svo_ctx* c, int stage, double* ms_out, long long* launches_out) {
-    if (!c || stage < 0 || stage >= 5) return fail(SVO_ERR_INVALID, "bad stage");
+    if (!c || stage < 0 || stage >= 6) return fail(SVO_ERR_INVALID, "bad stage");
     if (ms_out) *ms_out = c->stage_ms[stage];
     if (launches_out) *launches_out = c->stage_launches[stage];
     return SVO_OK;
@@ -362,8 +363,10 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         if (tm) cudaEventRecord(c->ev[3], st);
         launch_select(c->d, c->pc, st);
         if (tm) cudaEventRecord(c->ev[4], st);
-        launch_pnp(c->d, c->pc, st);
+        launch_pnp_hyp(c->d, c->pc, st);
         if (tm) cudaEventRecord(c->ev[5], st);
+        launch_pnp_final(c->d, c->pc, st);
+        if (tm) cudaEventRecord(c->ev[6], st);
         c->launches += 5;
     }
     if (results_dev)
@@ -371,8 +374,8 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     CU(cudaGetLastError());
     if (tm) {
         CU(cudaStreamSynchronize(st));
-        const int nst = first ? 1 : 5;
-        const int nl[5] = {n_ingest, 1, 1, 1, 2};
+        const int nst = first ? 1 : 6;
+        const int nl[6] = {n_ingest, 1, 1, 1, 1, 1};
         for (int i = 0; i < nst; ++i) {
             float ms = 0.f;
             cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]);

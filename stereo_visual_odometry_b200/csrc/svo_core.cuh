@@ -187,6 +187,17 @@ SVO_HD float fsub(float a, float b) {
 #define SVO_LK_PATCH (SVO_LK_WIN + 3)     // 13: window + 1 (bilinear) + 2 (Scharr halo)
 #define SVO_LK_PATCH_PITCH 16
 #define SVO_LK_NPIX (SVO_LK_WIN * SVO_LK_WIN)
+#define SVO_LK_DW (SVO_LK_WIN + 1)        // 11 x 11 derivative positions
+#define SVO_LK_DP 12                      // derivative patch pitch
+#define SVO_LK_JR 18                      // rows of the staged J patch
+#define SVO_LK_JC 24                      // pixel pairs per row of the staged J patch
+
+// Per-feature scratch shared by the cooperating lanes (shared memory on the device).
+struct LkScratch {
+    uint8_t ipatch[SVO_LK_PATCH * SVO_LK_PATCH_PITCH];     // template neighbourhood, u8
+    int dxy[SVO_LK_DW * SVO_LK_DP];                        // Scharr (dx | dy << 16), two int16
+    unsigned short jp[SVO_LK_JR * SVO_LK_JC];              // J patch as horizontal pixel pairs p(x) | p(x+1) << 8
+};
 
 SVO_HD void lk_weights(float a, float b, int& iw00, int& iw01, int& iw10, int& iw11) {
     const float W = 16384.f;   // 1 << W_BITS
@@ -196,14 +207,61 @@ SVO_HD void lk_weights(float a, float b, int& iw00, int& iw01, int& iw10, int& i
     iw11 = 16384 - iw00 - iw01 - iw10;
 }
 
-// Track ONE feature through all pyramid levels.  Executed by LANES cooperating
-// lanes (every lane runs the same scalar control flow; window pixels are
-// distributed lane-cyclically; Red sums across lanes).  `patch` is scratch of
-// SVO_LK_PATCH * SVO_LK_PATCH_PITCH bytes shared by the lanes.
+template <int LANES> struct LkAcc { typedef int type; };
+template <> struct LkAcc<1> { typedef long long type; };   // host unit tests: one lane carries all 100 pixels
+
+// c + a.lo16 * b.byte0 + a.hi16 * b.byte1 with SIGNED 16-bit weights (iw11 = 2^14 - iw00 - iw01 - iw10
+// can be -1 or -2) and UNSIGNED pixels: one IDP.2A (dp2a.lo.s32.u32) on the device
+SVO_HD int dp2a_lo_su(unsigned a, unsigned b, int c) {
+#if defined(__CUDA_ARCH__)
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#else
+    return c + (int)(short)(a & 0xFFFFu) * (int)(b & 0xFFu) + (int)(short)(a >> 16) * (int)((b >> 8) & 0xFFu);
+#endif
+}
+SVO_HD unsigned pack_weights(int lo, int hi) { return ((unsigned)lo & 0xFFFFu) | ((unsigned)hi << 16); }
+
+// Stage the J patch whose top-left pixel is (jx0, jy0): jp[y][x] = J(jx0+x, jy0+y) | J(jx0+x+1, jy0+y) << 8
+// with BORDER_REFLECT_101.  jx0 is a multiple of 4, so interior patches are fetched as aligned words.
+template <int LANES>
+SVO_HD void lk_stage_j(const LkLevel& J, int jx0, int jy0, int lane, unsigned short* jp) {
+    const bool interior = jx0 >= 0 && jy0 >= 0 && jx0 + SVO_LK_JC + 4 <= J.w && jy0 + SVO_LK_JR <= J.h &&
+                          (J.pitch & 3) == 0 && (((size_t)J.img) & 3) == 0;
+    if (interior) {
+        constexpr int WORDS = SVO_LK_JC / 4;   // 6 words -> 24 pairs (the 25th pixel comes from the next word)
+        for (int it = lane; it < SVO_LK_JR * WORDS; it += LANES) {
+            const int y = it / WORDS, k = it - y * WORDS;
+            const uint8_t* src = J.img + (size_t)(jy0 + y) * J.pitch + jx0 + 4 * k;
+            unsigned w0, w1;
+#if defined(__CUDA_ARCH__)
+            w0 = *reinterpret_cast<const unsigned*>(src);
+            w1 = *reinterpret_cast<const unsigned*>(src + 4);
+#else
+            w0 = src[0] | (src[1] << 8) | (src[2] << 16) | ((unsigned)src[3] << 24);
+            w1 = src[4] | (src[5] << 8) | (src[6] << 16) | ((unsigned)src[7] << 24);
+#endif
+            const unsigned p0 = w0 & 0xFFFFu, p1 = (w0 >> 8) & 0xFFFFu, p2 = w0 >> 16, p3 = (w0 >> 24) | ((w1 & 0xFFu) << 8);
+            unsigned* dst = reinterpret_cast<unsigned*>(jp + y * SVO_LK_JC + 4 * k);
+            dst[0] = p0 | (p1 << 16);
+            dst[1] = p2 | (p3 << 16);
+        }
+    } else {
+        for (int it = lane; it < SVO_LK_JR * SVO_LK_JC; it += LANES) {
+            const int y = it / SVO_LK_JC, x = it - y * SVO_LK_JC;
+            const uint8_t* row = J.img + (size_t)reflect101(jy0 + y, J.h) * J.pitch;
+            jp[it] = (unsigned short)(row[reflect101(jx0 + x, J.w)] | (row[reflect101(jx0 + x + 1, J.w)] << 8));
+        }
+    }
+}
+
+// Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
+// the same scalar control flow; window pixels are distributed lane-cyclically; Red sums across lanes).
 // Returns status (1 = tracked) and writes the output position.
 template <int LANES, class Red>
 SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const LkConfig& cfg,
-                            float ptx, float pty, int lane, uint8_t* patch, float& outx,
+                            float ptx, float pty, int lane, LkScratch& sc, float& outx,
                             float& outy, int& iters_out) {
     constexpr int SLOTS = (SVO_LK_NPIX + LANES - 1) / LANES;
     const float half_win = 4.5f;   // (winSize - 1) * 0.5f
@@ -238,16 +296,41 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         int iw00, iw01, iw10, iw11;
         lk_weights(fsub(prx, (float)ipx), fsub(pry, (float)ipy), iw00, iw01, iw10, iw11);
 
-        // ---- stage the 13x13 neighbourhood of the template window
+        // ---- stage the 13x13 neighbourhood of the template window (BORDER_REFLECT_101)
         Red::sync();
         for (int idx = lane; idx < SVO_LK_PATCH * SVO_LK_PATCH; idx += LANES) {
             const int py = idx / SVO_LK_PATCH, px = idx - py * SVO_LK_PATCH;
-            patch[py * SVO_LK_PATCH_PITCH + px] = (uint8_t)I.at_r(ipx - 1 + px, ipy - 1 + py);
+            sc.ipatch[py * SVO_LK_PATCH_PITCH + px] = (uint8_t)I.at_r(ipx - 1 + px, ipy - 1 + py);
+        }
+        // J patch around the start of the search (independent of the template work)
+        float cx = fsub(nxt_x, half_win), cy = fsub(nxt_y, half_win);   // nextPt -= halfWin
+        int jx0 = (floor_int(cx) - 5) & ~3, jy0 = floor_int(cy) - 3;
+        {
+            const int fx0 = floor_int(cx), fy0 = floor_int(cy);
+            if (!(fx0 < -SVO_LK_WIN || fx0 >= J.w || fy0 < -SVO_LK_WIN || fy0 >= J.h)) lk_stage_j<LANES>(J, jx0, jy0, lane, sc.jp);
+        }
+        Red::sync();
+        // ---- Scharr derivatives on the 11x11 positions of the window (zero outside the level:
+        // derivBorder = BORDER_CONSTANT), packed (dx, dy) int16
+        for (int idx = lane; idx < SVO_LK_DW * SVO_LK_DW; idx += LANES) {
+            const int y = idx / SVO_LK_DW, x = idx - y * SVO_LK_DW;
+            const int ax = ipx + x, ay = ipy + y;
+            int v = 0;
+            if (ax >= 0 && ax < I.w && ay >= 0 && ay < I.h) {
+                const uint8_t* p = sc.ipatch + y * SVO_LK_PATCH_PITCH + x;   // top-left of the 3x3 around patch (x+1, y+1)
+                const int a00 = p[0], a01 = p[1], a02 = p[2];
+                const int a10 = p[SVO_LK_PATCH_PITCH], a12 = p[SVO_LK_PATCH_PITCH + 2];
+                const int a20 = p[2 * SVO_LK_PATCH_PITCH], a21 = p[2 * SVO_LK_PATCH_PITCH + 1], a22 = p[2 * SVO_LK_PATCH_PITCH + 2];
+                const int dx = 3 * (a02 + a22 - a00 - a20) + 10 * (a12 - a10);
+                const int dy = 3 * (a20 + a22 - a00 - a02) + 10 * (a21 - a01);
+                v = (dx & 0xFFFF) | (dy << 16);
+            }
+            sc.dxy[y * SVO_LK_DP + x] = v;
         }
         Red::sync();
 
-        // ---- template window: Ival (x32), Ix, Iy (Scharr, bilinear), structure tensor
-        short Iv[SLOTS], Ixv[SLOTS], Iyv[SLOTS];
+        // ---- template window: Ival (x32), Ix, Iy (bilinear), structure tensor
+        int Iv[SLOTS], Ixv[SLOTS], Iyv[SLOTS];
         int sA11 = 0, sA12 = 0, sA22 = 0;
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) {
@@ -255,33 +338,14 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             Iv[s] = 0; Ixv[s] = 0; Iyv[s] = 0;
             if (idx < SVO_LK_NPIX) {
                 const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
-                // 4x4 block of the patch whose inner 2x2 are the bilinear taps
-                int P[4][4];
-#pragma unroll
-                for (int r = 0; r < 4; ++r)
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) P[r][c] = patch[(wy + r) * SVO_LK_PATCH_PITCH + wx + c];
-                int dx[2][2], dy[2][2];
-#pragma unroll
-                for (int r = 0; r < 2; ++r)
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        // Scharr at patch (c+1, r+1); zero outside the level (derivBorder = CONSTANT)
-                        const int ax = ipx + wx + c, ay = ipy + wy + r;
-                        const bool inside = (ax >= 0) & (ax < I.w) & (ay >= 0) & (ay < I.h);
-                        const int t0m = 3 * (P[r][c] + P[r + 2][c]) + 10 * P[r + 1][c];
-                        const int t0p = 3 * (P[r][c + 2] + P[r + 2][c + 2]) + 10 * P[r + 1][c + 2];
-                        const int t1m = P[r + 2][c] - P[r][c];
-                        const int t1c = P[r + 2][c + 1] - P[r][c + 1];
-                        const int t1p = P[r + 2][c + 2] - P[r][c + 2];
-                        dx[r][c] = inside ? (t0p - t0m) : 0;
-                        dy[r][c] = inside ? (3 * (t1m + t1p) + 10 * t1c) : 0;
-                    }
-                const int iv = (P[1][1] * iw00 + P[1][2] * iw01 + P[2][1] * iw10 + P[2][2] * iw11 + (1 << 8)) >> 9;
-                const int ix = (dx[0][0] * iw00 + dx[0][1] * iw01 + dx[1][0] * iw10 + dx[1][1] * iw11 + (1 << 13)) >> 14;
-                const int iy = (dy[0][0] * iw00 + dy[0][1] * iw01 + dy[1][0] * iw10 + dy[1][1] * iw11 + (1 << 13)) >> 14;
+                const uint8_t* p = sc.ipatch + (wy + 1) * SVO_LK_PATCH_PITCH + wx + 1;
+                const int iv = (p[0] * iw00 + p[1] * iw01 + p[SVO_LK_PATCH_PITCH] * iw10 + p[SVO_LK_PATCH_PITCH + 1] * iw11 + (1 << 8)) >> 9;
+                const int* dq = sc.dxy + wy * SVO_LK_DP + wx;
+                const int d00 = dq[0], d01 = dq[1], d10 = dq[SVO_LK_DP], d11 = dq[SVO_LK_DP + 1];
+                const int ix = ((int)(short)d00 * iw00 + (int)(short)d01 * iw01 + (int)(short)d10 * iw10 + (int)(short)d11 * iw11 + (1 << 13)) >> 14;
+                const int iy = ((d00 >> 16) * iw00 + (d01 >> 16) * iw01 + (d10 >> 16) * iw10 + (d11 >> 16) * iw11 + (1 << 13)) >> 14;
                 Iv[s] = (short)iv; Ixv[s] = (short)ix; Iyv[s] = (short)iy;
-                sA11 += ix * ix; sA12 += ix * iy; sA22 += iy * iy;
+                sA11 += Ixv[s] * Ixv[s]; sA12 += Ixv[s] * Iyv[s]; sA22 += Iyv[s] * Iyv[s];
             }
         }
         sA11 = Red::sum(sA11); sA12 = Red::sum(sA12); sA22 = Red::sum(sA22);
@@ -298,7 +362,6 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         }
         D = 1.f / D;
 
-        float cx = fsub(nxt_x, half_win), cy = fsub(nxt_y, half_win);   // nextPt -= halfWin
         float pdx = 0.f, pdy = 0.f;
         for (int j = 0; j < cfg.max_iters; ++j) {
             const int inx = floor_int(cx), iny = floor_int(cy);
@@ -307,33 +370,41 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
                 break;
             }
             ++iters;
+            if (inx < jx0 || inx + SVO_LK_WIN > jx0 + SVO_LK_JC || iny < jy0 || iny + SVO_LK_WIN + 1 > jy0 + SVO_LK_JR) {
+                // the window left the staged patch: re-centre it
+                jx0 = (inx - 5) & ~3;
+                jy0 = iny - 3;
+                Red::sync();
+                lk_stage_j<LANES>(J, jx0, jy0, lane, sc.jp);
+                Red::sync();
+            }
+#ifdef SVO_LK_TRACE
+            printf("L%d j%d c=(%.4f,%.4f) in=(%d,%d) j0=(%d,%d)\n", level, j, cx, cy, inx, iny, jx0, jy0);
+#endif
             lk_weights(fsub(cx, (float)inx), fsub(cy, (float)iny), iw00, iw01, iw10, iw11);
-            const bool interior = (inx >= 0) & (inx + SVO_LK_WIN < J.w) & (iny >= 0) & (iny + SVO_LK_WIN < J.h);
-            long long sb1 = 0, sb2 = 0;
+            const unsigned jt = pack_weights(iw00, iw01), jb = pack_weights(iw10, iw11);
+            const unsigned short* jbase = sc.jp + (iny - jy0) * SVO_LK_JC + (inx - jx0);
+            typename LkAcc<LANES>::type sb1 = 0, sb2 = 0;   // <= 4 pixels per lane fit 32 bits
 #pragma unroll
             for (int s = 0; s < SLOTS; ++s) {
                 const int idx = lane + s * LANES;
                 if (idx < SVO_LK_NPIX) {
                     const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
-                    int j00, j01, j10, j11;
-                    if (interior) {
-                        const uint8_t* p = J.img + (size_t)(iny + wy) * J.pitch + inx + wx;
-                        j00 = p[0]; j01 = p[1]; j10 = p[J.pitch]; j11 = p[J.pitch + 1];
-                    } else {
-                        j00 = J.at_r(inx + wx, iny + wy);     j01 = J.at_r(inx + wx + 1, iny + wy);
-                        j10 = J.at_r(inx + wx, iny + wy + 1); j11 = J.at_r(inx + wx + 1, iny + wy + 1);
-                    }
-                    const int diff = ((j00 * iw00 + j01 * iw01 + j10 * iw10 + j11 * iw11 + (1 << 8)) >> 9) - (int)Iv[s];
-                    sb1 += diff * (int)Ixv[s];
-                    sb2 += diff * (int)Iyv[s];
+                    const unsigned short* q = jbase + wy * SVO_LK_JC + wx;
+                    const int v = dp2a_lo_su(jb, q[SVO_LK_JC], dp2a_lo_su(jt, q[0], 1 << 8));
+                    const int diff = (v >> 9) - Iv[s];
+                    sb1 += diff * Ixv[s];
+                    sb2 += diff * Iyv[s];
                 }
             }
-            sb1 = Red::sum64(sb1);
-            sb2 = Red::sum64(sb2);
-            const float b1 = fmul((float)sb1, FLT_SCALE);
-            const float b2 = fmul((float)sb2, FLT_SCALE);
+            const long long tb1 = Red::sum64(sb1), tb2 = Red::sum64(sb2);
+            const float b1 = fmul((float)tb1, FLT_SCALE);
+            const float b2 = fmul((float)tb2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);
             const float ddy = fmul(fsub(fmul(A12, b1), fmul(A11, b2)), D);
+#ifdef SVO_LK_TRACE
+            printf("   b=(%lld,%lld) d=(%g,%g) cy=%.9g iny=%d\n", (long long)tb1, (long long)tb2, ddx, ddy, cy, iny);
+#endif
             cx = fadd(cx, ddx);
             cy = fadd(cy, ddy);
             nx = fadd(cx, half_win);
@@ -509,13 +580,26 @@ SVO_HD double rotation_angle(const double* R) {
     return atan2(s, c);
 }
 
+// 1/z to ~4e-15 relative: float32 reciprocal refined by one Newton step in FP64 (the projection is
+// rounded to float32 afterwards, so this is far inside the noise; a full FP64 division costs ~10x more).
+SVO_HD double fast_rcp(double z) {
+#if defined(__CUDA_ARCH__)
+    if (!(fabs(z) > 1e-30 && fabs(z) < 1e30)) return 1.0 / z;
+    const double r = (double)__frcp_rn((float)z);
+    const double r1 = r * (2.0 - z * r);
+    return r1 * (2.0 - z * r1);
+#else
+    return 1.0 / z;
+#endif
+}
+
 // cv::projectPoints (no distortion), FP64.
 SVO_HD void project_point(const Pose& P, const Intrinsics& K, double X, double Y, double Z, double& u,
                           double& v) {
     const double x = P.R[0] * X + P.R[1] * Y + P.R[2] * Z + P.t[0];
     const double y = P.R[3] * X + P.R[4] * Y + P.R[5] * Z + P.t[1];
     const double z = P.R[6] * X + P.R[7] * Y + P.R[8] * Z + P.t[2];
-    const double iz = z != 0.0 ? 1.0 / z : 1.0;
+    const double iz = z != 0.0 ? fast_rcp(z) : 1.0;
     u = K.fx * (x * iz) + K.cx;
     v = K.fy * (y * iz) + K.cy;
 }
@@ -652,15 +736,19 @@ SVO_HD void pnp_refine_lm(Pose& P, Eval& eval, int max_iter) {
             pnp_apply_step(P, d, cand);
             eval(cand, cand_acc, true);
         }
+        const double ang = rotation_angle(P.R);
+        const double pn = sqrt(ang * ang + P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
+        const double dn = solved ? sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + d[3] * d[3] + d[4] * d[4] + d[5] * d[5]) : 0.0;
         if (!solved || !(cand_acc[27] <= prev_err)) {
+            // CvLevMarq would now raise lambda up to 16 times, re-evaluating the error each time, until rounding
+            // noise lets a (still smaller) step pass and the relative-change test ends the loop.  When the rejected
+            // step is already below that termination size the outcome is the current pose to ~1e-12: stop here.
+            if (solved && dn < (double)FLT_EPSILON * pn) return;
             if (++lg <= 16) continue;   // retry with more damping from the same linearisation
             if (!solved) return;
         }
         lg = lg - 1 < -16 ? -16 : lg - 1;
         // accepted
-        const double ang = rotation_angle(P.R);
-        const double pn = sqrt(ang * ang + P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
-        const double dn = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + d[3] * d[3] + d[4] * d[4] + d[5] * d[5]);
         P = cand;
         ++iters;
         if (iters >= max_iter || dn < (double)FLT_EPSILON * pn) return;

@@ -68,7 +68,8 @@ struct DevArrays {
     // matched (compacted) sets
     float2* m_L0; float2* m_L1; float2* m_R0; float2* m_R1; int* m_age; int* m_str;
     float* X3;                        // [cap][3] matched (compacted)
-    float* X3u;                       // [cap][3] per bucketed feature (written by the KLT kernel)
+    float* X3u;                       // [cap][3] inlier 3-D points, compacted for the LM refit
+    float2* in_uv;                    // [cap] inlier image points, compacted for the LM refit
     // RANSAC hypotheses
     double* hyp_pose;                 // [n_seq][H][12]
     int* hyp_count;                   // [n_seq][H]

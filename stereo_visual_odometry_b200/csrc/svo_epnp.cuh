@@ -72,6 +72,7 @@ SVO_HD void jacobi_eigen_sym(double* A, double* Vt, double* d) {
 // Returns false if A is (numerically) rank deficient.
 template <int ROWS, int COLS>
 SVO_HD bool householder_ls(double* A, double* b, double* x) {
+#pragma unroll
     for (int k = 0; k < COLS; ++k) {
         double norm = 0.0;
         for (int i = k; i < ROWS; ++i) norm += A[i * COLS + k] * A[i * COLS + k];
@@ -185,6 +186,7 @@ struct EpnpWork {              // per-hypothesis scratch (shared memory on the d
     double Vt[144];            // rows = eigenvectors
     double M[120];             // 10 x 12
     double cs[12];             // (c, s) of the 6 concurrent rotations
+    unsigned char pq[136];     // round-robin pair table [11][6][2]
     double dv[72];             // [4][6][3]
     double L[60], rho[6];
     double pws[15], us[10], alphas[20], cws[12];
@@ -207,10 +209,39 @@ SVO_HD void rr_pair(int r, int k, int& p, int& q) {
     q = a < b ? b : a;
 }
 
+// Jacobi rotation zeroing a_pq of a symmetric matrix: one sqrt, one division, one rsqrt.
+SVO_HD void jacobi_cs(double app, double aqq, double apq, double& c, double& s) {
+    c = 1.0;
+    s = 0.0;
+    if (apq != 0.0) {
+        const double h = aqq - app;
+        const double r = sqrt(h * h + 4.0 * apq * apq);
+        const double t = (h >= 0 ? 2.0 : -2.0) * apq / (fabs(h) + r);
+#if defined(__CUDA_ARCH__)
+        c = rsqrt(t * t + 1.0);
+#else
+        c = 1.0 / sqrt(t * t + 1.0);
+#endif
+        s = t * c;
+    }
+}
+
+// Parallel-order (round-robin) Jacobi on the 12x12 symmetric matrix w.A: 11 rounds of 6 disjoint
+// rotations per sweep.  Per round: 6 lanes compute (c, s); then the 21 upper 2x2 blocks
+// A_blk <- J_i^T A_blk J_j are updated in place (each block is owned by one lane, the mirror
+// block is written too so the matrix stays exactly symmetric) together with the 6 x 12 row pairs of Vt.
 template <int LANES, class Red>
 SVO_HD void jacobi12_parallel(EpnpWork& w, int lane) {
     for (int i = lane; i < 144; i += LANES) w.Vt[i] = (i / 12 == i % 12) ? 1.0 : 0.0;
+    for (int i = lane; i < 66; i += LANES) {
+        int p, q;
+        rr_pair(i / 6, i % 6, p, q);
+        w.pq[2 * i] = (unsigned char)p;
+        w.pq[2 * i + 1] = (unsigned char)q;
+    }
     Red::sync();
+    constexpr int NB = (21 + LANES - 1) / LANES;   // blocks per lane
+    constexpr int NV = (72 + LANES - 1) / LANES;   // Vt items per lane
     for (int sweep = 0; sweep < 30; ++sweep) {
         double off = 0.0, diag = 0.0;
         for (int i = lane; i < 144; i += LANES) {
@@ -219,43 +250,46 @@ SVO_HD void jacobi12_parallel(EpnpWork& w, int lane) {
         }
         off = Red::sumd(off);
         diag = Red::sumd(diag);
-        if (off <= 1e-28 * diag || off == 0.0) break;
+#ifdef SVO_DEBUG_SWEEPS
+        printf("sweep %d off %.3g diag %.3g\n", sweep, off, diag);
+#endif
+        if (off <= 1e-22 * diag || off == 0.0) break;
         for (int r = 0; r < 11; ++r) {
+            const unsigned char* pq = w.pq + 12 * r;
             for (int k = lane; k < 6; k += LANES) {
-                int p, q;
-                rr_pair(r, k, p, q);
-                const double apq = w.A[p * 12 + q];
-                double c = 1.0, s = 0.0;
-                if (apq != 0.0) {
-                    const double theta = (w.A[q * 12 + q] - w.A[p * 12 + p]) / (2.0 * apq);
-                    const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                    c = 1.0 / sqrt(t * t + 1.0);
-                    s = t * c;
+                const int p = pq[2 * k], q = pq[2 * k + 1];
+                jacobi_cs(w.A[p * 13], w.A[q * 13], w.A[p * 12 + q], w.cs[2 * k], w.cs[2 * k + 1]);
+            }
+            Red::sync();
+#pragma unroll
+            for (int bi = 0; bi < NB; ++bi) {
+                const int l = lane + bi * LANES;
+                if (l < 21) {
+                    // l -> (ki <= kj) in row-major upper-triangular order
+                    int ki = 0, rem = l;
+                    while (rem >= 6 - ki) { rem -= 6 - ki; ++ki; }
+                    const int kj = ki + rem;
+                    const int pi = pq[2 * ki], qi = pq[2 * ki + 1], pj = pq[2 * kj], qj = pq[2 * kj + 1];
+                    const double ci = w.cs[2 * ki], si = w.cs[2 * ki + 1], cj = w.cs[2 * kj], sj = w.cs[2 * kj + 1];
+                    const double a = w.A[pi * 12 + pj], b = w.A[pi * 12 + qj], c = w.A[qi * 12 + pj], d = w.A[qi * 12 + qj];
+                    const double a1 = ci * a - si * c, b1 = ci * b - si * d, c1 = si * a + ci * c, d1 = si * b + ci * d;
+                    double a2 = cj * a1 - sj * b1, b2 = sj * a1 + cj * b1, c2 = cj * c1 - sj * d1, d2 = sj * c1 + cj * d1;
+                    if (ki == kj) { b2 = 0.0; c2 = 0.0; }
+                    w.A[pi * 12 + pj] = a2; w.A[pi * 12 + qj] = b2; w.A[qi * 12 + pj] = c2; w.A[qi * 12 + qj] = d2;
+                    w.A[pj * 12 + pi] = a2; w.A[qj * 12 + pi] = b2; w.A[pj * 12 + qi] = c2; w.A[qj * 12 + qi] = d2;
                 }
-                w.cs[2 * k] = c;
-                w.cs[2 * k + 1] = s;
             }
-            Red::sync();
-            for (int it = lane; it < 72; it += LANES) {   // A <- A J (columns)
-                const int row = it / 6, k = it - row * 6;
-                int p, q;
-                rr_pair(r, k, p, q);
-                const double c = w.cs[2 * k], s = w.cs[2 * k + 1];
-                const double ap = w.A[row * 12 + p], aq = w.A[row * 12 + q];
-                w.A[row * 12 + p] = c * ap - s * aq;
-                w.A[row * 12 + q] = s * ap + c * aq;
-            }
-            Red::sync();
-            for (int it = lane; it < 144; it += LANES) {   // A <- J^T A (rows), Vt <- J^T Vt
-                const int half = it / 72, j = it - half * 72;
-                const int k = j / 12, col = j - k * 12;
-                int p, q;
-                rr_pair(r, k, p, q);
-                const double c = w.cs[2 * k], s = w.cs[2 * k + 1];
-                double* Mx = half ? w.Vt : w.A;
-                const double ap = Mx[p * 12 + col], aq = Mx[q * 12 + col];
-                Mx[p * 12 + col] = c * ap - s * aq;
-                Mx[q * 12 + col] = s * ap + c * aq;
+#pragma unroll
+            for (int vi = 0; vi < NV; ++vi) {
+                const int it = lane + vi * LANES;
+                if (it < 72) {
+                    const int k = it / 12, col = it - k * 12;
+                    const int p = pq[2 * k], q = pq[2 * k + 1];
+                    const double c = w.cs[2 * k], s = w.cs[2 * k + 1];
+                    const double vp = w.Vt[p * 12 + col], vq = w.Vt[q * 12 + col];
+                    w.Vt[p * 12 + col] = c * vp - s * vq;
+                    w.Vt[q * 12 + col] = s * vp + c * vq;
+                }
             }
             Red::sync();
         }
@@ -300,22 +334,51 @@ SVO_HD bool householder_ls6(double* A /*6 x 5 storage, row stride 5*/, double* b
 
 SVO_HD void epnp_gauss_newton(const double* L, const double* rho, double* betas) {
     for (int it = 0; it < 5; ++it) {
-        double A[30], b[6], x[5];
+        double A[24], b[6], x[4];
+        const double b0 = betas[0], b1 = betas[1], b2 = betas[2], b3 = betas[3];
+#pragma unroll
         for (int i = 0; i < 6; ++i) {
             const double* r = L + i * 10;
-            double* a = A + i * 5;
-            a[0] = 2 * r[0] * betas[0] + r[1] * betas[1] + r[3] * betas[2] + r[6] * betas[3];
-            a[1] = r[1] * betas[0] + 2 * r[2] * betas[1] + r[4] * betas[2] + r[7] * betas[3];
-            a[2] = r[3] * betas[0] + r[4] * betas[1] + 2 * r[5] * betas[2] + r[8] * betas[3];
-            a[3] = r[6] * betas[0] + r[7] * betas[1] + r[8] * betas[2] + 2 * r[9] * betas[3];
-            b[i] = rho[i] - (r[0] * betas[0] * betas[0] + r[1] * betas[0] * betas[1] + r[2] * betas[1] * betas[1] +
-                             r[3] * betas[0] * betas[2] + r[4] * betas[1] * betas[2] + r[5] * betas[2] * betas[2] +
-                             r[6] * betas[0] * betas[3] + r[7] * betas[1] * betas[3] + r[8] * betas[2] * betas[3] +
-                             r[9] * betas[3] * betas[3]);
+            double* a = A + i * 4;
+            a[0] = 2 * r[0] * b0 + r[1] * b1 + r[3] * b2 + r[6] * b3;
+            a[1] = r[1] * b0 + 2 * r[2] * b1 + r[4] * b2 + r[7] * b3;
+            a[2] = r[3] * b0 + r[4] * b1 + 2 * r[5] * b2 + r[8] * b3;
+            a[3] = r[6] * b0 + r[7] * b1 + r[8] * b2 + 2 * r[9] * b3;
+            b[i] = rho[i] - (r[0] * b0 * b0 + r[1] * b0 * b1 + r[2] * b1 * b1 + r[3] * b0 * b2 + r[4] * b1 * b2 +
+                             r[5] * b2 * b2 + r[6] * b0 * b3 + r[7] * b1 * b3 + r[8] * b2 * b3 + r[9] * b3 * b3);
         }
-        if (!householder_ls6(A, b, x, 4)) return;   // OpenCV's qr_solve gives up on a singular A
+        if (!householder_ls<6, 4>(A, b, x)) return;   // OpenCV's qr_solve gives up on a singular A
+#pragma unroll
         for (int i = 0; i < 4; ++i) betas[i] += x[i];
     }
+}
+
+// Orthogonal polar factor of a 3x3 matrix by scaled Newton iteration.  false if (near-)singular.
+SVO_HD bool polar_orthogonal3(const double* M, double* Q) {
+    double X[9], n2 = 0.0;
+    for (int i = 0; i < 9; ++i) n2 += M[i] * M[i];
+    if (!(n2 > 0.0)) return false;
+    const double sc = sqrt(3.0 / n2);
+    for (int i = 0; i < 9; ++i) X[i] = M[i] * sc;
+    for (int it = 0; it < 40; ++it) {
+        // cofactors: inv(X)^T = cof(X) / det(X)
+        double C[9];
+        C[0] = X[4] * X[8] - X[5] * X[7]; C[1] = X[5] * X[6] - X[3] * X[8]; C[2] = X[3] * X[7] - X[4] * X[6];
+        C[3] = X[2] * X[7] - X[1] * X[8]; C[4] = X[0] * X[8] - X[2] * X[6]; C[5] = X[1] * X[6] - X[0] * X[7];
+        C[6] = X[1] * X[5] - X[2] * X[4]; C[7] = X[2] * X[3] - X[0] * X[5]; C[8] = X[0] * X[4] - X[1] * X[3];
+        const double det = X[0] * C[0] + X[1] * C[1] + X[2] * C[2];
+        if (!(fabs(det) > 1e-9)) return false;   // X has unit-scale entries: rank deficient input
+        const double id = 1.0 / det;
+        double diff = 0.0;
+        for (int i = 0; i < 9; ++i) {
+            const double nx = 0.5 * (X[i] + C[i] * id);
+            diff += fabs(nx - X[i]);
+            X[i] = nx;
+        }
+        if (diff < 1e-15) break;
+    }
+    for (int i = 0; i < 9; ++i) Q[i] = X[i];
+    return true;
 }
 
 // compute_ccs / compute_pcs / solve_for_sign / estimate_R_and_t / reprojection_error of epnp.cpp
@@ -348,11 +411,15 @@ SVO_HD double epnp_R_and_t(const EpnpWork& w, const Intrinsics& K, const double*
     for (int i = 0; i < 5; ++i)
         for (int j = 0; j < 3; ++j)
             for (int k = 0; k < 3; ++k) abt[3 * j + k] += (pcs[3 * i + j] - pc0[j]) * (w.pws[3 * i + k] - pw0[k]);
-    double U[9], S[3], V[9];
-    svd3x3(abt, U, S, V);
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j)
-            R9[i * 3 + j] = U[i * 3] * V[j * 3] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
+    // R = U V^T of the SVD of ABt == the orthogonal polar factor of ABt (det = sign(det ABt)):
+    // Newton iteration X <- (X + X^-T) / 2, quadratically convergent; SVD only for a (near-)singular ABt.
+    if (!polar_orthogonal3(abt, R9)) {
+        double U[9], S[3], V[9];
+        svd3x3(abt, U, S, V);
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j)
+                R9[i * 3 + j] = U[i * 3] * V[j * 3] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
+    }
     const double det = R9[0] * R9[4] * R9[8] + R9[1] * R9[5] * R9[6] + R9[2] * R9[3] * R9[7] - R9[2] * R9[4] * R9[6] -
                        R9[1] * R9[3] * R9[8] - R9[0] * R9[5] * R9[7];
     if (det < 0) {

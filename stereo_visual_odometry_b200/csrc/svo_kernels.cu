@@ -437,7 +437,7 @@ __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom
 // The four legs L0->L1->R1->R0->L0 (vo.cpp:203-215) run in ONE loop body to keep the code I-cache sized.
 __global__ void __launch_bounds__(KLT_WARPS * 32)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc) {
-    __shared__ uint8_t patch[KLT_WARPS][SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     SeqState* s = d.state + seq;
@@ -500,7 +500,7 @@ void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int
 __global__ void __launch_bounds__(KLT_WARPS * 32)
 lk_single_kernel(LkPyramid I, LkPyramid J, LkConfig cfg, const float2* __restrict__ pts, int n,
                  float2* __restrict__ out, uint8_t* __restrict__ status) {
-    __shared__ uint8_t patch[KLT_WARPS][SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    __shared__ LkScratch patch[KLT_WARPS];
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int f = blockIdx.x * KLT_WARPS + wid;
     if (f >= n) return;
@@ -659,11 +659,11 @@ struct BlockInlierEval {
     __device__ void operator()(const Pose& P, double* acc, bool jac) const {
 #pragma unroll
         for (int i = 0; i < SVO_PNP_ACC; ++i) acc[i] = 0.0;
-        for (int i = threadIdx.x; i < n; i += FIN_THREADS) {
-            const int k = idx[i];
-            const float2 q = uv[k];
+#pragma unroll 2
+        for (int i = threadIdx.x; i < n; i += FIN_THREADS) {   // compact inlier arrays: coalesced, no indirection
+            const float2 q = uv[i];
             const float uvf[2] = {q.x, q.y};
-            pnp_accumulate(P, K, X3 + 3 * k, uvf, acc, jac);
+            pnp_accumulate(P, K, X3 + 3 * i, uvf, acc, jac);
         }
         const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -758,12 +758,19 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         }
         int tile_total;
         const int off = n_in + block_excl_scan<FIN_THREADS>(in ? 1 : 0, &tile_total, sm_i);
-        if (in) idx[off] = i;
+        if (in) {
+            idx[off] = i;
+            const float2 q = uv[i];
+            d.in_uv[fo + off] = q;
+            d.X3u[(fo + off) * 3] = X3[3 * i];
+            d.X3u[(fo + off) * 3 + 1] = X3[3 * i + 1];
+            d.X3u[(fo + off) * 3 + 2] = X3[3 * i + 2];
+        }
         n_in += tile_total;
     }
     __syncthreads();
     // ---- LM refit on all inliers (uniform control flow across the block)
-    BlockInlierEval ev{X3, uv, idx, n_in, pc.K, sm_acc};
+    BlockInlierEval ev{d.X3u + fo * 3, d.in_uv + fo, idx, n_in, pc.K, sm_acc};
     pnp_refine_lm(P, ev, 20);
     bool finite = true;
     for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
@@ -826,10 +833,16 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         write_result(d, seq, 1, SVO_REASON_OK, T);
     }
 }
-void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     dim3 grid((d.n_hyp + HYP_WARPS - 1) / HYP_WARPS, d.n_seq);
     pnp_hyp_kernel<<<grid, HYP_WARPS * 32, 0, st>>>(d, pc);
+}
+void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     pnp_final_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);
+}
+void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+    launch_pnp_hyp(d, pc, st);
+    launch_pnp_final(d, pc, st);
 }
 
 // ============================================================================

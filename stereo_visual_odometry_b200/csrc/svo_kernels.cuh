@@ -36,6 +36,8 @@ void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeCon
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, cudaStream_t st);
 void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_samples(const DevArrays& d, cudaStream_t st);   // standalone (select_kernel fuses it)
 
 // ---- stage-level helpers used by the stateless API ----

@@ -99,7 +99,7 @@ int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, in
     cfg.max_iters = max_iters;
     cfg.eps_sq = eps * eps;
     cfg.min_eig = min_eig;
-    uint8_t patch[SVO_LK_PATCH * SVO_LK_PATCH_PITCH];
+    static LkScratch patch;
     int total_iters = 0;
     for (int i = 0; i < n; ++i) {
         float ox, oy;
