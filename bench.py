@@ -237,12 +237,9 @@ def run_gpu(args, rank, world, local_rank):
     launches = L_.svo_launch_count(ctx) - launches0
     # trajectories: gather over NCCL (the only exchange of the path), inside the step budget
     traj = res_dev[k_timed0:k].clone()
-    if world > 1:
-        gathered = [torch.empty_like(traj) for _ in range(world)] if rank == 0 else None
-        dist.gather(traj, gathered, dst=0)
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    from stereo_visual_odometry_b200 import dist as svo_dist
+    gathered = svo_dist.gather_results(traj, dst=0)      # one NCCL gather: the path's only exchange
+    ms = svo_dist.max_over_ranks(ms, device="cuda")      # multi-GPU time = max over ranks
     clocks = sampler.stop()
     res = np.frombuffer(traj.cpu().numpy().tobytes(), dtype=np.dtype([
         ("i", np.int32, 8), ("R", np.float64, 9), ("t", np.float64, 3), ("T", np.float64, 16)]))
@@ -302,10 +299,7 @@ def run_gpu(args, rank, world, local_rank):
             check(L_.svo_process_frame(ctx2, Lp[j].data_ptr(), Rp[j].data_ptr(), W, ptr(T, C.c_double)))
             kk += 1
         dt = time.perf_counter() - t0
-        if world > 1:
-            tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dt = float(tt.item())
+        dt = svo_dist.max_over_ranks(dt, device="cuda")
         e2e = {"value": world * n_e2e / dt, "unit": "frames/s", "h2d_bytes_per_step": 2 * W * H * FRAMES_PER_STEP,
                "d2h_bytes_per_step": C.sizeof(FrameResult) * FRAMES_PER_STEP, "frames_timed": n_e2e,
                "timing": "host wall clock around synchronous svo_process_frame calls (each call syncs the stream)"}

@@ -1,0 +1,171 @@
+// C++ acceptance checks of the drop-in header include/vo.h (this repo) -- the known answers of the
+// reference's own assert-tests (src/main.cpp:50-264 of Alex7Li/stereo_visual_odometry), re-expressed
+// against the same class / function signatures.  Needs a CUDA device; run by tests/test_gpu_cpp.py.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+
+#include "vo.h"
+
+using namespace visual_odometry;
+
+#define REQUIRE(cond)                                                            \
+    do {                                                                         \
+        if (!(cond)) {                                                           \
+            std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond);        \
+            std::exit(1);                                                        \
+        }                                                                        \
+    } while (0)
+
+static cv::Mat blank(int rows, int cols) { return cv::Mat::zeros(rows, cols, CV_8UC1); }
+
+// filled triangle of value 120 with a one-pixel hole at its apex column (main.cpp:89-100)
+static void stamp(cv::Mat& img, int x, int y, int r) {
+    for (int i = -r; i <= r; ++i)
+        for (int j = 0; j <= r; ++j)
+            if (std::abs(i) <= r - std::abs(j)) img.at<unsigned char>(i + y, j + x) = 120;
+    img.at<unsigned char>(y, x) = 0;
+}
+
+static void bucket_policy() {
+    const int ages[5] = {6, 2, 3, 4, 5}, strengths[5] = {60, 20, 30, 40, 50};
+    Bucket none(0), three(3);
+    for (int i = 0; i < 5; ++i) {
+        none.add_feature(cv::Point2f(1, 1), ages[i], strengths[i]);
+        three.add_feature(cv::Point2f(1, 1), ages[i], strengths[i]);
+    }
+    REQUIRE(none.max_size == 0 && none.features.size() == 0);
+    REQUIRE(three.features.size() == 3);
+    REQUIRE(three.features.ages[0] == 6 && three.features.ages[1] == 4 && three.features.ages[2] == 5);
+    REQUIRE(three.features.strengths[0] == 60 && three.features.strengths[1] == 40 && three.features.strengths[2] == 50);
+    // the same policy through the GPU bucketing kernel (one bucket of capacity 3)
+    FeatureSet fs;
+    for (int i = 0; i < 5; ++i) {
+        fs.points.push_back(cv::Point2f(1, 1));
+        fs.ages.push_back(ages[i]);
+        fs.strengths.push_back(strengths[i]);
+    }
+    cv::Mat img = blank(10, 10);
+    fs.filterByBucketLocationInternal(img, 1, 1, 0, 3);
+    REQUIRE(fs.size() == 3 && fs.ages[0] == 6 && fs.ages[1] == 4 && fs.ages[2] == 5);
+}
+
+static void featureset_counts() {
+    FeatureSet fs;
+    REQUIRE(fs.size() == 0);
+    cv::Mat img = blank(300, 200);
+    for (int i = 0; i <= 10; ++i) stamp(img, 20, (i + 1) * 20, 8);
+    fs.appendFeaturesFromImage(img, 1);
+    for (int a : fs.ages) REQUIRE(a == 0);
+    for (int s : fs.strengths) REQUIRE(s <= 128);
+    REQUIRE(fs.size() == 11);
+    fs.filterByBucketLocationInternal(img, 1, 1, 0, 7);
+    REQUIRE(fs.size() == 7);
+}
+
+static void featureset_edges() {
+    FeatureSet fs;
+    cv::Mat img = blank(300, 300);
+    for (int i = 0; i < 15; ++i) { fs.points.push_back({299.f, 299.f}); fs.ages.push_back(0); fs.strengths.push_back(40); }
+    for (int i = 0; i < 10; ++i) { fs.points.push_back({299.f, 0.f}); fs.ages.push_back(0); fs.strengths.push_back(40); }
+    for (int i = 0; i < 5; ++i) { fs.points.push_back({0.f, 150.f}); fs.ages.push_back(0); fs.strengths.push_back(40); }
+    fs.filterByBucketLocationInternal(img, 2, 2, 0, 11);
+    FeatureSet copy = fs;
+    REQUIRE(fs.size() == 26);
+    fs.filterByBucketLocationInternal(img, 2, 1, 0, 11);
+    REQUIRE(fs.size() == 21);
+    copy.filterByBucketLocationInternal(img, 1, 2, 0, 11);
+    REQUIRE(copy.size() == 16);
+}
+
+static void unmoved_points() {
+    std::vector<cv::Point2f> a, b;
+    for (int i = 0; i < 35; ++i) {
+        a.push_back({float(i), float(i)});
+        b.push_back({float(i) + !(i % 5), float(i) + !(i % 7)});
+    }
+    std::vector<bool> ok = findClosePoints(a, b, .5f);
+    for (int i = 0; i < 35; ++i) REQUIRE(ok[i] == ((i % 5) && (i % 7)));
+    std::vector<cv::Point2f> kept = a;
+    deletePointsWithFailureStatus(kept, ok);
+    size_t expect = 0;
+    for (bool k : ok) expect += k;
+    REQUIRE(kept.size() == expect);
+}
+
+static void circular_matching() {
+    cv::Mat iL0 = blank(600, 600), iR0 = blank(600, 600), iL1 = blank(600, 600), iR1 = blank(600, 600);
+    for (int i = 0; i <= 10; ++i)
+        for (int j = 0; j <= 10; ++j) {
+            stamp(iL0, (j + 1) * 40, (i + 1) * 40, 8);
+            stamp(iL1, (j + 1) * 40 + 1, (i + 1) * 40, 8);
+            stamp(iR0, (j + 1) * 40, (i + 1) * 40 + 1, 8);
+            stamp(iR1, (j + 1) * 40 + 1, (i + 1) * 40 + 1, 8);
+        }
+    VisualOdometry vo;
+    std::vector<cv::Point2f> pl0, pr0, pl1, pr1;
+    vo.stereo_callback(iL0, iR0);
+    FeatureSet fs;
+    fs.appendFeaturesFromImage(iL0, FAST_THRESHOLD);
+    vo.circularMatching(iL1, iR1, pl0, pr0, pl1, pr1, fs);   // empty input must not crash
+    pl0.push_back(fs.points[0]);
+    FeatureSet one;
+    vo.circularMatching(iL1, iR1, pl0, pr0, pl1, pr1, one);  // single element must not crash
+    pl0 = fs.points;
+    vo.circularMatching(iL1, iR1, pl0, pr0, pl1, pr1, fs);
+    const size_t n = fs.points.size();
+    REQUIRE(pl0.size() == n && pl1.size() == n && pr0.size() == n && pr1.size() == n);
+    REQUIRE(n == 121);
+}
+
+static void camera_to_world() {
+    cv::Mat_<float> K = cv::Mat_<float>::eye(3, 3);
+    const int n = 27;
+    cv::Mat world(n, 1, CV_32FC3);
+    std::vector<cv::Point2f> cam(n);
+    int k = 0;
+    for (int i = -1; i <= 1; ++i)
+        for (int j = -1; j <= 1; ++j)
+            for (int z = 5; z <= 7; ++z) {
+                float* w = world.ptr<float>(k);
+                w[0] = -j; w[1] = i; w[2] = z;                       // 90 degrees about z, then +1 along z
+                cam[k] = cv::Point2f(float(i) / (z + 1), float(j) / (z + 1));
+                ++k;
+            }
+    cv::Mat rotation = cv::Mat::eye(3, 3, CV_64F), translation = cv::Mat::zeros(3, 1, CV_64F);
+    cv::Mat_<float> wtyped;
+    static_cast<cv::Mat&>(wtyped) = world;
+    auto res = cameraToWorld(K, cam, wtyped, rotation, translation);
+    REQUIRE(res.second);
+    REQUIRE(res.first.size().height == n);
+    REQUIRE(std::fabs(translation.at<double>(0)) < 1e-6 && std::fabs(translation.at<double>(1)) < 1e-6);
+    REQUIRE(std::fabs(translation.at<double>(2) - 1) < 1e-6);
+    const double expect[3][3] = {{0, 1, 0}, {-1, 0, 0}, {0, 0, 1}};
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) REQUIRE(std::fabs(rotation.at<double>(i, j) - expect[i][j]) < 1e-8);
+    cv::Mat T = getInverseTransform(rotation, translation);
+    REQUIRE(std::fabs(T.at<double>(2, 3) + 1) < 1e-6 && std::fabs(T.at<double>(3, 3) - 1) < 1e-12);
+}
+
+static void first_frame_contract() {
+    cv::Mat a = blank(200, 320), b = blank(200, 320);
+    StereoVO vo;   // upstream alias
+    auto r0 = vo.run(a, b);
+    REQUIRE(r0.first == false);
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) REQUIRE(r0.second(i, j) == (i == j ? 1.0 : 0.0));
+    auto r1 = vo.run(a, b);   // nothing to track: soft failure, last_transform (identity) returned
+    REQUIRE(r1.first == false && r1.second(0, 0) == 1.0 && r1.second(0, 3) == 0.0);
+}
+
+int main() {
+    std::printf("TEST BUCKET POLICY\n");        bucket_policy();
+    std::printf("TEST FEATURE SET\n");          featureset_counts();
+    std::printf("TEST FEATURE SET EDGE\n");     featureset_edges();
+    std::printf("TEST FIND UNMOVED POINTS\n");  unmoved_points();
+    std::printf("TEST CIRCULAR MATCHING\n");    circular_matching();
+    std::printf("TEST CAMERA TO WORLD\n");      camera_to_world();
+    std::printf("TEST FIRST FRAME\n");          first_frame_contract();
+    std::printf("ALL TESTS PASS\n");
+    return 0;
+}
