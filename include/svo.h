@@ -116,6 +116,18 @@ int svo_process_frame_batch(svo_ctx* ctx, const uint8_t* left, const uint8_t* ri
  * results_dev may be NULL. */
 int svo_process_frame_batch_dev(svo_ctx* ctx, const uint8_t* left_dev, const uint8_t* right_dev,
                                 int stride, long long seq_stride, svo_frame_result* results_dev);
+/* Streaming form of svo_process_frame[_batch] for a camera that delivers frames faster than one
+ * frame's latency: svo_submit_frame enqueues the H2D copy (left/right should be pinned host memory and
+ * stay valid until the frame is collected), the ingest kernels and the tracking chain and returns at
+ * once; svo_collect blocks until the OLDEST uncollected frame is done and returns its result exactly as
+ * svo_process_frame_batch would (frames are processed strictly in submission order, results are
+ * identical to the synchronous calls).  The ingest of frame f + 1 (its own stream) overlaps the
+ * tracking chain of frame f.  At most 8 frames may be pending (SVO_ERR_STATE beyond that). */
+int svo_submit_frame(svo_ctx* ctx, const uint8_t* left, const uint8_t* right, int stride);
+int svo_submit_frame_batch(svo_ctx* ctx, const uint8_t* left, const uint8_t* right, int stride,
+                           long long seq_stride);
+int svo_collect(svo_ctx* ctx, svo_frame_result* results /* [n_seq], may be NULL */);
+int svo_pending(svo_ctx* ctx);                  /* submitted, not yet collected */
 int svo_synchronize(svo_ctx* ctx);
 /* Last frame's result for sequence `seq` (host copy; synchronises). */
 int svo_get_result(svo_ctx* ctx, int seq, svo_frame_result* out);

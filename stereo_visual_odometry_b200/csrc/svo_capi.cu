@@ -19,6 +19,7 @@
 
 using namespace svo;
 
+#define SVO_RESULT_RING 8
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) {
     g_err = msg;
@@ -82,13 +83,20 @@ struct svo_ctx {
     BucketGeom bg;
     PipeConfig pc;
     DevArrays d;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // tracking chain (bucket .. PnP) and everything synchronous
+    cudaStream_t stream_in = nullptr;   // ingest of the next frame (H2D, pyramid, FAST) overlaps the chain
+    cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
+    cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // last reader of frame f's "previous" slot done
+    cudaEvent_t ev_done[SVO_RESULT_RING];                           // result of frame f in host_result ring
     std::vector<void*> allocs;
     uint8_t* stage_L = nullptr;
     uint8_t* stage_R = nullptr;
-    svo_frame_result* host_result = nullptr;   // pinned
-    long long frames = 0;
+    svo_frame_result* host_result = nullptr;   // pinned, [SVO_RESULT_RING][n_seq]
+    long long frames = 0;       // frames submitted
+    long long collected = 0;    // frames whose result was handed to the caller (host API only)
+    long long tracked = 0;      // frames whose result goes to the host ring (submitted through the host API)
     long long launches = 0;
+    int last_collected = 0;     // ring index of the result returned by the last svo_collect
     bool have_projection = false;
     int klt_blocks = 148;   // persistent KLT blocks per sequence
     // timers
@@ -183,6 +191,15 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     c->p = *p;
     CU(cudaSetDevice(p->device));
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->stream_in, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; ++i) {
+        CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < SVO_RESULT_RING; ++i) {
+        c->ev_done[i] = nullptr;
+        CU(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
+    }
     c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size);
     c->bg = make_bucket_geom(p->height, p->width, p->buckets_along_height, p->buckets_along_width,
                              p->bucket_start_row, p->age_threshold, p->fast_threshold);
@@ -211,10 +228,11 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     d.n_hyp = p->ransac_hypotheses;
     int cap = c->bg.nb;   // one feature per bucket at most
     if (cap_override > cap) cap = cap_override;
+    cap = (cap + 3) & ~3;   // word-aligned per-sequence status bytes
     d.cap = cap;
     const size_t S = (size_t)p->n_seq, C = S * (size_t)cap;
-    CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 4 * S));
-    CU(dev_alloc(c, &d.fastkeys, (size_t)4 * S * c->bg.nb));
+    CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 2 * SVO_PYR_SLOTS * S));
+    CU(dev_alloc(c, &d.fastkeys, (size_t)2 * SVO_PYR_SLOTS * S * c->bg.nb));
     CU(dev_alloc(c, &d.trackkeys, S * c->bg.nb));
     CU(dev_alloc(c, &d.state, S));
     CU(dev_alloc(c, &d.result, S));
@@ -242,7 +260,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     }
     CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S, false));
     CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S, false));
-    CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S));
+    CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S * SVO_RESULT_RING));
     // initial state: rotation = I, translation = 0, last_transform = I (vo.h:262-264)
     std::vector<SeqState> init(S);
     memset(init.data(), 0, sizeof(SeqState) * S);
@@ -294,8 +312,16 @@ extern "C" svo_ctx* svo_create(const svo_params* p) {
 extern "C" void svo_destroy(svo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->p.device);
+    if (c->stream_in) cudaStreamSynchronize(c->stream_in);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (void* q : c->allocs) cudaFree(q);
+    for (int i = 0; i < 4; ++i) {
+        if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
+        if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
+    }
+    for (int i = 0; i < SVO_RESULT_RING; ++i)
+        if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+    if (c->stream_in) cudaStreamDestroy(c->stream_in);
     if (c->host_result) cudaFreeHost(c->host_result);
     if (c->stream) {
         for (int i = 0; i < 7; ++i)
@@ -341,39 +367,57 @@ extern "C" int svo_get_stage_time(svo_ctx* c, int stage, double* ms_out, long lo
     return SVO_OK;
 }
 
-// The stream-ordered per-frame chain.  Images are device pointers.
+// One frame = ingest (stream_in) + tracking chain (stream).  The ingest of frame f + 1 depends on nothing the
+// chain of frame f produces (FAST runs on the NEW left image and is consumed one frame later), so the two
+// streams overlap; events order the ring reuse (slot f % 3 is last read by the KLT of frame f - 2 ... f - 1).
+// `left`/`right`: device planes, or nullptr when level 0 of the slot was already written (H2D in place).
+// to_host: also copy the result structs into the pinned host ring (slot tracked % SVO_RESULT_RING).
 static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
-                         svo_frame_result* results_dev) {
-    const bool first = c->frames == 0;
-    const int parity = (int)(c->frames & 1);
-    const bool tm = c->timers;
-    cudaStream_t st = c->stream;
-    if (tm) cudaEventRecord(c->ev[0], st);
-    launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, first ? 1 : 0, parity, st);
-    const int n_ingest = 1 + (c->pg.nlevels - 1) + 1;
+                         svo_frame_result* results_dev, bool to_host) {
+    const long long f = c->frames;
+    const bool first = f == 0;
+    const int cur = (int)(f % SVO_PYR_SLOTS), prev = (int)((f + SVO_PYR_SLOTS - 1) % SVO_PYR_SLOTS);
+    const bool tm = c->timers;   // timed mode: everything serial on one stream
+    cudaStream_t sP = c->stream, sI = tm ? c->stream : c->stream_in;
+    if (tm) cudaEventRecord(c->ev[0], sP);
+    const int n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
     c->launches += n_ingest;
-    if (tm) cudaEventRecord(c->ev[1], st);
+    if (!tm) {
+        CU(cudaEventRecord(c->ev_in[f & 3], sI));
+        CU(cudaStreamWaitEvent(sP, c->ev_in[f & 3], 0));
+    }
+    if (tm) cudaEventRecord(c->ev[1], sP);
     if (first) {
-        launch_first_frame(c->d, st);
+        launch_first_frame(c->d, sP);
         c->launches += 1;
     } else {
-        launch_bucket_merge(c->d, c->bg, c->pc, parity ^ 1, st);   // FAST winners of the PREVIOUS left image
-        if (tm) cudaEventRecord(c->ev[2], st);
-        launch_klt(c->d, c->pg, c->pc, c->klt_blocks, st);
-        if (tm) cudaEventRecord(c->ev[3], st);
-        launch_select(c->d, c->pc, st);
-        if (tm) cudaEventRecord(c->ev[4], st);
-        launch_pnp_hyp(c->d, c->pc, st);
-        if (tm) cudaEventRecord(c->ev[5], st);
-        launch_pnp_final(c->d, c->pc, st);
-        if (tm) cudaEventRecord(c->ev[6], st);
+        launch_bucket_merge(c->d, c->bg, c->pc, prev, sP);   // FAST winners of the PREVIOUS left image
+        if (tm) cudaEventRecord(c->ev[2], sP);
+        launch_klt(c->d, c->pg, c->pc, c->klt_blocks, prev, cur, sP);
+        if (tm) cudaEventRecord(c->ev[3], sP);
+        launch_select(c->d, c->pg, c->pc, prev, cur, sP);
+        if (tm) cudaEventRecord(c->ev[4], sP);
+    }
+    CU(cudaEventRecord(c->ev_sel[f & 3], sP));
+    if (!first) {
+        launch_pnp_hyp(c->d, c->pc, sP);
+        if (tm) cudaEventRecord(c->ev[5], sP);
+        launch_pnp_final(c->d, c->pc, sP);
+        if (tm) cudaEventRecord(c->ev[6], sP);
         c->launches += 5;
     }
     if (results_dev)
-        CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, sP));
+    if (to_host) {
+        const int r = (int)(c->tracked % SVO_RESULT_RING);
+        CU(cudaMemcpyAsync(c->host_result + (size_t)r * c->d.n_seq, c->d.result, sizeof(svo_frame_result) * c->d.n_seq,
+                           cudaMemcpyDeviceToHost, sP));
+        CU(cudaEventRecord(c->ev_done[r], sP));
+        c->tracked += 1;
+    }
     CU(cudaGetLastError());
     if (tm) {
-        CU(cudaStreamSynchronize(st));
+        CU(cudaStreamSynchronize(sP));
         const int nst = first ? 1 : 6;
         const int nl[6] = {n_ingest, 1, 1, 1, 1, 1};
         for (int i = 0; i < nst; ++i) {
@@ -387,40 +431,89 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     return SVO_OK;
 }
 
+// the ingest stream may not start writing slot f % 3 / key buffer f % 3 before frame f - 2 is done reading
+static int wait_ring(svo_ctx* c) {
+    const long long f = c->frames;
+    if (!c->timers && f >= 2) CU(cudaStreamWaitEvent(c->stream_in, c->ev_sel[(f - 2) & 3], 0));
+    return SVO_OK;
+}
+
 extern "C" int svo_process_frame_batch_dev(svo_ctx* c, const uint8_t* left_dev, const uint8_t* right_dev, int stride,
                                            long long seq_stride, svo_frame_result* results_dev) {
     if (!c || !left_dev || !right_dev) return fail(SVO_ERR_INVALID, "NULL argument");
     if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
     if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
     CU(cudaSetDevice(c->p.device));
-    return enqueue_frame(c, left_dev, right_dev, stride, seq_stride, results_dev);
+    int rc = wait_ring(c);
+    if (rc != SVO_OK) return rc;
+    return enqueue_frame(c, left_dev, right_dev, stride, seq_stride, results_dev, false);
+}
+
+extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride,
+                                      long long seq_stride) {
+    if (!c || !left || !right) return fail(SVO_ERR_INVALID, "NULL argument");
+    if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
+    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    if (c->tracked - c->collected >= SVO_RESULT_RING)
+        return fail(SVO_ERR_STATE, "result ring full: call svo_collect before submitting more frames");
+    CU(cudaSetDevice(c->p.device));
+    int rc = wait_ring(c);
+    if (rc != SVO_OK) return rc;
+    const int S = c->d.n_seq, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
+    const long long plane = (long long)P0 * H;
+    cudaStream_t sI = c->timers ? c->stream : c->stream_in;
+    if (S == 1) {
+        // straight into level 0 of the frame's pyramid slot: no staging copy
+        const int cur = (int)(c->frames % SVO_PYR_SLOTS);
+        uint8_t* l0 = c->d.pyr + c->pg.base(0, cur, 0) + c->pg.off[0];
+        uint8_t* r0 = c->d.pyr + c->pg.base(0, cur, 1) + c->pg.off[0];
+        CU(cudaMemcpy2DAsync(l0, P0, left, stride, W, H, cudaMemcpyHostToDevice, sI));
+        CU(cudaMemcpy2DAsync(r0, P0, right, stride, W, H, cudaMemcpyHostToDevice, sI));
+        return enqueue_frame(c, nullptr, nullptr, P0, plane, nullptr, true);
+    }
+    // the staging planes are read by the ingest of the previous frame: same stream, so ordered
+    if (seq_stride == (long long)stride * H) {
+        CU(cudaMemcpy2DAsync(c->stage_L, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sI));
+        CU(cudaMemcpy2DAsync(c->stage_R, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sI));
+    } else {
+        for (int s = 0; s < S; ++s) {
+            CU(cudaMemcpy2DAsync(c->stage_L + s * plane, P0, left + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sI));
+            CU(cudaMemcpy2DAsync(c->stage_R + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sI));
+        }
+    }
+    return enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr, true);
+}
+
+extern "C" int svo_submit_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    if (c->d.n_seq != 1) return fail(SVO_ERR_INVALID, "svo_submit_frame needs a context with n_seq == 1");
+    return svo_submit_frame_batch(c, left, right, stride, 0);
+}
+
+extern "C" int svo_pending(svo_ctx* c) { return c ? (int)(c->tracked - c->collected) : SVO_ERR_INVALID; }
+
+extern "C" int svo_collect(svo_ctx* c, svo_frame_result* results) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    if (c->tracked == c->collected) return fail(SVO_ERR_STATE, "no submitted frame is pending");
+    CU(cudaSetDevice(c->p.device));
+    const int r = (int)(c->collected % SVO_RESULT_RING), S = c->d.n_seq;
+    CU(cudaEventSynchronize(c->ev_done[r]));
+    const svo_frame_result* hr = c->host_result + (size_t)r * S;
+    int ok = 0;
+    for (int s = 0; s < S; ++s) ok += hr[s].success ? 1 : 0;
+    if (results) memcpy(results, hr, sizeof(svo_frame_result) * S);
+    c->last_collected = r;
+    c->collected += 1;
+    return ok;
 }
 
 extern "C" int svo_process_frame_batch(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride,
                                        long long seq_stride, svo_frame_result* results) {
-    if (!c || !left || !right) return fail(SVO_ERR_INVALID, "NULL argument");
-    if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
-    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
-    CU(cudaSetDevice(c->p.device));
-    const int S = c->d.n_seq, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
-    const long long plane = (long long)P0 * H;
-    if (S == 1 || seq_stride == (long long)stride * H) {
-        CU(cudaMemcpy2DAsync(c->stage_L, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpy2DAsync(c->stage_R, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, c->stream));
-    } else {
-        for (int s = 0; s < S; ++s) {
-            CU(cudaMemcpy2DAsync(c->stage_L + s * plane, P0, left + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, c->stream));
-            CU(cudaMemcpy2DAsync(c->stage_R + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, c->stream));
-        }
-    }
-    int rc = enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr);
-    if (rc != SVO_OK) return rc;
-    CU(cudaMemcpyAsync(c->host_result, c->d.result, sizeof(svo_frame_result) * S, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    int ok = 0;
-    for (int s = 0; s < S; ++s) ok += c->host_result[s].success ? 1 : 0;
-    if (results) memcpy(results, c->host_result, sizeof(svo_frame_result) * S);
-    return ok;
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    if (c->tracked != c->collected) return fail(SVO_ERR_STATE, "submitted frames are pending: svo_collect them first");
+    int rc = svo_submit_frame_batch(c, left, right, stride, seq_stride);
+    if (rc < 0) return rc;
+    return svo_collect(c, results);
 }
 
 extern "C" int svo_process_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, double T_out[16]) {
@@ -428,13 +521,15 @@ extern "C" int svo_process_frame(svo_ctx* c, const uint8_t* left, const uint8_t*
     if (c->d.n_seq != 1) return fail(SVO_ERR_INVALID, "svo_process_frame needs a context with n_seq == 1");
     int rc = svo_process_frame_batch(c, left, right, stride, 0, nullptr);
     if (rc < 0) return rc;
-    if (T_out) memcpy(T_out, c->host_result[0].transform, sizeof(double) * 16);
-    return c->host_result[0].success ? 1 : 0;
+    const svo_frame_result* hr = c->host_result + (size_t)c->last_collected * c->d.n_seq;
+    if (T_out) memcpy(T_out, hr->transform, sizeof(double) * 16);
+    return hr->success ? 1 : 0;
 }
 
 extern "C" int svo_synchronize(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     CU(cudaSetDevice(c->p.device));
+    CU(cudaStreamSynchronize(c->stream_in));
     CU(cudaStreamSynchronize(c->stream));
     return SVO_OK;
 }
@@ -442,9 +537,8 @@ extern "C" int svo_synchronize(svo_ctx* c) {
 extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
     if (!c || !out || seq < 0 || seq >= c->d.n_seq) return fail(SVO_ERR_INVALID, "bad argument");
     CU(cudaSetDevice(c->p.device));
-    CU(cudaMemcpyAsync(c->host_result + seq, c->d.result + seq, sizeof(svo_frame_result), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    *out = c->host_result[seq];
+    CU(cudaMemcpy(out, c->d.result + seq, sizeof(svo_frame_result), cudaMemcpyDeviceToHost));
     return SVO_OK;
 }
 
@@ -707,11 +801,11 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     };
     int rc = up(L0, R0);
     if (rc != SVO_OK) return rc;
-    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 1, 0, st);
+    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 0, st);
     launch_first_frame(d, st);
     rc = up(L1, R1);
     if (rc != SVO_OK) return rc;
-    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 0, 1, st);
+    launch_ingest(d, c->pg, c->bg, c->pc, c->stage_L, c->stage_R, P0, plane, 1, st);
     SeqState s;
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -731,8 +825,8 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
         CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
     }
     CU(cudaMemsetAsync(d.klt_next, 0, sizeof(int), st));
-    launch_klt(d, c->pg, c->pc, c->klt_blocks, st);
-    launch_select(d, c->pc, st);
+    launch_klt(d, c->pg, c->pc, c->klt_blocks, 0, 1, st);
+    launch_select(d, c->pg, c->pc, 0, 1, st);
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());

@@ -2,8 +2,8 @@
 // and the C-ABI host layer (svo_capi.cu).
 //
 // HBM layout (one context = n_seq independent sequences, all arrays SoA per sequence):
-//   pyramids  [seq][slot 0/1][cam L/R][level 0..3]  u8, row pitch 128-B aligned
-//   fastkeys  [parity 0/1][A|B][seq][bucket]        u64 per-bucket FAST winners of one left image
+//   pyramids  [seq][slot 0..2][cam L/R][level 0..3] u8, row pitch 128-B aligned; frame f lives in slot f % 3
+//   fastkeys  [frame % 3][A|B][seq][bucket]         u64 per-bucket FAST winners of one left image
 //   trackkeys [seq][bucket]                         u64 scratch for the tracked-feature winners
 //   feature set / bucketed list / LK legs / matched set / 3-D points: [seq][cap]
 //   hypotheses [seq][H] pose (12 f64) + inlier count
@@ -16,6 +16,10 @@
 
 namespace svo {
 
+// Ring of pyramid slots / FAST key buffers: frame f uses slot f % 3, so the ingest of frame f + 1 (its own
+// stream) never touches what the tracking chain of frame f reads (slots f % 3 and (f - 1) % 3).
+#define SVO_PYR_SLOTS 3
+
 struct PyrGeom {
     int nlevels;
     int w[SVO_MAX_LEVELS], h[SVO_MAX_LEVELS], pitch[SVO_MAX_LEVELS];
@@ -23,7 +27,7 @@ struct PyrGeom {
     long long image_bytes;           // bytes of one image pyramid (all levels)
     // pyramid of (seq, slot, cam)
     __host__ __device__ long long base(int seq, int slot, int cam) const {
-        return ((long long)(seq * 2 + slot) * 2 + cam) * image_bytes;
+        return ((long long)(seq * SVO_PYR_SLOTS + slot) * 2 + cam) * image_bytes;
     }
 };
 
@@ -37,7 +41,7 @@ struct BucketGeom {
 };
 
 struct SeqState {
-    int slot;            // pyramid slot holding lastLeftPyramid / lastRightPyramid (vo.h:257-258)
+    int slot_unused_;    // (pyramid slots are a host-known ring: frame f -> slot f % 3)
     int n_feat;          // currentVOFeatures.size()
     int n_bucketed;
     int n_matched;
@@ -55,7 +59,7 @@ struct SeqState {
 // All device pointers of a context, passed by value to the kernels.
 struct DevArrays {
     uint8_t* pyr;                     // pyramids
-    unsigned long long* fastkeys;     // [2][2][n_seq][nb]
+    unsigned long long* fastkeys;     // [3][2][n_seq][nb]
     unsigned long long* trackkeys;    // [n_seq][nb]
     SeqState* state;                  // [n_seq]
     svo_frame_result* result;         // [n_seq]

@@ -242,6 +242,14 @@ SVO_HD void jacobi12_parallel(EpnpWork& w, int lane) {
     Red::sync();
     constexpr int NB = (21 + LANES - 1) / LANES;   // blocks per lane
     constexpr int NV = (72 + LANES - 1) / LANES;   // Vt items per lane
+    // block l -> (ki <= kj) in row-major upper-triangular order, decoded once (packed ki | kj << 4)
+    unsigned char blk[NB];
+#pragma unroll
+    for (int bi = 0; bi < NB; ++bi) {
+        int ki = 0, rem = lane + bi * LANES;
+        while (ki < 5 && rem >= 6 - ki) { rem -= 6 - ki; ++ki; }
+        blk[bi] = (unsigned char)(ki | ((ki + rem) << 4));
+    }
     for (int sweep = 0; sweep < 30; ++sweep) {
         double off = 0.0, diag = 0.0;
         for (int i = lane; i < 144; i += LANES) {
@@ -265,10 +273,7 @@ SVO_HD void jacobi12_parallel(EpnpWork& w, int lane) {
             for (int bi = 0; bi < NB; ++bi) {
                 const int l = lane + bi * LANES;
                 if (l < 21) {
-                    // l -> (ki <= kj) in row-major upper-triangular order
-                    int ki = 0, rem = l;
-                    while (rem >= 6 - ki) { rem -= 6 - ki; ++ki; }
-                    const int kj = ki + rem;
+                    const int ki = blk[bi] & 15, kj = blk[bi] >> 4;
                     const int pi = pq[2 * ki], qi = pq[2 * ki + 1], pj = pq[2 * kj], qj = pq[2 * kj + 1];
                     const double ci = w.cs[2 * ki], si = w.cs[2 * ki + 1], cj = w.cs[2 * kj], sj = w.cs[2 * kj + 1];
                     const double a = w.A[pi * 12 + pj], b = w.A[pi * 12 + qj], c = w.A[qi * 12 + pj], d = w.A[qi * 12 + qj];

@@ -235,16 +235,12 @@ void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, in
     pyrdown_kernel<<<grid, 256, 0, st>>>(src, src_stride, sw, sh, spitch, dst, dst_stride, dw, dh, dpitch);
 }
 
-// ---- context ingest: slot chosen on the device from SeqState
-__device__ __forceinline__ int ingest_slot(const SeqState* s, int first_frame) {
-    return first_frame ? 0 : (s->slot ^ 1);
-}
+// ---- context ingest into pyramid slot `slot` (host-known ring, frame f -> f % 3)
 // z = seq * 2 + cam
 __global__ void __launch_bounds__(256)
 ctx_copy_level0_kernel(DevArrays d, PyrGeom pg, const uint8_t* __restrict__ left,
-                       const uint8_t* __restrict__ right, int stride, long long seq_stride, int first_frame) {
+                       const uint8_t* __restrict__ right, int stride, long long seq_stride, int slot) {
     const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
-    const int slot = ingest_slot(d.state + seq, first_frame);
     const uint8_t* src = (cam ? right : left) + (long long)seq * seq_stride;
     uint8_t* dst = d.pyr + pg.base(seq, slot, cam) + pg.off[0];
     const int y = blockIdx.y;
@@ -262,9 +258,8 @@ ctx_copy_level0_kernel(DevArrays d, PyrGeom pg, const uint8_t* __restrict__ left
     }
 }
 __global__ void __launch_bounds__(256)
-ctx_pyrdown_kernel(DevArrays d, PyrGeom pg, int level /* destination level >= 1 */, int first_frame) {
+ctx_pyrdown_kernel(DevArrays d, PyrGeom pg, int level /* destination level >= 1 */, int slot) {
     const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
-    const int slot = ingest_slot(d.state + seq, first_frame);
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= pg.w[level] || y >= pg.h[level]) return;
     uint8_t* base = d.pyr + pg.base(seq, slot, cam);
@@ -274,21 +269,26 @@ ctx_pyrdown_kernel(DevArrays d, PyrGeom pg, int level /* destination level >= 1 
         (uint8_t)pyrdown_pixel(g, pg.w[level - 1], pg.h[level - 1], x, y);
 }
 
-void launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
-                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int first_frame,
-                   int parity, cudaStream_t st) {
-    {
+int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                  const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
+                  cudaStream_t st) {
+    int launches = 0;
+    if (left) {   // images outside the context: copy into level 0 of the slot
         dim3 grid(1, pg.h[0], d.n_seq * 2);
-        ctx_copy_level0_kernel<<<grid, 256, 0, st>>>(d, pg, left, right, stride, seq_stride, first_frame);
+        ctx_copy_level0_kernel<<<grid, 256, 0, st>>>(d, pg, left, right, stride, seq_stride, slot);
+        ++launches;
     }
     for (int l = 1; l < pg.nlevels; ++l) {
         dim3 grid((pg.w[l] + 31) / 32, (pg.h[l] + 7) / 8, d.n_seq * 2);
-        ctx_pyrdown_kernel<<<grid, 256, 0, st>>>(d, pg, l, first_frame);
+        ctx_pyrdown_kernel<<<grid, 256, 0, st>>>(d, pg, l, slot);
+        ++launches;
     }
-    unsigned long long* keysA = d.fastkeys + ((long long)(parity * 2 + 0) * d.n_seq) * bg.nb;
-    unsigned long long* keysB = d.fastkeys + ((long long)(parity * 2 + 1) * d.n_seq) * bg.nb;
-    launch_fast(left, seq_stride, pc.width, pc.height, stride, d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, keysA,
-                keysB, bg, st);
+    unsigned long long* keysA = d.fastkeys + ((long long)(slot * 2 + 0) * d.n_seq) * bg.nb;
+    unsigned long long* keysB = d.fastkeys + ((long long)(slot * 2 + 1) * d.n_seq) * bg.nb;
+    // FAST on the left level 0 of the slot (the pitch-aligned copy)
+    launch_fast(d.pyr + pg.base(0, slot, 0) + pg.off[0], pg.base(1, 0, 0) - pg.base(0, 0, 0), pc.width, pc.height,
+                pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, keysA, keysB, bg, st);
+    return launches + 1;
 }
 
 // ============================================================================
@@ -297,7 +297,6 @@ __global__ void first_frame_kernel(DevArrays d) {
     const int seq = blockIdx.x * blockDim.x + threadIdx.x;
     if (seq >= d.n_seq) return;
     SeqState* s = d.state + seq;
-    s->slot = 0;
     s->frame_id = 1;
     svo_frame_result* r = d.result + seq;
     r->success = 0;
@@ -318,15 +317,15 @@ void launch_first_frame(const DevArrays& d, cudaStream_t st) {
 // block scan over the (tile, warp) popcounts.
 constexpr int BM_TILES = 16;   // nb <= 16384 (checked in svo_create)
 __global__ void __launch_bounds__(1024)
-bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
+bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
     __shared__ int sm[33];
     __shared__ int wcount[BM_TILES * 32];
     const int seq = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     SeqState* s = d.state + seq;
     const long long fo = (long long)seq * d.cap;
     unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
-    unsigned long long* keyA = d.fastkeys + ((long long)(parity * 2 + 0) * d.n_seq + seq) * bg.nb;
-    unsigned long long* keyB = d.fastkeys + ((long long)(parity * 2 + 1) * d.n_seq + seq) * bg.nb;
+    unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
+    unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
     const int n = s->n_feat;
 
     for (int i = tid; i < n; i += 1024) {
@@ -413,9 +412,9 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int parity) {
         d.klt_next[seq] = 0;
     }
 }
-void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf,
                          cudaStream_t st) {
-    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, parity);
+    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, keybuf);
 }
 
 // ============================================================================
@@ -436,16 +435,15 @@ __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom
 // finish a quickly converging feature immediately start another one (the per-feature cost varies 10x).
 // The four legs L0->L1->R1->R0->L0 (vo.cpp:203-215) run in ONE loop body to keep the code I-cache sized.
 __global__ void __launch_bounds__(KLT_WARPS * 32)
-klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc) {
+klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     SeqState* s = d.state + seq;
     const int n = s->n_bucketed;
-    const int slot = s->slot;
     // pyramid k: 0 = L0, 1 = L1, 2 = R1, 3 = R0 ; leg l tracks from pyramid l to pyramid (l + 1) & 3
-    const long long base[4] = {pg.base(seq, slot, 0), pg.base(seq, slot ^ 1, 0), pg.base(seq, slot ^ 1, 1),
-                               pg.base(seq, slot, 1)};
+    const long long base[4] = {pg.base(seq, slot_prev, 0), pg.base(seq, slot_cur, 0), pg.base(seq, slot_cur, 1),
+                               pg.base(seq, slot_prev, 1)};
     int* counter = d.klt_next + seq;
     for (;;) {
         int f = 0;
@@ -492,9 +490,10 @@ klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc) {
         }
     }
 }
-void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, cudaStream_t st) {
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
+                int slot_cur, cudaStream_t st) {
     dim3 grid(blocks_per_seq, d.n_seq);
-    klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc);
+    klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
 }
 
 __global__ void __launch_bounds__(KLT_WARPS * 32)
@@ -520,14 +519,53 @@ void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, cons
 }
 
 // ============================================================================
-// select: circular check + status AND + bounds, stable compaction, ages++, triangulation
-// one full warp: RNG outputs modulo n in parallel, then lane 0 replays getSubset()
+// select: keep mask -> stable compaction, ages++, triangulation, RANSAC sample indices
+//
+// OpenCV's getSubset() redraws on duplicates, so hypothesis h starts at RNG position 5h + (redraws so far).
+// Lane l replays hypotheses 4l..4l+3 sequentially from a speculated start position; the per-lane draw totals
+// are prefix-summed and the replay repeats until the start positions are stable (one redraw event costs one
+// extra round; with thousands of points there is usually none).  Result == the sequential replay.
+__device__ __forceinline__ int lane_replay_samples(const int* __restrict__ mods, int pos, int h0, int h1,
+                                                   int* __restrict__ samples) {
+    for (int h = h0; h < h1; ++h) {
+        int idx[5] = {-1, -1, -1, -1, -1};
+        bool ok = true;
+        for (int i = 0; i < 5 && ok; ++i) {
+            for (;;) {
+                if (pos >= SVO_RNG_TABLE) { ok = false; break; }
+                const int v = mods[pos++];
+                bool dup = false;
+                for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
+                if (!dup) { idx[i] = v; break; }
+            }
+        }
+        if (samples)
+            for (int i = 0; i < 5; ++i) samples[h * 5 + i] = ok ? idx[i] : -1;
+    }
+    return pos;
+}
 __device__ __forceinline__ void warp_build_samples(const unsigned* __restrict__ raw, int n, int n_hyp,
                                                    int* __restrict__ samples, int* mods /* smem [SVO_RNG_TABLE] */) {
     const int lane = threadIdx.x & 31;
     for (int i = lane; i < SVO_RNG_TABLE; i += 32) mods[i] = (int)(raw[i] % (unsigned)n);
     __syncwarp();
-    if (lane == 0) ransac_build_samples([&](int pos) { return mods[pos]; }, n_hyp, samples);
+    const int per = (n_hyp + 31) / 32;
+    const int h0 = min(n_hyp, lane * per), h1 = min(n_hyp, h0 + per);
+    int start = 5 * h0;
+    for (int round = 0; round <= 32; ++round) {
+        const int used = lane_replay_samples(mods, start, h0, h1, nullptr) - start;
+        int incl = used;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int ns = incl - used;
+        const bool changed = ns != start;
+        start = ns;
+        if (!__any_sync(0xffffffffu, changed)) break;
+    }
+    lane_replay_samples(mods, start, h0, h1, samples);
 }
 __global__ void pnp_samples_kernel(DevArrays d) {
     __shared__ int mods[SVO_RNG_TABLE];
@@ -537,50 +575,81 @@ __global__ void pnp_samples_kernel(DevArrays d) {
 }
 void launch_pnp_samples(const DevArrays& d, cudaStream_t st) { pnp_samples_kernel<<<d.n_seq, 32, 0, st>>>(d); }
 
-__global__ void __launch_bounds__(1024) select_kernel(DevArrays d, PipeConfig pc) {
-    __shared__ int sm[33];
+// grid (tiles + 1, n_seq): block b < tiles compacts features [256 b, 256 b + 256) -- its output offset is the
+// number of kept features before the tile, counted redundantly from the status bytes (<= 14 KB, L2 hits) so no
+// inter-block dependency exists; the last block only counts, builds the RANSAC samples and updates the state.
+constexpr int SEL_T = 256;
+__global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev,
+                                                       int slot_cur) {
+    __shared__ int sm[SEL_T / 32 + 1];
     __shared__ int mods[SVO_RNG_TABLE];
-    const int seq = blockIdx.x, tid = threadIdx.x;
+    const int seq = blockIdx.y, tid = threadIdx.x;
     SeqState* s = d.state + seq;
     const long long fo = (long long)seq * d.cap;
     const int n = s->n_bucketed;
-    int base = 0;
-    for (int t0 = 0; t0 < n; t0 += 1024) {   // coalesced tiles, stable order
-        const int i = t0 + tid;
-        const bool ok = i < n && (d.lk_status[fo + i] & 16) != 0;
-        int tile_total;
-        const int off = base + block_excl_scan<1024>(ok ? 1 : 0, &tile_total, sm);
-        if (ok) {
-            const float2 p0 = d.bk_xy[fo + i];
-            const int age = d.bk_age[fo + i] + pc.age_increment, str = d.bk_str[fo + i];   // ages++ (vo.cpp:70-72)
-            d.m_L0[fo + off] = p0;
-            d.m_L1[fo + off] = d.lk_L1[fo + i];
-            d.m_R1[fo + off] = d.lk_R1[fo + i];
-            d.m_age[fo + off] = age;
-            d.m_str[fo + off] = str;
-            // currentVOFeatures after matchingFeatures: t0 coordinates (vo.cpp:360)
-            d.fs_xy[fo + off] = p0;
-            d.fs_age[fo + off] = age;
-            d.fs_str[fo + off] = str;
-            const float2 r0 = d.lk_R0[fo + i];
-            d.m_R0[fo + off] = r0;
-            triangulate_dlt(pc.Pl, pc.Pr, p0.x, p0.y, r0.x, r0.y, d.X3 + (fo + off) * 3);   // vo.cpp:89-94
-        }
-        base += tile_total;
+    const bool tail = blockIdx.x == gridDim.x - 1;
+    const int t0 = tail ? n : blockIdx.x * SEL_T;
+    if (n == 0) {
+        // circularMatching returns before lastLeft/RightPyramid are replaced (vo.cpp:179-181): keep the old
+        // pyramids as "previous" by copying them into this frame's ring slot
+        const uint4* src = reinterpret_cast<const uint4*>(d.pyr + pg.base(seq, slot_prev, 0));
+        uint4* dst = reinterpret_cast<uint4*>(d.pyr + pg.base(seq, slot_cur, 0));
+        const long long nv = pg.image_bytes * 2 / 16;
+        if (slot_prev != slot_cur)
+            for (long long i = (long long)blockIdx.x * SEL_T + tid; i < nv; i += (long long)gridDim.x * SEL_T) dst[i] = src[i];
     }
-    const int total = base;
-    // RANSAC sample indices in OpenCV's order (depends only on the survivor count)
-    if (tid < 32 && total >= 5) warp_build_samples(d.rng_raw, total, d.n_hyp, d.hyp_samples + (long long)seq * d.n_hyp * 5, mods);
-    if (tid == 0) {
-        s->n_matched = total;
-        s->n_feat = total;
-        s->n_inliers = 0;
-        s->pnp_ok = 0;
-        if (n > 0) s->slot ^= 1;   // lastLeft/RightPyramid = pyramid(l1/r1) (vo.cpp:231-232); not when n == 0 (179-181)
+    if (!tail && t0 >= n) return;
+    // kept features before the tile
+    const uint8_t* stt = d.lk_status + fo;
+    int c = 0;
+    if ((fo & 3) == 0) {
+        const unsigned* w = reinterpret_cast<const unsigned*>(stt);
+        const int nw = t0 >> 2;
+        for (int i = tid; i < nw; i += SEL_T) c += __popc(w[i] & 0x10101010u);
+        for (int i = (nw << 2) + tid; i < t0; i += SEL_T) c += (stt[i] >> 4) & 1;
+    } else {
+        for (int i = tid; i < t0; i += SEL_T) c += (stt[i] >> 4) & 1;
+    }
+    const int i = t0 + tid;
+    const bool ok = !tail && i < n && (stt[i] & 16) != 0;
+    // one scan gives both: low 16 bits = own flag, high bits = the count (<= 2^15 features)
+    int packed_total;
+    const int packed = block_excl_scan<SEL_T>((ok ? 1 : 0) | (c << 16), &packed_total, sm);
+    const int base = packed_total >> 16;
+    const int off = base + (packed & 0xFFFF);
+    if (ok) {
+        const float2 p0 = d.bk_xy[fo + i];
+        const int age = d.bk_age[fo + i] + pc.age_increment, str = d.bk_str[fo + i];   // ages++ (vo.cpp:70-72)
+        d.m_L0[fo + off] = p0;
+        d.m_L1[fo + off] = d.lk_L1[fo + i];
+        d.m_R1[fo + off] = d.lk_R1[fo + i];
+        d.m_age[fo + off] = age;
+        d.m_str[fo + off] = str;
+        // currentVOFeatures after matchingFeatures: t0 coordinates (vo.cpp:360)
+        d.fs_xy[fo + off] = p0;
+        d.fs_age[fo + off] = age;
+        d.fs_str[fo + off] = str;
+        const float2 r0 = d.lk_R0[fo + i];
+        d.m_R0[fo + off] = r0;
+        triangulate_dlt(pc.Pl, pc.Pr, p0.x, p0.y, r0.x, r0.y, d.X3 + (fo + off) * 3);   // vo.cpp:89-94
+    }
+    if (tail) {
+        const int total = base;
+        // RANSAC sample indices in OpenCV's order (they depend only on the survivor count)
+        if (tid < 32 && total >= 5)
+            warp_build_samples(d.rng_raw, total, d.n_hyp, d.hyp_samples + (long long)seq * d.n_hyp * 5, mods);
+        if (tid == 0) {
+            s->n_matched = total;
+            s->n_feat = total;
+            s->n_inliers = 0;
+            s->pnp_ok = 0;
+        }
     }
 }
-void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
-    select_kernel<<<d.n_seq, 1024, 0, st>>>(d, pc);
+void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
+                   cudaStream_t st) {
+    dim3 grid((d.cap + SEL_T - 1) / SEL_T + 1, d.n_seq);
+    select_kernel<<<grid, SEL_T, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
 }
 
 // ============================================================================

@@ -22,19 +22,22 @@ void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pit
 void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch,
                     uint8_t* dst, long long dst_stride, int dw, int dh, int dpitch, int n_img,
                     cudaStream_t st);
-// context ingest: copies the new frame (left/right planes, n_seq each) into level 0 of
-// slot (state.slot ^ 1) (slot 0 on the first frame), builds levels 1.., runs FAST on the
-// new LEFT image into fastkeys[parity].
-void launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
-                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
-                   int first_frame, int parity, cudaStream_t st);
+// context ingest of one frame into pyramid slot `slot` (ring, frame f -> f % 3): copies the new frame
+// (left/right planes, n_seq each) into level 0 -- skipped when left == nullptr, i.e. level 0 was already
+// written in place (H2D straight into the slot) --, builds levels 1.., runs FAST on the new LEFT image into
+// fastkeys[slot].  Returns the number of kernel launches.
+int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                  const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
+                  cudaStream_t st);
 
 // ---- per-frame pipeline stages (all sequences of the context per launch) ----
 void launch_first_frame(const DevArrays& d, cudaStream_t st);
-void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int parity,
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf,
                          cudaStream_t st);
-void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, cudaStream_t st);
-void launch_select(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
+                int slot_cur, cudaStream_t st);
+void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
+                   cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);

@@ -252,6 +252,26 @@ class VisualOdometry:
         self._last_images = (L, R)
         return bool(ok), T
 
+    def submit(self, image_left, image_right):
+        """Streaming form of stereo_callback (svo_submit_frame): enqueue one frame and return at once.  The
+        arrays must stay alive (ideally pinned) until the matching collect()."""
+        L, R = _img(image_left), _img(image_right)
+        if L.shape != R.shape or L.strides[0] != R.strides[0]:
+            raise SvoError("left / right image layouts differ")
+        if self._ctx is None:
+            self._create(L.shape[1], L.shape[0])
+        check(lib().svo_submit_frame(self._ctx, ptr(L), ptr(R), L.strides[0]))
+        self._inflight = getattr(self, "_inflight", [])
+        self._inflight.append((L, R))
+
+    def collect(self):
+        """Result of the oldest submitted frame: (success, 4x4 float64), identical to stereo_callback's."""
+        r = FrameResult()
+        check(lib().svo_collect(self._ctx, C.byref(r)))
+        if getattr(self, "_inflight", None):
+            self._last_images = self._inflight.pop(0)
+        return bool(r.success), np.array(r.transform, np.float64).reshape(4, 4)
+
     def stereo_callback_batch(self, left, right):
         """n_seq sequences per call: left/right are [n_seq, H, W] uint8.  Returns list[FrameResult]."""
         L, R = np.ascontiguousarray(left), np.ascontiguousarray(right)

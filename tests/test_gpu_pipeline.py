@@ -148,3 +148,49 @@ def test_batched_sequences_equal_single():
             assert bool(res[k].success) == ok
             assert np.array_equal(np.array(res[k].transform).reshape(4, 4), T)
     vb.close()
+
+
+def test_streaming_submit_collect_matches_synchronous_calls():
+    """svo_submit_frame / svo_collect (ingest of frame f+1 overlapping the chain of frame f, ring of 3 pyramid
+    slots) must return exactly what the synchronous svo_process_frame returns, in order."""
+    seq = synth.make_sequence(width=640, height=240, n_frames=12, seed=5)
+    frames = list(seq.frames())
+    a = V.VisualOdometry(640, 240)
+    a.initalize_projection_matricies(seq.Pl, seq.Pr)
+    sync = [a.stereo_callback(L, R) for (L, R) in frames]
+    b = V.VisualOdometry(640, 240)
+    b.initalize_projection_matricies(seq.Pl, seq.Pr)
+    got = []
+    for i, (L, R) in enumerate(frames):
+        b.submit(L, R)
+        if i >= 3:
+            got.append(b.collect())
+    while len(got) < len(frames):
+        got.append(b.collect())
+    assert sum(ok for ok, _ in sync) >= len(frames) - 2
+    for (ok0, T0), (ok1, T1) in zip(sync, got):
+        assert ok0 == ok1 and np.array_equal(T0, T1)
+    with pytest.raises(V.SvoError):
+        b.collect()   # nothing pending
+
+
+def test_empty_frame_keeps_the_previous_pyramids():
+    """vo.cpp:179-181: with no feature to track circularMatching returns before the cached pyramids are replaced,
+    so the next frame tracks from the OLD images.  Frame 1 is blank (no FAST corner on frame 0's ... frame order:
+    textured, blank-detected)."""
+    seq = synth.make_sequence(width=640, height=240, n_frames=4, seed=7)
+    fr = list(seq.frames())
+    blank = np.full_like(fr[0][0], 90)
+    order = [(blank, blank), fr[1], fr[2], fr[3]]   # frame 0 blank: frame 1 has no FAST corners to track
+    vo = V.VisualOdometry(640, 240)
+    vo.initalize_projection_matricies(seq.Pl, seq.Pr)
+    ref = O.RefVO(seq.Pl, seq.Pr)
+    for i, (L, R) in enumerate(order):
+        ok, T = vo.stereo_callback(L, R)
+        rok, rT = ref.stereo_callback(L, R)
+        assert ok == rok, f"frame {i}"
+        r = vo.last_result()
+        if i == 1:
+            assert r.n_bucketed == 0
+        if ok:
+            assert np.abs(T - rT).max() < 5e-3
