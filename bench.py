@@ -232,6 +232,7 @@ def run_gpu(args, rank, world, local_rank):
         for _ in range(FRAMES_PER_STEP):
             enqueue(ctx, k)
             k += 1
+    check(L_.svo_stream_join(ctx))   # the primary stream waits for the context's other streams
     e1.record(stream)
     check(L_.svo_synchronize(ctx))
     torch.cuda.synchronize()
@@ -351,6 +352,7 @@ def run_gpu(args, rank, world, local_rank):
             b0.record(sb)
             for f in range(5, nfb):
                 check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+            check(L_.svo_stream_join(ctxb))
             b1.record(sb)
             check(L_.svo_synchronize(ctxb))
             bms = b0.elapsed_time(b1)

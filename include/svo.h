@@ -128,6 +128,13 @@ int svo_submit_frame_batch(svo_ctx* ctx, const uint8_t* left, const uint8_t* rig
                            long long seq_stride);
 int svo_collect(svo_ctx* ctx, svo_frame_result* results /* [n_seq], may be NULL */);
 int svo_pending(svo_ctx* ctx);                  /* submitted, not yet collected */
+/* Makes the context's primary stream (svo_stream) wait for everything enqueued so far on the context's
+ * other streams, so that an event recorded on svo_stream afterwards covers all submitted frames. */
+int svo_stream_join(svo_ctx* ctx);
+/* Pipeline introspection (synchronises): out = { speculative tracking on, SMs of the chain / ingest / KLT
+ * partitions (0 = whole GPU, no partitioning), features of sequence 0 the last frame had to track outside the
+ * speculative cache, persistent KLT blocks per sequence (chain side / KLT partition), 0 }. */
+int svo_pipeline_info(svo_ctx* ctx, int out[8]);
 int svo_synchronize(svo_ctx* ctx);
 /* Last frame's result for sequence `seq` (host copy; synchronises). */
 int svo_get_result(svo_ctx* ctx, int seq, svo_frame_result* out);

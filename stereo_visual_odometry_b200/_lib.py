@@ -52,7 +52,7 @@ REASONS = {0: "", 1: "first", 2: "few_features", 3: "pnp_failed", 4: "too_big"}
 SYMBOLS = [
     "svo_version", "svo_last_error", "svo_device_count", "svo_default_params", "svo_create",
     "svo_destroy", "svo_set_projection", "svo_process_frame", "svo_process_frame_batch",
-    "svo_process_frame_batch_dev", "svo_submit_frame", "svo_submit_frame_batch", "svo_collect", "svo_pending",
+    "svo_process_frame_batch_dev", "svo_submit_frame", "svo_submit_frame_batch", "svo_collect", "svo_pending", "svo_stream_join", "svo_pipeline_info",
     "svo_synchronize", "svo_get_result", "svo_get_tap", "svo_stream",
     "svo_launch_count", "svo_enable_timers", "svo_get_stage_time", "svo_reset_timers",
     "svo_fast_detect", "svo_bucket_filter", "svo_build_pyramid", "svo_lk_track",
@@ -98,6 +98,8 @@ def lib():
     L.svo_submit_frame_batch.argtypes = [vp, u8p, u8p, C.c_int, C.c_longlong]
     L.svo_collect.argtypes = [vp, C.POINTER(FrameResult)]
     L.svo_pending.argtypes = [vp]
+    L.svo_stream_join.argtypes = [vp]
+    L.svo_pipeline_info.argtypes = [vp, ip]
     L.svo_synchronize.argtypes = [vp]
     L.svo_get_result.argtypes = [vp, C.c_int, C.POINTER(FrameResult)]
     L.svo_get_tap.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, ip, u8p]

@@ -2,10 +2,18 @@
 //
 // Owns the device-resident state of VisualOdometry (include/vo.h:233-268 of the
 // reference): frame id, the t0/t1 image pyramids, currentVOFeatures, the rotation /
-// translation guess and last_transform, for n_seq independent sequences.  One CUDA
-// stream per context; the per-frame chain is stream-ordered with device-side
-// predicates for every branch of stereo_callback (vo.cpp:41-137), so the host never
-// has to look at intermediate results.
+// translation guess and last_transform, for n_seq independent sequences.  Every branch
+// of stereo_callback (vo.cpp:41-137) is a device-side predicate, so the host never looks
+// at intermediate results: a frame is a fixed set of launches on four streams --
+//   stream_in  ingest (H2D, pyramid, FAST) of frame f + 1
+//   stream_k   speculative circular matching of the candidates of frame f + 1
+//   stream     the dependent chain of frame f: bucketing -> (left-over KLT) -> select ->
+//              RANSAC hypotheses -> inliers / feature set
+//   stream_fb  LM pose refit + result of frame f
+// ordered by events.  For a single sequence the streams live in three green contexts
+// (disjoint SM partitions), so the latency-bound pose chain never queues behind the
+// throughput-bound tracking kernels.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
@@ -83,10 +91,22 @@ struct svo_ctx {
     BucketGeom bg;
     PipeConfig pc;
     DevArrays d;
-    cudaStream_t stream = nullptr;      // tracking chain (bucket .. PnP) and everything synchronous
-    cudaStream_t stream_in = nullptr;   // ingest of the next frame (H2D, pyramid, FAST) overlaps the chain
+    cudaStream_t stream = nullptr;      // dependent chain (bucket .. inliers) and everything synchronous
+    cudaStream_t stream_in = nullptr;   // ingest of the next frame (H2D, pyramid, FAST)
+    cudaStream_t stream_k = nullptr;    // speculative KLT
+    cudaStream_t stream_fb = nullptr;   // pose refit + result
+    cudaStream_t stream_full = nullptr; // whole-GPU stream for serial frames (== stream when there are no partitions)
+    int klt_blocks_full = 0;            // persistent KLT blocks per sequence on the whole GPU
+    void* green[3] = {nullptr, nullptr, nullptr};   // CUgreenCtx of the chain / ingest / KLT partitions
+    int sm_chain = 0, sm_in = 0, sm_k = 0;          // SMs of each partition (0: no partitioning)
+    bool spec = false;                  // speculative tracking on
+    bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
+    int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
-    cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // last reader of frame f's "previous" slot done
+    cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
+    cudaEvent_t ev_trk[4] = {nullptr, nullptr, nullptr, nullptr};   // speculative KLT of frame f complete
+    cudaEvent_t ev_fa[4] = {nullptr, nullptr, nullptr, nullptr};    // chain of frame f complete
+    cudaEvent_t ev_fb[4] = {nullptr, nullptr, nullptr, nullptr};    // refit + result of frame f complete
     cudaEvent_t ev_done[SVO_RESULT_RING];                           // result of frame f in host_result ring
     std::vector<void*> allocs;
     uint8_t* stage_L = nullptr;
@@ -157,6 +177,7 @@ static LkConfig make_lk_config(const svo_params& p, int nlevels) {
     double e = p.lk_epsilon < 0.f ? 0.0 : (p.lk_epsilon > 10.f ? 10.0 : (double)p.lk_epsilon);
     c.eps_sq = e * e;
     c.min_eig = p.lk_min_eig;
+    lk_config_finish(c);
     return c;
 }
 
@@ -187,14 +208,123 @@ static int validate_params(const svo_params* p) {
     return SVO_OK;
 }
 
+// Streams of a context.  A single-sequence context is latency bound: its pose chain (a few small blocks) must
+// never wait for a block slot behind the persistent tracking kernels, so the SMs are split with CUDA green
+// contexts into chain / ingest / KLT partitions (SVO_PARTITION="chain,ingest" SM counts, "0" = off; default
+// 24,16 of the 148 SMs).  Batched contexts are throughput bound and use plain streams on the whole GPU.
+// SVO_SPEC=0/1 overrides whether the speculative tracking runs (default: single-sequence contexts only).
+static int create_streams(svo_ctx* c, const svo_params* p) {
+    int want_chain = 24, want_in = 16;
+    c->spec = p->n_seq == 1 && c->pipeline_ctx;
+    if (const char* e = getenv("SVO_SPEC"))
+        if (c->pipeline_ctx) c->spec = atoi(e) != 0;
+    if (const char* e = getenv("SVO_PARTITION")) {
+        want_chain = want_in = 0;
+        sscanf(e, "%d,%d", &want_chain, &want_in);
+    }
+    if (!c->spec || p->n_seq != 1) want_chain = want_in = 0;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, p->device));
+    bool ok = false;
+    if (want_chain >= 8 && want_in >= 8 && want_chain + want_in + 16 <= prop.multiProcessorCount) {
+#define DRV(name)                                                                                      \
+    decltype(&name) p_##name = nullptr;                                                                \
+    {                                                                                                  \
+        cudaDriverEntryPointQueryResult qr;                                                            \
+        if (cudaGetDriverEntryPoint(#name, (void**)&p_##name, cudaEnableDefault, &qr) != cudaSuccess) \
+            p_##name = nullptr;                                                                        \
+    }
+        DRV(cuDeviceGetDevResource) DRV(cuDevSmResourceSplitByCount) DRV(cuDevResourceGenerateDesc)
+        DRV(cuGreenCtxCreate) DRV(cuGreenCtxStreamCreate)
+#undef DRV
+        if (p_cuDeviceGetDevResource && p_cuDevSmResourceSplitByCount && p_cuDevResourceGenerateDesc &&
+            p_cuGreenCtxCreate && p_cuGreenCtxStreamCreate) {
+            // split the GPU into groups of 8 SMs (the granularity the driver accepts) and assemble the three
+            // partitions from whole groups; what is left over joins the KLT partition
+            CUdevResource all, grp[32], rem;
+            unsigned ngrp = 32;
+            CUgreenCtx gc[3] = {nullptr, nullptr, nullptr};
+            CUdevResourceDesc dc[3];
+            CUstream st[4] = {nullptr, nullptr, nullptr, nullptr};
+            const bool dbg = getenv("SVO_DEBUG") != nullptr;
+            int step = 0;
+            auto TRY = [&](CUresult x) {
+                ++step;
+                if (ok && x != CUDA_SUCCESS) {
+                    ok = false;
+                    if (dbg) fprintf(stderr, "svo: green-context step %d failed with CUresult %d\n", step, (int)x);
+                }
+                return ok;
+            };
+            ok = true;
+            TRY(p_cuDeviceGetDevResource(p->device, &all, CU_DEV_RESOURCE_TYPE_SM));
+            if (ok) TRY(p_cuDevSmResourceSplitByCount(grp, &ngrp, &all, &rem, 0, 8));
+            const int n_chain = (want_chain + 7) / 8, n_in = (want_in + 7) / 8;
+            ok = ok && (int)ngrp >= n_chain + n_in + 2;
+            unsigned sm_cnt[3] = {0, 0, 0};
+            if (ok) {
+                CUdevResource kl[33];
+                int nk = 0;
+                for (unsigned i = n_chain + n_in; i < ngrp; ++i) kl[nk++] = grp[i];
+                if (rem.sm.smCount > 0) kl[nk++] = rem;
+                for (int i = 0; i < n_chain; ++i) sm_cnt[0] += grp[i].sm.smCount;
+                for (int i = 0; i < n_in; ++i) sm_cnt[1] += grp[n_chain + i].sm.smCount;
+                for (int i = 0; i < nk; ++i) sm_cnt[2] += kl[i].sm.smCount;
+                TRY(p_cuDevResourceGenerateDesc(&dc[0], grp, n_chain));
+                if (ok) TRY(p_cuDevResourceGenerateDesc(&dc[1], grp + n_chain, n_in));
+                if (ok && p_cuDevResourceGenerateDesc(&dc[2], kl, nk) != CUDA_SUCCESS) {
+                    // the remainder may not combine with full groups: leave it unused
+                    nk -= rem.sm.smCount > 0 ? 1 : 0;
+                    sm_cnt[2] -= rem.sm.smCount;
+                    TRY(p_cuDevResourceGenerateDesc(&dc[2], kl, nk));
+                }
+            }
+            if (dbg) fprintf(stderr, "svo: SM partitions chain %u ingest %u klt %u (groups %u, ok %d)\n", sm_cnt[0], sm_cnt[1], sm_cnt[2], ngrp, (int)ok);
+            for (int i = 0; i < 3 && ok; ++i) TRY(p_cuGreenCtxCreate(&gc[i], dc[i], p->device, CU_GREEN_CTX_DEFAULT_STREAM));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[0], gc[0], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[1], gc[0], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[2], gc[1], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[3], gc[2], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) {
+                c->stream = (cudaStream_t)st[0];
+                c->stream_fb = (cudaStream_t)st[1];
+                c->stream_in = (cudaStream_t)st[2];
+                c->stream_k = (cudaStream_t)st[3];
+                for (int i = 0; i < 3; ++i) c->green[i] = gc[i];
+                c->sm_chain = (int)sm_cnt[0];
+                c->sm_in = (int)sm_cnt[1];
+                c->sm_k = (int)sm_cnt[2];
+            }
+            cudaGetLastError();
+        } else if (getenv("SVO_DEBUG")) {
+            fprintf(stderr, "svo: green-context driver entry points not available\n");
+        }
+    }
+    if (ok) CU(cudaStreamCreateWithFlags(&c->stream_full, cudaStreamNonBlocking));
+    if (!ok) {
+        c->sm_chain = c->sm_in = c->sm_k = 0;
+        CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->stream_fb, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->stream_in, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->stream_k, cudaStreamNonBlocking));
+        c->stream_full = c->stream;
+    }
+    return SVO_OK;
+}
+
 static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     c->p = *p;
     CU(cudaSetDevice(p->device));
-    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&c->stream_in, cudaStreamNonBlocking));
+    {
+        int rc = create_streams(c, p);
+        if (rc != SVO_OK) return rc;
+    }
     for (int i = 0; i < 4; ++i) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_trk[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_fa[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_fb[i], cudaEventDisableTiming));
     }
     for (int i = 0; i < SVO_RESULT_RING; ++i) {
         c->ev_done[i] = nullptr;
@@ -249,6 +379,20 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
     CU(dev_alloc(c, &d.inl_idx, C));
     CU(dev_alloc(c, &d.klt_next, S));
+    d.nb = c->bg.nb;
+    CU(dev_alloc(c, &d.specF_pts, (size_t)2 * S * c->bg.nb * 4));
+    CU(dev_alloc(c, &d.specF_st, (size_t)2 * S * c->bg.nb));
+    CU(dev_alloc(c, &d.specF_it, (size_t)2 * S * c->bg.nb));
+    CU(dev_alloc(c, &d.specT_pts, C * 4));
+    CU(dev_alloc(c, &d.specT_st, C));
+    CU(dev_alloc(c, &d.specT_it, C));
+    CU(dev_alloc(c, &d.cntF, S));
+    CU(dev_alloc(c, &d.cntT, S));
+    CU(dev_alloc(c, &d.listF, S * c->bg.nb));
+    CU(dev_alloc(c, &d.nF, S));
+    CU(dev_alloc(c, &d.todo, C));
+    CU(dev_alloc(c, &d.n_todo, S));
+    CU(dev_alloc(c, &d.job, S));
     CU(dev_alloc(c, &d.hyp_samples, S * d.n_hyp * 5));
     CU(dev_alloc(c, &d.rng_raw, (size_t)SVO_RNG_TABLE));
     {
@@ -273,21 +417,29 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     {
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, p->device));
-        // 3 resident blocks of 8 warps per SM (register bound); split the machine between the sequences
-        int per_seq = (prop.multiProcessorCount * 3 + p->n_seq - 1) / p->n_seq;
+        // every resident block slot of the partition the kernel runs on, split between the sequences
+        const int per_sm = klt_resident_blocks_per_sm();
+        const int sm_chain = c->sm_chain > 0 ? c->sm_chain : prop.multiProcessorCount;
+        const int sm_k = c->sm_k > 0 ? c->sm_k : prop.multiProcessorCount;
+        int per_seq = (sm_chain * per_sm + p->n_seq - 1) / p->n_seq;
         c->klt_blocks = per_seq < 1 ? 1 : per_seq;
+        per_seq = (sm_k * per_sm + p->n_seq - 1) / p->n_seq;
+        c->klt_blocks_k = per_seq < 1 ? 1 : per_seq;
+        per_seq = (prop.multiProcessorCount * per_sm + p->n_seq - 1) / p->n_seq;
+        c->klt_blocks_full = per_seq < 1 ? 1 : per_seq;
     }
     CU(cudaStreamSynchronize(c->stream));
     return SVO_OK;
 }
 
-static svo_ctx* ctx_create(const svo_params* p, int cap_override) {
+static svo_ctx* ctx_create(const svo_params* p, int cap_override, bool pipeline_ctx = true) {
     if (validate_params(p) != SVO_OK) return nullptr;
     if (svo_device_count() <= 0) {
         if (g_err.empty()) g_err = "no CUDA device";
         return nullptr;
     }
     svo_ctx* c = new svo_ctx();
+    c->pipeline_ctx = pipeline_ctx;
     if (ctx_init(c, p, cap_override) != SVO_OK) {
         std::string keep = g_err;
         svo_destroy(c);
@@ -312,13 +464,22 @@ extern "C" svo_ctx* svo_create(const svo_params* p) {
 extern "C" void svo_destroy(svo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->p.device);
-    if (c->stream_in) cudaStreamSynchronize(c->stream_in);
-    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb})
+        if (st) cudaStreamSynchronize(st);
     for (void* q : c->allocs) cudaFree(q);
     for (int i = 0; i < 4; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
+        if (c->ev_trk[i]) cudaEventDestroy(c->ev_trk[i]);
+        if (c->ev_fa[i]) cudaEventDestroy(c->ev_fa[i]);
+        if (c->ev_fb[i]) cudaEventDestroy(c->ev_fb[i]);
     }
+    if (c->stream_full && c->stream_full != c->stream) {
+        cudaStreamSynchronize(c->stream_full);
+        cudaStreamDestroy(c->stream_full);
+    }
+    for (cudaStream_t st : {c->stream_k, c->stream_fb})
+        if (st) cudaStreamDestroy(st);
     for (int i = 0; i < SVO_RESULT_RING; ++i)
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
     if (c->stream_in) cudaStreamDestroy(c->stream_in);
@@ -327,6 +488,14 @@ extern "C" void svo_destroy(svo_ctx* c) {
         for (int i = 0; i < 7; ++i)
             if (c->ev[i]) cudaEventDestroy(c->ev[i]);
         cudaStreamDestroy(c->stream);
+    }
+    {
+        decltype(&cuGreenCtxDestroy) p_destroy = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (c->green[0] && cudaGetDriverEntryPoint("cuGreenCtxDestroy", (void**)&p_destroy, cudaEnableDefault, &qr) == cudaSuccess &&
+            p_destroy)
+            for (int i = 0; i < 3; ++i)
+                if (c->green[i]) p_destroy((CUgreenCtx)c->green[i]);
     }
     delete c;
 }
@@ -367,59 +536,111 @@ extern "C" int svo_get_stage_time(svo_ctx* c, int stage, double* ms_out, long lo
     return SVO_OK;
 }
 
-// One frame = ingest (stream_in) + tracking chain (stream).  The ingest of frame f + 1 depends on nothing the
-// chain of frame f produces (FAST runs on the NEW left image and is consumed one frame later), so the two
-// streams overlap; events order the ring reuse (slot f % 3 is last read by the KLT of frame f - 2 ... f - 1).
+// serial frame: every launch of the frame goes to ONE stream that owns the whole GPU (per-stage timers; a
+// partitioned context whose caller is not streaming)
+static bool serial_frame(const svo_ctx* c, bool speculate) {
+    return c->timers || (c->sm_chain > 0 && !(c->spec && speculate));
+}
+static cudaStream_t ingest_stream(const svo_ctx* c, bool speculate) {
+    return serial_frame(c, speculate) ? c->stream_full : c->stream_in;
+}
+
+// One frame = a fixed set of launches on four streams (see the file header).  Dependencies of frame f:
+//   ingest(f)    [stream_in]  after select(f - 2): pyramid slot / FAST key buffer f % 3 are free again
+//   F(f), T(f)   [stream_k]   speculative circular matching of the candidates of frame f: F needs ingest(f),
+//                             T needs select(f - 1) (the matched list); results are a cache keyed by bucket /
+//                             matched index that bucket_merge(f) looks up
+//   chain(f)     [stream]     bucket_merge (needs the inliers of f - 1 and the cache) -> klt (only what the cache
+//                             missed) -> select -> hypotheses -> inliers / feature set
+//   refit(f)     [stream_fb]  LM refit, gates, result struct, result copies
 // `left`/`right`: device planes, or nullptr when level 0 of the slot was already written (H2D in place).
 // to_host: also copy the result structs into the pinned host ring (slot tracked % SVO_RESULT_RING).
 static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
-                         svo_frame_result* results_dev, bool to_host) {
+                         svo_frame_result* results_dev, bool to_host, bool speculate) {
     const long long f = c->frames;
     const bool first = f == 0;
     const int cur = (int)(f % SVO_PYR_SLOTS), prev = (int)((f + SVO_PYR_SLOTS - 1) % SVO_PYR_SLOTS);
-    const bool tm = c->timers;   // timed mode: everything serial on one stream
-    cudaStream_t sP = c->stream, sI = tm ? c->stream : c->stream_in;
-    if (tm) cudaEventRecord(c->ev[0], sP);
+    const int e = (int)(f & 3), e1 = (int)((f + 3) & 3);   // event slots of frame f and f - 1
+    // speculation pays when frames are in flight (its kernels then run beside the previous frame's pose chain);
+    // a caller that waits for every result before sending the next frame, and the per-stage timers, get the
+    // plain serial chain on one stream that owns the whole GPU
+    const bool spec = c->spec && !c->timers && speculate;
+    const bool tm = serial_frame(c, speculate);
+    cudaStream_t sP = tm ? c->stream_full : c->stream;
+    cudaStream_t sI = tm ? sP : c->stream_in, sK = tm ? sP : c->stream_k, sB = tm ? sP : c->stream_fb;
+    if (tm && !first) CU(cudaStreamWaitEvent(sP, c->ev_fb[e1], 0));   // the previous frame may have run on the partitions
+    if (c->timers) cudaEventRecord(c->ev[0], sP);
     const int n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
     c->launches += n_ingest;
     if (!tm) {
-        CU(cudaEventRecord(c->ev_in[f & 3], sI));
-        CU(cudaStreamWaitEvent(sP, c->ev_in[f & 3], 0));
+        CU(cudaEventRecord(c->ev_in[e], sI));
+        CU(cudaStreamWaitEvent(sP, c->ev_in[e], 0));
     }
-    if (tm) cudaEventRecord(c->ev[1], sP);
+    if (spec && !first) {
+        CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
+        launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k, prev, cur, prev, (int)(f & 1), sK);
+        CU(cudaStreamWaitEvent(sK, c->ev_sel[e1], 0));
+        launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k, prev, cur, sK);
+        CU(cudaEventRecord(c->ev_trk[e], sK));
+        CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
+        c->launches += 2;
+    }
+    if (c->timers) cudaEventRecord(c->ev[1], sP);
     if (first) {
         launch_first_frame(c->d, sP);
         c->launches += 1;
+        CU(cudaEventRecord(c->ev_sel[e], sP));
     } else {
-        launch_bucket_merge(c->d, c->bg, c->pc, prev, sP);   // FAST winners of the PREVIOUS left image
-        if (tm) cudaEventRecord(c->ev[2], sP);
-        launch_klt(c->d, c->pg, c->pc, c->klt_blocks, prev, cur, sP);
-        if (tm) cudaEventRecord(c->ev[3], sP);
+        launch_bucket_merge(c->d, c->bg, c->pc, prev, (int)(f & 1), spec ? 1 : 0, sP);   // FAST winners of the PREVIOUS left image
+        if (c->timers) cudaEventRecord(c->ev[2], sP);
+        if (tm) {
+            launch_klt(c->d, c->pg, c->pc, c->klt_blocks_full, prev, cur, sP);
+        } else if (spec) {
+            // normally nothing is left to track: a small grid on the chain's own SMs
+            launch_klt(c->d, c->pg, c->pc, c->klt_blocks, prev, cur, sP);
+        } else {
+            // no cache: all bucketed features, on the KLT partition
+            CU(cudaEventRecord(c->ev_trk[e], sP));
+            CU(cudaStreamWaitEvent(sK, c->ev_trk[e], 0));
+            launch_klt(c->d, c->pg, c->pc, c->klt_blocks_k, prev, cur, sK);
+            CU(cudaEventRecord(c->ev_trk[e], sK));
+            CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
+        }
+        if (c->timers) cudaEventRecord(c->ev[3], sP);
         launch_select(c->d, c->pg, c->pc, prev, cur, sP);
-        if (tm) cudaEventRecord(c->ev[4], sP);
-    }
-    CU(cudaEventRecord(c->ev_sel[f & 3], sP));
-    if (!first) {
+        if (c->timers) cudaEventRecord(c->ev[4], sP);
+        CU(cudaEventRecord(c->ev_sel[e], sP));
         launch_pnp_hyp(c->d, c->pc, sP);
-        if (tm) cudaEventRecord(c->ev[5], sP);
-        launch_pnp_final(c->d, c->pc, sP);
-        if (tm) cudaEventRecord(c->ev[6], sP);
-        c->launches += 5;
+        if (c->timers) cudaEventRecord(c->ev[5], sP);
+        if (!tm) CU(cudaStreamWaitEvent(sP, c->ev_fb[e1], 0));   // the refit of f - 1 still reads the inlier arrays
+        launch_pnp_final_a(c->d, c->pc, sP);
+        c->launches += 6;
     }
+    if (!tm) {
+        CU(cudaEventRecord(c->ev_fa[e], sP));
+        CU(cudaStreamWaitEvent(sB, c->ev_fa[e], 0));
+    }
+    if (!first) launch_pnp_final_b(c->d, c->pc, sB);
+    if (c->timers) cudaEventRecord(c->ev[6], sP);
     if (results_dev)
-        CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, sP));
+        CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, sB));
     if (to_host) {
         const int r = (int)(c->tracked % SVO_RESULT_RING);
         CU(cudaMemcpyAsync(c->host_result + (size_t)r * c->d.n_seq, c->d.result, sizeof(svo_frame_result) * c->d.n_seq,
-                           cudaMemcpyDeviceToHost, sP));
-        CU(cudaEventRecord(c->ev_done[r], sP));
+                           cudaMemcpyDeviceToHost, sB));
+        CU(cudaEventRecord(c->ev_done[r], sB));
         c->tracked += 1;
     }
+    if (!tm) {
+        CU(cudaEventRecord(c->ev_fb[e], sB));
+    } else {   // a later frame may run on the partitions again: it finds every event of this frame signalled
+        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
+    }
     CU(cudaGetLastError());
-    if (tm) {
+    if (c->timers) {
         CU(cudaStreamSynchronize(sP));
         const int nst = first ? 1 : 6;
-        const int nl[6] = {n_ingest, 1, 1, 1, 1, 1};
+        const int nl[6] = {n_ingest, 1, 1, 1, 1, 2};
         for (int i = 0; i < nst; ++i) {
             float ms = 0.f;
             cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]);
@@ -432,9 +653,9 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
 }
 
 // the ingest stream may not start writing slot f % 3 / key buffer f % 3 before frame f - 2 is done reading
-static int wait_ring(svo_ctx* c) {
+static int wait_ring(svo_ctx* c, bool speculate) {
     const long long f = c->frames;
-    if (!c->timers && f >= 2) CU(cudaStreamWaitEvent(c->stream_in, c->ev_sel[(f - 2) & 3], 0));
+    if (f >= 2) CU(cudaStreamWaitEvent(ingest_stream(c, speculate), c->ev_sel[(f - 2) & 3], 0));
     return SVO_OK;
 }
 
@@ -444,9 +665,9 @@ extern "C" int svo_process_frame_batch_dev(svo_ctx* c, const uint8_t* left_dev, 
     if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
     if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
     CU(cudaSetDevice(c->p.device));
-    int rc = wait_ring(c);
+    int rc = wait_ring(c, true);
     if (rc != SVO_OK) return rc;
-    return enqueue_frame(c, left_dev, right_dev, stride, seq_stride, results_dev, false);
+    return enqueue_frame(c, left_dev, right_dev, stride, seq_stride, results_dev, false, true);
 }
 
 extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride,
@@ -457,11 +678,12 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
     if (c->tracked - c->collected >= SVO_RESULT_RING)
         return fail(SVO_ERR_STATE, "result ring full: call svo_collect before submitting more frames");
     CU(cudaSetDevice(c->p.device));
-    int rc = wait_ring(c);
+    const bool in_flight = c->tracked > c->collected;   // streaming caller: an earlier frame is still uncollected
+    int rc = wait_ring(c, in_flight);
     if (rc != SVO_OK) return rc;
     const int S = c->d.n_seq, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
     const long long plane = (long long)P0 * H;
-    cudaStream_t sI = c->timers ? c->stream : c->stream_in;
+    cudaStream_t sI = ingest_stream(c, in_flight);
     if (S == 1) {
         // straight into level 0 of the frame's pyramid slot: no staging copy
         const int cur = (int)(c->frames % SVO_PYR_SLOTS);
@@ -469,7 +691,7 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
         uint8_t* r0 = c->d.pyr + c->pg.base(0, cur, 1) + c->pg.off[0];
         CU(cudaMemcpy2DAsync(l0, P0, left, stride, W, H, cudaMemcpyHostToDevice, sI));
         CU(cudaMemcpy2DAsync(r0, P0, right, stride, W, H, cudaMemcpyHostToDevice, sI));
-        return enqueue_frame(c, nullptr, nullptr, P0, plane, nullptr, true);
+        return enqueue_frame(c, nullptr, nullptr, P0, plane, nullptr, true, in_flight);
     }
     // the staging planes are read by the ingest of the previous frame: same stream, so ordered
     if (seq_stride == (long long)stride * H) {
@@ -481,7 +703,7 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
             CU(cudaMemcpy2DAsync(c->stage_R + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sI));
         }
     }
-    return enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr, true);
+    return enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr, true, in_flight);
 }
 
 extern "C" int svo_submit_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride) {
@@ -529,15 +751,42 @@ extern "C" int svo_process_frame(svo_ctx* c, const uint8_t* left, const uint8_t*
 extern "C" int svo_synchronize(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     CU(cudaSetDevice(c->p.device));
-    CU(cudaStreamSynchronize(c->stream_in));
-    CU(cudaStreamSynchronize(c->stream));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    return SVO_OK;
+}
+
+extern "C" int svo_pipeline_info(svo_ctx* c, int out[8]) {
+    if (!c || !out) return fail(SVO_ERR_INVALID, "NULL argument");
+    CU(cudaSetDevice(c->p.device));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    int n_todo = 0;
+    CU(cudaMemcpy(&n_todo, c->d.n_todo, sizeof(int), cudaMemcpyDeviceToHost));
+    out[0] = c->spec ? 1 : 0;
+    out[1] = c->sm_chain;
+    out[2] = c->sm_in;
+    out[3] = c->sm_k;
+    out[4] = n_todo;
+    out[5] = c->klt_blocks;
+    out[6] = c->klt_blocks_k;
+    out[7] = 0;
+    return SVO_OK;
+}
+
+extern "C" int svo_stream_join(svo_ctx* c) {
+    if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
+    if (c->frames == 0 || c->timers) return SVO_OK;
+    CU(cudaSetDevice(c->p.device));
+    const int e = (int)((c->frames - 1) & 3);
+    CU(cudaStreamWaitEvent(c->stream, c->ev_fb[e], 0));
+    CU(cudaStreamWaitEvent(c->stream, c->ev_in[e], 0));
+    if (c->spec && c->frames > 1) CU(cudaStreamWaitEvent(c->stream, c->ev_trk[e], 0));
     return SVO_OK;
 }
 
 extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
     if (!c || !out || seq < 0 || seq >= c->d.n_seq) return fail(SVO_ERR_INVALID, "bad argument");
     CU(cudaSetDevice(c->p.device));
-    CU(cudaStreamSynchronize(c->stream));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     CU(cudaMemcpy(out, c->d.result + seq, sizeof(svo_frame_result), cudaMemcpyDeviceToHost));
     return SVO_OK;
 }
@@ -545,7 +794,7 @@ extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
 extern "C" int svo_get_tap(svo_ctx* c, int seq, int which, int cap, float* f_out, int* i_out, uint8_t* u8_out) {
     if (!c || seq < 0 || seq >= c->d.n_seq || cap < 0) return fail(SVO_ERR_INVALID, "bad argument");
     CU(cudaSetDevice(c->p.device));
-    CU(cudaStreamSynchronize(c->stream));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     SeqState s;
     CU(cudaMemcpy(&s, c->d.state + seq, sizeof(s), cudaMemcpyDeviceToHost));
     const DevArrays& d = c->d;
@@ -782,7 +1031,7 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     svo_params q = *p;
     q.n_seq = 1;
     q.features_per_bucket = 1;
-    svo_ctx* c = ctx_create(&q, n_in > fs_cap ? n_in : fs_cap);
+    svo_ctx* c = ctx_create(&q, n_in > fs_cap ? n_in : fs_cap, false);
     if (!c) return SVO_ERR_CUDA;
     struct Guard {
         svo_ctx* c;
@@ -818,11 +1067,17 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
         }
         s.n_feat = n0;
         CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
-        launch_bucket_merge(d, c->bg, c->pc, 0, st);
+        launch_bucket_merge(d, c->bg, c->pc, 0, 0, 0, st);
     } else {
         if (n_in > 0) CU(cudaMemcpyAsync(d.bk_xy, pL0_in, sizeof(float2) * n_in, cudaMemcpyHostToDevice, st));
         s.n_bucketed = n_in;
         CU(cudaMemcpyAsync(d.state, &s, sizeof(s), cudaMemcpyHostToDevice, st));
+        // no bucketing pass here: queue every given point for klt_kernel
+        std::vector<int> iota(n_in > 0 ? n_in : 1);
+        for (int i = 0; i < n_in; ++i) iota[i] = i;
+        CU(cudaMemcpyAsync(d.todo, iota.data(), sizeof(int) * (n_in > 0 ? n_in : 1), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d.n_todo, &n_in, sizeof(int), cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
     }
     CU(cudaMemsetAsync(d.klt_next, 0, sizeof(int), st));
     launch_klt(d, c->pg, c->pc, c->klt_blocks, 0, 1, st);
@@ -968,7 +1223,7 @@ extern "C" int svo_camera_to_world(const svo_params* p, const float K[9], const 
     if (rc != SVO_OK) return rc;
     rc = need_device();
     if (rc != SVO_OK) return rc;
-    svo_ctx* c = ctx_create(&q, n);
+    svo_ctx* c = ctx_create(&q, n, false);
     if (!c) return SVO_ERR_CUDA;
     struct Guard {
         svo_ctx* c;

@@ -131,12 +131,21 @@ struct LkConfig {
     int max_iters;    // criteria.maxCount
     double eps_sq;    // criteria.epsilon^2
     float min_eig;    // minEigThreshold
+    // float32 brackets of eps_sq (1e-6 relative): the FP64 termination test of OpenCV is only evaluated when the
+    // float32 value falls between them.  lk_config_finish() fills them.
+    float eps_lo, eps_hi;
 };
+SVO_HD void lk_config_finish(LkConfig& c) {
+    c.eps_lo = (float)(c.eps_sq * (1.0 - 1e-6));
+    c.eps_hi = (float)(c.eps_sq * (1.0 + 1e-6));
+}
 
 // Reduction policy for LANES == 1 (host unit tests).
 struct SerialRed {
     static SVO_HD int sum(int v) { return v; }
     static SVO_HD long long sum64(long long v) { return v; }
+    // exact integer sums of the two mismatch accumulators, converted to float32 (round to nearest)
+    static SVO_HD void sum2f(long long a, long long b, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
     static SVO_HD void sync() {}
 };
 
@@ -210,6 +219,27 @@ SVO_HD void lk_weights(float a, float b, int& iw00, int& iw01, int& iw10, int& i
 template <int LANES> struct LkAcc { typedef int type; };
 template <> struct LkAcc<1> { typedef long long type; };   // host unit tests: one lane carries all 100 pixels
 
+// Which window pixel (row, col of the 10x10 window) a (lane, slot) pair owns.
+//   LANES == 32: lanes 0..29 own column lane % 10 of rows lane / 10 + 3 * slot (slot 3 only exists for the
+//   first row group), so the four pixels of a lane sit at CONSTANT row strides (one address register, immediate
+//   offsets) and no per-slot index arithmetic is left in the iteration loop.  Slots without a pixel point at
+//   a valid pixel and carry zero template values, which makes their contribution exactly zero without predicates.
+//   LANES == 1 (host unit tests): one lane walks all 100 pixels.
+template <int LANES> struct LkMap;
+template <> struct LkMap<32> {
+    static constexpr int SLOTS = 4;
+    static SVO_HD bool valid(int lane, int s) { return lane < 30 && lane / 10 + 3 * s < SVO_LK_WIN; }
+    // slots 0..2 keep the constant stride for every lane (lanes 30, 31 read rows 3, 6, 9 with zero template values)
+    static SVO_HD int row(int lane, int s) { return s < 3 ? lane / 10 + 3 * s : (lane < 10 ? 9 : 0); }
+    static SVO_HD int col(int lane, int) { return lane % 10; }
+};
+template <> struct LkMap<1> {
+    static constexpr int SLOTS = SVO_LK_NPIX;
+    static SVO_HD bool valid(int, int) { return true; }
+    static SVO_HD int row(int, int s) { return s / SVO_LK_WIN; }
+    static SVO_HD int col(int, int s) { return s % SVO_LK_WIN; }
+};
+
 // c + a.lo16 * b.byte0 + a.hi16 * b.byte1 with SIGNED 16-bit weights (iw11 = 2^14 - iw00 - iw01 - iw10
 // can be -1 or -2) and UNSIGNED pixels: one IDP.2A (dp2a.lo.s32.u32) on the device
 SVO_HD int dp2a_lo_su(unsigned a, unsigned b, int c) {
@@ -256,19 +286,64 @@ SVO_HD void lk_stage_j(const LkLevel& J, int jx0, int jy0, int lane, unsigned sh
     }
 }
 
+// Stage the 13x13 neighbourhood of the template window whose top-left pixel is (x0, y0) (BORDER_REFLECT_101)
+// into sc.ipatch (pitch 16).  Interior windows are fetched as 13 x 4 aligned words; the patch then starts at
+// byte column `xo` = x0 & 3 of each row.  Returns xo.
+template <int LANES>
+SVO_HD int lk_stage_i(const LkLevel& I, int x0, int y0, int lane, uint8_t* ip) {
+    const bool interior = x0 >= 0 && y0 >= 0 && x0 + SVO_LK_PATCH <= I.w && y0 + SVO_LK_PATCH <= I.h &&
+                          (I.pitch & 3) == 0 && (((size_t)I.img) & 3) == 0 && ((x0 & ~3) + 16 <= I.pitch);
+    if (interior) {
+        const int xa = x0 & ~3;
+        for (int it = lane; it < SVO_LK_PATCH * 4; it += LANES) {
+            const int y = it >> 2, k = it & 3;
+            const uint8_t* src = I.img + (size_t)(y0 + y) * I.pitch + xa + 4 * k;
+            unsigned w0;
+#if defined(__CUDA_ARCH__)
+            w0 = *reinterpret_cast<const unsigned*>(src);
+#else
+            w0 = src[0] | (src[1] << 8) | (src[2] << 16) | ((unsigned)src[3] << 24);
+#endif
+            *reinterpret_cast<unsigned*>(ip + y * SVO_LK_PATCH_PITCH + 4 * k) = w0;
+        }
+        return x0 & 3;
+    }
+    for (int idx = lane; idx < SVO_LK_PATCH * SVO_LK_PATCH; idx += LANES) {
+        const int py = idx / SVO_LK_PATCH, px = idx - py * SVO_LK_PATCH;
+        ip[py * SVO_LK_PATCH_PITCH + px] = (uint8_t)I.at_r(x0 + px, y0 + py);
+    }
+    return 0;
+}
+
 // Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
-// the same scalar control flow; window pixels are distributed lane-cyclically; Red sums across lanes).
+// the same scalar control flow; window pixels are distributed by LkMap; Red sums across lanes).
 // Returns status (1 = tracked) and writes the output position.
 template <int LANES, class Red>
 SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const LkConfig& cfg,
                             float ptx, float pty, int lane, LkScratch& sc, float& outx,
                             float& outy, int& iters_out) {
-    constexpr int SLOTS = (SVO_LK_NPIX + LANES - 1) / LANES;
+    typedef LkMap<LANES> Map;
+    constexpr int SLOTS = Map::SLOTS;
     const float half_win = 4.5f;   // (winSize - 1) * 0.5f
     const float FLT_SCALE = 1.f / (1 << 20);
+    // termination test `ddx^2 + ddy^2 <= eps^2` is evaluated in FP64 by OpenCV; a float32 evaluation decides
+    // it whenever the value is not within 1e-6 relative of the threshold (exact FP64 otherwise)
+    const float eps_lo = cfg.eps_lo, eps_hi = cfg.eps_hi;
     int status = 1;
     float nx = 0.f, ny = 0.f;      // nextPts[ptidx]
     int iters = 0;
+    // per-lane window pixel offsets inside the template patch (pitch 16), the derivative patch (pitch 12) and
+    // the staged J patch (pitch SVO_LK_JC)
+    int offI[SLOTS], offD[SLOTS], offJ[SLOTS];
+    bool val[SLOTS];
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+        const int wy = Map::row(lane, s), wx = Map::col(lane, s);
+        val[s] = Map::valid(lane, s);
+        offI[s] = (wy + 1) * SVO_LK_PATCH_PITCH + wx + 1;
+        offD[s] = wy * SVO_LK_DP + wx;
+        offJ[s] = wy * SVO_LK_JC + wx;
+    }
 
     for (int level = cfg.nlevels - 1; level >= 0; --level) {
         const LkLevel I = Ipyr.lv[level];
@@ -298,10 +373,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
 
         // ---- stage the 13x13 neighbourhood of the template window (BORDER_REFLECT_101)
         Red::sync();
-        for (int idx = lane; idx < SVO_LK_PATCH * SVO_LK_PATCH; idx += LANES) {
-            const int py = idx / SVO_LK_PATCH, px = idx - py * SVO_LK_PATCH;
-            sc.ipatch[py * SVO_LK_PATCH_PITCH + px] = (uint8_t)I.at_r(ipx - 1 + px, ipy - 1 + py);
-        }
+        const int xo = lk_stage_i<LANES>(I, ipx - 1, ipy - 1, lane, sc.ipatch);
         // J patch around the start of the search (independent of the template work)
         float cx = fsub(nxt_x, half_win), cy = fsub(nxt_y, half_win);   // nextPt -= halfWin
         int jx0 = (floor_int(cx) - 5) & ~3, jy0 = floor_int(cy) - 3;
@@ -312,12 +384,12 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         Red::sync();
         // ---- Scharr derivatives on the 11x11 positions of the window (zero outside the level:
         // derivBorder = BORDER_CONSTANT), packed (dx, dy) int16
+        const bool dinside = ipx >= 0 && ipx + SVO_LK_DW <= I.w && ipy >= 0 && ipy + SVO_LK_DW <= I.h;
         for (int idx = lane; idx < SVO_LK_DW * SVO_LK_DW; idx += LANES) {
             const int y = idx / SVO_LK_DW, x = idx - y * SVO_LK_DW;
-            const int ax = ipx + x, ay = ipy + y;
             int v = 0;
-            if (ax >= 0 && ax < I.w && ay >= 0 && ay < I.h) {
-                const uint8_t* p = sc.ipatch + y * SVO_LK_PATCH_PITCH + x;   // top-left of the 3x3 around patch (x+1, y+1)
+            if (dinside || (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h)) {
+                const uint8_t* p = sc.ipatch + y * SVO_LK_PATCH_PITCH + x + xo;   // top-left of the 3x3 around patch (x+1, y+1)
                 const int a00 = p[0], a01 = p[1], a02 = p[2];
                 const int a10 = p[SVO_LK_PATCH_PITCH], a12 = p[SVO_LK_PATCH_PITCH + 2];
                 const int a20 = p[2 * SVO_LK_PATCH_PITCH], a21 = p[2 * SVO_LK_PATCH_PITCH + 1], a22 = p[2 * SVO_LK_PATCH_PITCH + 2];
@@ -334,19 +406,16 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         int sA11 = 0, sA12 = 0, sA22 = 0;
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) {
-            const int idx = lane + s * LANES;
-            Iv[s] = 0; Ixv[s] = 0; Iyv[s] = 0;
-            if (idx < SVO_LK_NPIX) {
-                const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
-                const uint8_t* p = sc.ipatch + (wy + 1) * SVO_LK_PATCH_PITCH + wx + 1;
-                const int iv = (p[0] * iw00 + p[1] * iw01 + p[SVO_LK_PATCH_PITCH] * iw10 + p[SVO_LK_PATCH_PITCH + 1] * iw11 + (1 << 8)) >> 9;
-                const int* dq = sc.dxy + wy * SVO_LK_DP + wx;
-                const int d00 = dq[0], d01 = dq[1], d10 = dq[SVO_LK_DP], d11 = dq[SVO_LK_DP + 1];
-                const int ix = ((int)(short)d00 * iw00 + (int)(short)d01 * iw01 + (int)(short)d10 * iw10 + (int)(short)d11 * iw11 + (1 << 13)) >> 14;
-                const int iy = ((d00 >> 16) * iw00 + (d01 >> 16) * iw01 + (d10 >> 16) * iw10 + (d11 >> 16) * iw11 + (1 << 13)) >> 14;
-                Iv[s] = (short)iv; Ixv[s] = (short)ix; Iyv[s] = (short)iy;
-                sA11 += Ixv[s] * Ixv[s]; sA12 += Ixv[s] * Iyv[s]; sA22 += Iyv[s] * Iyv[s];
-            }
+            const uint8_t* p = sc.ipatch + offI[s] + xo;
+            const int iv = (p[0] * iw00 + p[1] * iw01 + p[SVO_LK_PATCH_PITCH] * iw10 + p[SVO_LK_PATCH_PITCH + 1] * iw11 + (1 << 8)) >> 9;
+            const int* dq = sc.dxy + offD[s];
+            const int d00 = dq[0], d01 = dq[1], d10 = dq[SVO_LK_DP], d11 = dq[SVO_LK_DP + 1];
+            const int ix = ((int)(short)d00 * iw00 + (int)(short)d01 * iw01 + (int)(short)d10 * iw10 + (int)(short)d11 * iw11 + (1 << 13)) >> 14;
+            const int iy = ((d00 >> 16) * iw00 + (d01 >> 16) * iw01 + (d10 >> 16) * iw10 + (d11 >> 16) * iw11 + (1 << 13)) >> 14;
+            Iv[s] = val[s] ? (int)(short)iv : 0;
+            Ixv[s] = val[s] ? (int)(short)ix : 0;
+            Iyv[s] = val[s] ? (int)(short)iy : 0;
+            sA11 += Ixv[s] * Ixv[s]; sA12 += Ixv[s] * Iyv[s]; sA22 += Iyv[s] * Iyv[s];
         }
         sA11 = Red::sum(sA11); sA12 = Red::sum(sA12); sA22 = Red::sum(sA22);
         const float A11 = fmul((float)sA11, FLT_SCALE);
@@ -365,12 +434,14 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         float pdx = 0.f, pdy = 0.f;
         for (int j = 0; j < cfg.max_iters; ++j) {
             const int inx = floor_int(cx), iny = floor_int(cy);
-            if (inx < -SVO_LK_WIN || inx >= J.w || iny < -SVO_LK_WIN || iny >= J.h) {
+            if ((unsigned)(inx + SVO_LK_WIN) >= (unsigned)(J.w + SVO_LK_WIN) ||
+                (unsigned)(iny + SVO_LK_WIN) >= (unsigned)(J.h + SVO_LK_WIN)) {   // window fully outside the level
                 if (level == 0) status = 0;
                 break;
             }
             ++iters;
-            if (inx < jx0 || inx + SVO_LK_WIN > jx0 + SVO_LK_JC || iny < jy0 || iny + SVO_LK_WIN + 1 > jy0 + SVO_LK_JR) {
+            if ((unsigned)(inx - jx0) > (unsigned)(SVO_LK_JC - SVO_LK_WIN) ||
+                (unsigned)(iny - jy0) > (unsigned)(SVO_LK_JR - SVO_LK_WIN - 1)) {
                 // the window left the staged patch: re-centre it
                 jx0 = (inx - 5) & ~3;
                 jy0 = iny - 3;
@@ -387,30 +458,30 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             typename LkAcc<LANES>::type sb1 = 0, sb2 = 0;   // <= 4 pixels per lane fit 32 bits
 #pragma unroll
             for (int s = 0; s < SLOTS; ++s) {
-                const int idx = lane + s * LANES;
-                if (idx < SVO_LK_NPIX) {
-                    const int wy = idx / SVO_LK_WIN, wx = idx - wy * SVO_LK_WIN;
-                    const unsigned short* q = jbase + wy * SVO_LK_JC + wx;
-                    const int v = dp2a_lo_su(jb, q[SVO_LK_JC], dp2a_lo_su(jt, q[0], 1 << 8));
-                    const int diff = (v >> 9) - Iv[s];
-                    sb1 += diff * Ixv[s];
-                    sb2 += diff * Iyv[s];
-                }
+                const unsigned short* q = jbase + offJ[s];
+                const int v = dp2a_lo_su(jb, q[SVO_LK_JC], dp2a_lo_su(jt, q[0], 1 << 8));
+                const int diff = (v >> 9) - Iv[s];
+                sb1 += diff * Ixv[s];
+                sb2 += diff * Iyv[s];
             }
-            const long long tb1 = Red::sum64(sb1), tb2 = Red::sum64(sb2);
-            const float b1 = fmul((float)tb1, FLT_SCALE);
-            const float b2 = fmul((float)tb2, FLT_SCALE);
+            float b1, b2;
+            Red::sum2f(sb1, sb2, b1, b2);
+            b1 = fmul(b1, FLT_SCALE);
+            b2 = fmul(b2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);
             const float ddy = fmul(fsub(fmul(A12, b1), fmul(A11, b2)), D);
 #ifdef SVO_LK_TRACE
-            printf("   b=(%lld,%lld) d=(%g,%g) cy=%.9g iny=%d\n", (long long)tb1, (long long)tb2, ddx, ddy, cy, iny);
+            printf("   b=(%g,%g) d=(%g,%g) cy=%.9g iny=%d\n", b1, b2, ddx, ddy, cy, iny);
 #endif
             cx = fadd(cx, ddx);
             cy = fadd(cy, ddy);
             nx = fadd(cx, half_win);
             ny = fadd(cy, half_win);
-            if ((double)ddx * (double)ddx + (double)ddy * (double)ddy <= cfg.eps_sq) break;
-            if (j > 0 && (double)fabsf(fadd(ddx, pdx)) < 0.01 && (double)fabsf(fadd(ddy, pdy)) < 0.01) {
+            const float d2 = fadd(fmul(ddx, ddx), fmul(ddy, ddy));
+            if (d2 < eps_lo) break;
+            if (!(d2 > eps_hi) && (double)ddx * (double)ddx + (double)ddy * (double)ddy <= cfg.eps_sq) break;
+            // std::abs(float) < 0.01 (a double): 0.01f is the largest float32 below 0.01, so `<= 0.01f` is the same test
+            if (j > 0 && fabsf(fadd(ddx, pdx)) <= 0.01f && fabsf(fadd(ddy, pdy)) <= 0.01f) {
                 nx = fsub(nx, fmul(ddx, 0.5f));
                 ny = fsub(ny, fmul(ddy, 0.5f));
                 break;

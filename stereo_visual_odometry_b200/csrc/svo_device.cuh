@@ -41,7 +41,8 @@ struct BucketGeom {
 };
 
 struct SeqState {
-    int slot_unused_;    // (pyramid slots are a host-known ring: frame f -> slot f % 3)
+    int spec_bad;        // 1: the speculative KLT results for the NEXT frame must not be used (this frame kept the
+                         // old pyramids, vo.cpp:179-181, so they were tracked from the wrong images)
     int n_feat;          // currentVOFeatures.size()
     int n_bucketed;
     int n_matched;
@@ -50,10 +51,22 @@ struct SeqState {
     int pnp_ok;
     int lk_iters;
     int frame_id;
-    int pad_;
+    int fs_from_inliers; // 1: the feature set is the inlier list of the last frame (fs[i] == matched[inl_idx[i]] at its
+                         // t1 position), i.e. the tracked-candidate cache is addressable; 0: it holds t0 positions
     double R[9];         // rotation      (vo.h:262)
     double t[3];         // translation   (vo.h:263)
     double last_T[16];   // last_transform (vo.h:264)
+};
+
+// What pnp_final_a hands to pnp_final_b (the LM refit runs off the critical chain, while the next frame's
+// bucketing / KLT / hypotheses already overwrite the per-frame counters of SeqState).
+struct FinalJob {
+    int action;          // 0: refit + gates; otherwise an svo_fail_reason to report without a refit
+    int n_in;            // inliers of the winning hypothesis
+    int enough;          // n_in >= FEATURES_THRESHOLD
+    int n_bucketed, n_matched, retry, lk_iters;
+    int pad_;
+    double R[9], t[3];   // winning hypothesis
 };
 
 // All device pointers of a context, passed by value to the kernels.
@@ -80,7 +93,18 @@ struct DevArrays {
     int* hyp_samples;                 // [n_seq][H][5] OpenCV-order sample indices (-1 = invalid)
     unsigned* rng_raw;                // [SVO_RNG_TABLE] cv::RNG((uint64)-1) output stream
     int* inl_idx;                     // [n_seq][cap] ascending inlier indices
-    int* klt_next;                    // [n_seq] next feature index for the persistent KLT warps
+    int* klt_next;                    // [n_seq] next todo index for the persistent KLT warps
+    // speculative KLT cache (see svo_kernels.cu "speculative tracking"): circular-matching results of
+    //   F: the FAST winner of every bucket of the previous left image   [frame & 1][n_seq][nb]
+    //   T: every matched feature of the previous frame at its t1 position [n_seq][cap]
+    // entry = 4 leg outputs + status bits (bit 4 = keep) + LK iteration count
+    float2* specF_pts; uint8_t* specF_st; int* specF_it;
+    float2* specT_pts; uint8_t* specT_st; int* specT_it;
+    int* cntF; int* cntT;             // [n_seq] work counters of the two speculative kernels
+    int* listF; int* nF;              // [n_seq][nb], [n_seq]: buckets holding a thr-20 FAST winner (any order)
+    int* todo; int* n_todo;           // [n_seq][cap], [n_seq]: bucketed features whose result was not cached
+    FinalJob* job;                    // [n_seq]
+    int nb;                           // buckets per sequence
     int cap;                          // per-sequence feature capacity
     int n_seq;
     int n_hyp;

@@ -28,6 +28,19 @@ struct WarpRed {
         const unsigned hi = __reduce_add_sync(0xffffffffu, u >> 16);
         return ((long long)hi << 16) + (long long)lo - (32ll << 27);
     }
+    // exact sums of the two per-lane mismatch accumulators as float32.  A lane holds <= 4 pixels (|v| < 2^27);
+    // when every lane is below 2^26 the warp total fits 32 bits and one REDUX each is exact, otherwise the
+    // split 64-bit path runs (warp-uniform branch).
+    static __device__ __forceinline__ void sum2f(int a, int b, float& fa, float& fb) {
+        const bool big = max(abs(a), abs(b)) >= (1 << 26);
+        if (__any_sync(0xffffffffu, big)) {
+            fa = (float)sum64(a);
+            fb = (float)sum64(b);
+        } else {
+            fa = (float)__reduce_add_sync(0xffffffffu, a);
+            fb = (float)__reduce_add_sync(0xffffffffu, b);
+        }
+    }
     static __device__ __forceinline__ void sync() { __syncwarp(); }
 };
 
@@ -317,16 +330,23 @@ void launch_first_frame(const DevArrays& d, cudaStream_t st) {
 // block scan over the (tile, warp) popcounts.
 constexpr int BM_TILES = 16;   // nb <= 16384 (checked in svo_create)
 __global__ void __launch_bounds__(1024)
-bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
+bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int specbuf, int use_spec) {
     __shared__ int sm[33];
     __shared__ int wcount[BM_TILES * 32];
+    __shared__ int sm_todo, sm_iters;
     const int seq = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     SeqState* s = d.state + seq;
+    if (tid == 0) {
+        sm_todo = 0;
+        sm_iters = 0;
+    }
     const long long fo = (long long)seq * d.cap;
     unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
     unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
     unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
     const int n = s->n_feat;
+    const bool spec_ok = use_spec != 0 && s->spec_bad == 0;
+    const bool trk_ok = s->fs_from_inliers != 0;
 
     for (int i = tid; i < n; i += 1024) {
         const float2 p = d.fs_xy[fo + i];
@@ -340,6 +360,7 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
 
     const int ntiles = (bg.nb + 1023) >> 10;
     unsigned long long w1[BM_TILES], kbv[BM_TILES];
+    unsigned isA = 0;   // bit j: the winner of tile j is this bucket's thr-20 FAST winner (cached by klt_spec_fast_kernel)
     int c1 = 0;
 #pragma unroll
     for (int j = 0; j < BM_TILES; ++j) {
@@ -350,6 +371,7 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
             const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
             kbv[j] = ld_key(keyB + b);
             w1[j] = kt > ka ? kt : ka;
+            isA |= (ka != 0ull && !(kt > ka)) ? (1u << j) : 0u;
             c1 += (w1[j] != 0ull) ? 1 : 0;
             keyT[b] = 0ull;   // consumed: ready for the next frame / the next FAST pass of this parity
             keyA[b] = 0ull;
@@ -367,7 +389,12 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
         const unsigned long long kb = kbv[j];
         // second append: the survivors come first in the feature order, so a thr/4 FAST feature only wins
         // with a strictly greater score
-        if (retry && kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) wv = kb;
+        if (retry && kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) {
+            // a thr-5 winner that differs from the cached thr-20 one was not tracked ahead of time
+            // (a bucket with a thr-20 corner has kb == ka, which never replaces: only un-cached winners get here)
+            isA &= ~(1u << j);
+            wv = kb;
+        }
         w1[j] = wv;
         ballots[j] = __ballot_sync(0xffffffffu, wv != 0ull);
         if (lane == 0) wcount[j * 32 + wid] = __popc(ballots[j]);
@@ -401,24 +428,52 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf) {
                 d.bk_xy[fo + off] = p;
                 d.bk_age[fo + off] = age;
                 d.bk_str[fo + off] = str;
+                // circular-matching result from the speculative cache, else queue the feature for klt_kernel
+                long long src = -1;
+                const float2* sp = nullptr;
+                const uint8_t* sst = nullptr;
+                const int* sit = nullptr;
+                if (spec_ok) {
+                    if (order >= SVO_FAST_ORDER_BASE) {
+                        if ((isA >> j) & 1u) {
+                            src = ((long long)specbuf * d.n_seq + seq) * bg.nb + (j << 10) + tid;
+                            sp = d.specF_pts; sst = d.specF_st; sit = d.specF_it;
+                        }
+                    } else if (trk_ok) {
+                        src = fo + d.inl_idx[fo + order];
+                        sp = d.specT_pts; sst = d.specT_st; sit = d.specT_it;
+                    }
+                }
+                if (src >= 0) {
+                    d.lk_L1[fo + off] = sp[src * 4 + 0];
+                    d.lk_R1[fo + off] = sp[src * 4 + 1];
+                    d.lk_R0[fo + off] = sp[src * 4 + 2];
+                    d.lk_C[fo + off] = sp[src * 4 + 3];
+                    d.lk_status[fo + off] = sst[src];
+                    atomicAdd(&sm_iters, sit[src]);
+                } else {
+                    d.todo[fo + atomicAdd(&sm_todo, 1)] = off;
+                }
             }
         }
     }
+    __syncthreads();
     if (tid == 0) {
         s->n_bucketed = min(total, d.cap);
         s->retry = retry ? 1 : 0;
-        s->lk_iters = 0;
+        s->lk_iters = sm_iters;
         s->frame_id += 1;
         d.klt_next[seq] = 0;
+        d.n_todo[seq] = sm_todo;
     }
 }
-void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf,
-                         cudaStream_t st) {
-    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, keybuf);
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf, int specbuf,
+                         int use_spec, cudaStream_t st) {
+    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, keybuf, specbuf, use_spec);
 }
 
 // ============================================================================
-// KLT: one warp per feature, the whole circular chain L0->L1->R1->R0->L0 in one launch
+// KLT: one warp per feature, the whole circular chain L0->L1->R1->R0->L0 per work item
 constexpr int KLT_WARPS = 8;
 __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom& pg) {
     LkPyramid p;
@@ -431,69 +486,196 @@ __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom
     }
     return p;
 }
-// Persistent warps: every warp pulls the next feature index from a per-sequence counter, so warps that
-// finish a quickly converging feature immediately start another one (the per-feature cost varies 10x).
+struct Circ {
+    float2 a, b, c, e;   // pL1, pR1, pR0, pL0'
+    unsigned st;         // bit l = status of leg l, bit 4 = keep (findClosePoints + status AND + bounds)
+    int iters;
+};
 // The four legs L0->L1->R1->R0->L0 (vo.cpp:203-215) run in ONE loop body to keep the code I-cache sized.
+// pyramid k: 0 = L0, 1 = L1, 2 = R1, 3 = R0 ; leg l tracks from pyramid l to pyramid (l + 1) & 3
+__device__ __forceinline__ Circ track_circular(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc,
+                                               const long long* base, float2 p0, int lane, LkScratch& sc) {
+    float2 pts[5];
+    pts[0] = p0;
+    int iters = 0;
+    unsigned st = 0;
+#pragma unroll 1
+    for (int leg = 0; leg < 4; ++leg) {
+        const LkPyramid I = make_pyr(d.pyr + base[leg], pg);
+        const LkPyramid J = make_pyr(d.pyr + base[(leg + 1) & 3], pg);
+        int it;
+        float ox, oy;
+        const float ix = leg == 0 ? pts[0].x : (leg == 1 ? pts[1].x : (leg == 2 ? pts[2].x : pts[3].x));
+        const float iy = leg == 0 ? pts[0].y : (leg == 1 ? pts[1].y : (leg == 2 ? pts[2].y : pts[3].y));
+        const int ok = lk_track_feature<32, WarpRed>(I, J, pc.lk, ix, iy, lane, sc, ox, oy, it);
+        st |= ok ? (1u << leg) : 0u;
+        iters += it;
+        if (leg == 0) pts[1] = make_float2(ox, oy);
+        else if (leg == 1) pts[2] = make_float2(ox, oy);
+        else if (leg == 2) pts[3] = make_float2(ox, oy);
+        else pts[4] = make_float2(ox, oy);
+    }
+    Circ r;
+    r.a = pts[1]; r.b = pts[2]; r.c = pts[3]; r.e = pts[4];
+    // findClosePoints + status AND (vo.cpp:217-230) + in-bounds test (vo.cpp:341-359): the keep bit
+    bool ok = st == 15u && close_points(p0.x, p0.y, r.e.x, r.e.y, pc.circular_threshold);
+    if (pc.check_bounds) {
+        const int W = pc.width, H = pc.height;
+        ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(r.a.x, r.a.y, W, H) && in_bounds(r.c.x, r.c.y, W, H) &&
+             in_bounds(r.b.x, r.b.y, W, H);
+    }
+    r.st = st | (ok ? 16u : 0u);
+    r.iters = iters;
+    return r;
+}
+__device__ __forceinline__ void circ_bases(const PyrGeom& pg, int seq, int slot_prev, int slot_cur, long long* base) {
+    base[0] = pg.base(seq, slot_prev, 0);
+    base[1] = pg.base(seq, slot_cur, 0);
+    base[2] = pg.base(seq, slot_cur, 1);
+    base[3] = pg.base(seq, slot_prev, 1);
+}
+
+// Persistent warps: every warp pulls the next work item from a per-sequence counter, so warps that finish a
+// quickly converging feature immediately start another one (the per-feature cost varies 10x).
+//
+// klt_kernel tracks the bucketed features listed in d.todo (the ones whose result was not found in the
+// speculative cache by bucket_merge_kernel; all of them when speculation is off).
 __global__ void __launch_bounds__(KLT_WARPS * 32)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     SeqState* s = d.state + seq;
-    const int n = s->n_bucketed;
-    // pyramid k: 0 = L0, 1 = L1, 2 = R1, 3 = R0 ; leg l tracks from pyramid l to pyramid (l + 1) & 3
-    const long long base[4] = {pg.base(seq, slot_prev, 0), pg.base(seq, slot_cur, 0), pg.base(seq, slot_cur, 1),
-                               pg.base(seq, slot_prev, 1)};
+    const int n = d.n_todo[seq];
+    if (n <= 0) return;
+    long long base[4];
+    circ_bases(pg, seq, slot_prev, slot_cur, base);
     int* counter = d.klt_next + seq;
+    const int* todo = d.todo + (long long)seq * d.cap;
     for (;;) {
-        int f = 0;
-        if (lane == 0) f = atomicAdd(counter, 1);
-        f = __shfl_sync(0xffffffffu, f, 0);
-        if (f >= n) break;
+        int t = 0;
+        if (lane == 0) t = atomicAdd(counter, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n) break;
+        const int f = todo[t];
         const long long o = (long long)seq * d.cap + f;
-        const float2 p0 = d.bk_xy[o];
-        float2 pts[5];
-        pts[0] = p0;
-        int iters = 0;
-        unsigned st = 0;
-#pragma unroll 1
-        for (int leg = 0; leg < 4; ++leg) {
-            const LkPyramid I = make_pyr(d.pyr + base[leg], pg);
-            const LkPyramid J = make_pyr(d.pyr + base[(leg + 1) & 3], pg);
-            int it;
-            float ox, oy;
-            const float ix = leg == 0 ? pts[0].x : (leg == 1 ? pts[1].x : (leg == 2 ? pts[2].x : pts[3].x));
-            const float iy = leg == 0 ? pts[0].y : (leg == 1 ? pts[1].y : (leg == 2 ? pts[2].y : pts[3].y));
-            const int ok = lk_track_feature<32, WarpRed>(I, J, pc.lk, ix, iy, lane, patch[wid], ox, oy, it);
-            st |= ok ? (1u << leg) : 0u;
-            iters += it;
-            if (leg == 0) pts[1] = make_float2(ox, oy);
-            else if (leg == 1) pts[2] = make_float2(ox, oy);
-            else if (leg == 2) pts[3] = make_float2(ox, oy);
-            else pts[4] = make_float2(ox, oy);
-        }
+        const Circ r = track_circular(d, pg, pc, base, d.bk_xy[o], lane, patch[wid]);
         if (lane == 0) {
-            const float2 a = pts[1], b = pts[2], c = pts[3], e = pts[4];
-            // findClosePoints + status AND (vo.cpp:217-230) + in-bounds test (vo.cpp:341-359): the is_ok bit
-            bool ok = st == 15u && close_points(p0.x, p0.y, e.x, e.y, pc.circular_threshold);
-            if (pc.check_bounds) {
-                const int W = pc.width, H = pc.height;
-                ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(a.x, a.y, W, H) && in_bounds(c.x, c.y, W, H) &&
-                     in_bounds(b.x, b.y, W, H);
-            }
-            d.lk_L1[o] = a;
-            d.lk_R1[o] = b;
-            d.lk_R0[o] = c;
-            d.lk_C[o] = e;
-            d.lk_status[o] = (uint8_t)(st | (ok ? 16u : 0u));
-            atomicAdd(&s->lk_iters, iters);
+            d.lk_L1[o] = r.a;
+            d.lk_R1[o] = r.b;
+            d.lk_R0[o] = r.c;
+            d.lk_C[o] = r.e;
+            d.lk_status[o] = (uint8_t)r.st;
+            atomicAdd(&s->lk_iters, r.iters);
         }
     }
+}
+int klt_resident_blocks_per_sm() {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, klt_kernel, KLT_WARPS * 32, 0) != cudaSuccess || nb < 1) nb = 3;
+    return nb;
 }
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st) {
     dim3 grid(blocks_per_seq, d.n_seq);
     klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
+}
+
+// ---- speculative tracking -------------------------------------------------------------------------------------
+// Which features enter circular matching of frame f is only known after the PnP of frame f - 1 (inliers) --
+// but every candidate is known earlier and tracking one feature does not depend on any other:
+//   F(f): the FAST winner of each bucket of left image f - 1   (known once image f - 1 and f are ingested)
+//   T(f): every feature matched in frame f - 1, at its t1 position, young enough (known after select(f - 1))
+// Both are tracked ahead of time on their own SM partition while PnP(f - 1) runs; bucket_merge_kernel(f) then
+// looks its winners up in this cache.  Anything not cached (low-threshold retry, failed PnP, ...) goes through
+// klt_kernel afterwards, so the cache never changes a result, only when it is computed.
+// the buckets that hold a thr-20 FAST winner, as an unordered list (one warp-aggregated atomic per 32 buckets)
+__global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, BucketGeom bg, int keybuf) {
+    const int seq = blockIdx.y, lane = threadIdx.x & 31;
+    const int b = blockIdx.x * 256 + threadIdx.x;
+    const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
+    const bool has = b < bg.nb && ld_key(keyA + b) != 0ull;
+    const unsigned m = __ballot_sync(0xffffffffu, has);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(d.nF + seq, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (has) d.listF[(long long)seq * bg.nb + base + __popc(m & ((1u << lane) - 1u))] = b;
+}
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int keybuf,
+                     int specbuf) {
+    __shared__ LkScratch patch[KLT_WARPS];
+    const int seq = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long base[4];
+    circ_bases(pg, seq, slot_prev, slot_cur, base);
+    const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
+    const long long so = ((long long)specbuf * d.n_seq + seq) * bg.nb;
+    const int* list = d.listF + (long long)seq * bg.nb;
+    const int n = d.nF[seq];
+    int* counter = d.cntF + seq;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(counter, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n) break;
+        const int b = list[t];
+        const unsigned order = bucket_key_order(ld_key(keyA + b));
+        const int pix = (int)(order - SVO_FAST_ORDER_BASE);
+        const int y = pix / pc.width;
+        const float2 p0 = make_float2((float)(pix - y * pc.width), (float)y);
+        const Circ r = track_circular(d, pg, pc, base, p0, lane, patch[wid]);
+        if (lane == 0) {
+            const long long o = so + b;
+            d.specF_pts[o * 4 + 0] = r.a;
+            d.specF_pts[o * 4 + 1] = r.b;
+            d.specF_pts[o * 4 + 2] = r.c;
+            d.specF_pts[o * 4 + 3] = r.e;
+            d.specF_st[o] = (uint8_t)r.st;
+            d.specF_it[o] = r.iters;
+        }
+    }
+}
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur) {
+    __shared__ LkScratch patch[KLT_WARPS];
+    const int seq = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long base[4];
+    circ_bases(pg, seq, slot_prev, slot_cur, base);
+    const int n = d.state[seq].n_matched;
+    const long long fo = (long long)seq * d.cap;
+    int* counter = d.cntT + seq;
+    for (;;) {
+        int k = 0;
+        if (lane == 0) k = atomicAdd(counter, 1);
+        k = __shfl_sync(0xffffffffu, k, 0);
+        if (k >= n) break;
+        if (d.m_age[fo + k] >= bg.age_threshold) continue;   // bucketing drops it (feature_set.cpp:24)
+        const Circ r = track_circular(d, pg, pc, base, d.m_L1[fo + k], lane, patch[wid]);
+        if (lane == 0) {
+            const long long o = fo + k;
+            d.specT_pts[o * 4 + 0] = r.a;
+            d.specT_pts[o * 4 + 1] = r.b;
+            d.specT_pts[o * 4 + 2] = r.c;
+            d.specT_pts[o * 4 + 3] = r.e;
+            d.specT_st[o] = (uint8_t)r.st;
+            d.specT_it[o] = r.iters;
+        }
+    }
+}
+void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
+                          int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st) {
+    cudaMemsetAsync(d.cntF, 0, sizeof(int) * d.n_seq, st);
+    cudaMemsetAsync(d.nF, 0, sizeof(int) * d.n_seq, st);
+    spec_fast_list_kernel<<<dim3((bg.nb + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg, keybuf);
+    dim3 grid(blocks_per_seq, d.n_seq);
+    klt_spec_fast_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur, keybuf, specbuf);
+}
+void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
+                         int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st) {
+    dim3 grid(blocks_per_seq, d.n_seq);   // d.cntT was reset by select_kernel
+    klt_spec_trk_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur);
 }
 
 __global__ void __launch_bounds__(KLT_WARPS * 32)
@@ -643,6 +825,9 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
             s->n_feat = total;
             s->n_inliers = 0;
             s->pnp_ok = 0;
+            s->spec_bad = n == 0 ? 1 : 0;   // the old pyramids stay: what was tracked ahead for the next frame is void
+            s->fs_from_inliers = 0;         // the feature set now holds the matched set at t0 positions
+            d.cntT[seq] = 0;
         }
     }
 }
@@ -759,33 +944,45 @@ struct BlockInlierEval {
     }
 };
 
-__device__ void write_result(const DevArrays& d, int seq, int success, int reason, const double* T) {
+__device__ void write_result(const DevArrays& d, int seq, const FinalJob& j, int success, int reason, int pnp_ok,
+                             int n_inliers, const double* T) {
     SeqState* s = d.state + seq;
     svo_frame_result* r = d.result + seq;
     r->success = success;
     r->reason = reason;
-    r->n_bucketed = s->n_bucketed;
-    r->n_matched = s->n_matched;
-    r->n_inliers = s->n_inliers;
-    r->retry = s->retry;
-    r->pnp_ok = s->pnp_ok;
-    r->lk_iters = s->lk_iters;
+    r->n_bucketed = j.n_bucketed;
+    r->n_matched = j.n_matched;
+    r->n_inliers = n_inliers;
+    r->retry = j.retry;
+    r->pnp_ok = pnp_ok;
+    r->lk_iters = j.lk_iters;
     for (int i = 0; i < 9; ++i) r->R[i] = s->R[i];
     for (int i = 0; i < 3; ++i) r->t[i] = s->t[i];
     for (int i = 0; i < 16; ++i) r->transform[i] = T[i];
 }
 
-__global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, PipeConfig pc) {
+// cameraToWorld is split in two kernels.  pnp_final_a_kernel does what the NEXT frame depends on: the replay of
+// OpenCV's sequential RANSAC loop over the hypothesis scores, the inlier list of the winner and the feature-set
+// update (vo.cpp:115-121).  pnp_final_b_kernel refits the pose on the inliers (LM, FP64), applies the gates and
+// writes the frame result -- it only feeds the pose output, so it runs beside the next frame's chain.
+__global__ void __launch_bounds__(FIN_THREADS) pnp_final_a_kernel(DevArrays d, PipeConfig pc) {
     __shared__ int sm_i[33];
-    __shared__ double sm_acc[(FIN_THREADS / 32 + 1) * SVO_PNP_ACC];
     const int seq = blockIdx.x, tid = threadIdx.x;
-    const int lane = tid & 31, wid = tid >> 5;
     SeqState* s = d.state + seq;
+    FinalJob* job = d.job + seq;
     const long long fo = (long long)seq * d.cap;
     const int n = s->n_matched;
     const int min_n = max(4, pc.features_threshold);
+    if (tid == 0) {
+        job->n_bucketed = s->n_bucketed;
+        job->n_matched = n;
+        job->retry = s->retry;
+        job->lk_iters = s->lk_iters;
+        job->n_in = 0;
+        job->enough = 0;
+    }
     if (n <= min_n) {   // vo.cpp:82-84
-        if (tid == 0) write_result(d, seq, 0, SVO_REASON_FEW_FEATURES, s->last_T);
+        if (tid == 0) job->action = SVO_REASON_FEW_FEATURES;
         return;
     }
     // ---- winning hypothesis: replay of OpenCV's sequential adaptive RANSAC loop over the counts
@@ -802,7 +999,7 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         if (tid == 0) {
             s->pnp_ok = 0;
             s->n_inliers = 0;
-            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
+            job->action = SVO_REASON_PNP_FAILED;
         }
         return;
     }
@@ -820,8 +1017,9 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
     for (int t0 = 0; t0 < n; t0 += FIN_THREADS) {   // coalesced tiles, ascending order
         const int i = t0 + tid;
         bool in = false;
+        float2 q = make_float2(0.f, 0.f);
         if (i < n) {
-            const float2 q = uv[i];
+            q = uv[i];
             const float uvf[2] = {q.x, q.y};
             in = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf) <= pc.reproj_thr_sq;
         }
@@ -829,7 +1027,6 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         const int off = n_in + block_excl_scan<FIN_THREADS>(in ? 1 : 0, &tile_total, sm_i);
         if (in) {
             idx[off] = i;
-            const float2 q = uv[i];
             d.in_uv[fo + off] = q;
             d.X3u[(fo + off) * 3] = X3[3 * i];
             d.X3u[(fo + off) * 3 + 1] = X3[3 * i + 1];
@@ -838,76 +1035,98 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_kernel(DevArrays d, Pip
         n_in += tile_total;
     }
     __syncthreads();
-    // ---- LM refit on all inliers (uniform control flow across the block)
-    BlockInlierEval ev{d.X3u + fo * 3, d.in_uv + fo, idx, n_in, pc.K, sm_acc};
-    pnp_refine_lm(P, ev, 20);
-    bool finite = true;
-    for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
-    for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
-    if (!finite) {
-        if (tid == 0) {
-            s->pnp_ok = 0;
-            s->n_inliers = 0;
-            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
-        }
-        return;
-    }
     const bool enough = n_in >= pc.features_threshold;
     if (enough) {
-        // currentVOFeatures.points = pointsLeftT1; keep inliers (vo.cpp:115-121).  fs_* currently
-        // holds the matched set at t0 coordinates; idx[i] >= i so the in-order rewrite is safe
-        // per element only after a barrier: stage through registers.
+        // currentVOFeatures.points = pointsLeftT1; keep inliers (vo.cpp:115-121).  fs_* holds the matched set
+        // (t0 coordinates); entry i of the new set comes from matched entry idx[i] >= i, read from the m_* copies.
         for (int base = 0; base < n_in; base += FIN_THREADS) {
             const int i = base + tid;
-            float2 p = make_float2(0.f, 0.f);
-            int age = 0, str = 0;
             if (i < n_in) {
                 const int k = idx[i];
-                p = d.m_L1[fo + k];
-                age = d.m_age[fo + k];
-                str = d.m_str[fo + k];
-            }
-            if (i < n_in) {
-                d.fs_xy[fo + i] = p;
-                d.fs_age[fo + i] = age;
-                d.fs_str[fo + i] = str;
+                d.fs_xy[fo + i] = d.m_L1[fo + k];
+                d.fs_age[fo + i] = d.m_age[fo + k];
+                d.fs_str[fo + i] = d.m_str[fo + k];
             }
         }
     }
     if (tid == 0) {
         s->pnp_ok = 1;
         s->n_inliers = n_in;
-        for (int i = 0; i < 9; ++i) s->R[i] = P.R[i];   // rotation / translation overwritten on PnP success
-        for (int i = 0; i < 3; ++i) s->t[i] = P.t[i];
-        if (!enough) {   // vo.cpp:106-113
-            write_result(d, seq, 0, SVO_REASON_PNP_FAILED, s->last_T);
-            return;
+        if (enough) {
+            s->n_feat = n_in;
+            s->fs_from_inliers = 1;
         }
-        s->n_feat = n_in;
-        const double tn = sqrt(P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
-        const double ang = rotation_angle(P.R);
-        if (tn > pc.max_t_norm || ang > pc.max_r_norm) {   // vo.cpp:123-132
-            write_result(d, seq, 0, SVO_REASON_TOO_BIG, s->last_T);
-            return;
-        }
-        // getInverseTransform (vo.cpp:246-258): inverse of the rigid [R|t]
-        double T[16];
-        for (int i = 0; i < 3; ++i) {
-            for (int j = 0; j < 3; ++j) T[i * 4 + j] = P.R[j * 3 + i];
-            T[i * 4 + 3] = -(P.R[0 * 3 + i] * P.t[0] + P.R[1 * 3 + i] * P.t[1] + P.R[2 * 3 + i] * P.t[2]);
-        }
-        T[12] = T[13] = T[14] = 0.0;
-        T[15] = 1.0;
-        for (int i = 0; i < 16; ++i) s->last_T[i] = T[i];
-        write_result(d, seq, 1, SVO_REASON_OK, T);
+        job->action = 0;
+        job->n_in = n_in;
+        job->enough = enough ? 1 : 0;
+        for (int i = 0; i < 9; ++i) job->R[i] = P.R[i];
+        for (int i = 0; i < 3; ++i) job->t[i] = P.t[i];
     }
+}
+
+__global__ void __launch_bounds__(FIN_THREADS) pnp_final_b_kernel(DevArrays d, PipeConfig pc) {
+    __shared__ double sm_acc[(FIN_THREADS / 32 + 1) * SVO_PNP_ACC];
+    const int seq = blockIdx.x, tid = threadIdx.x;
+    SeqState* s = d.state + seq;
+    const FinalJob job = d.job[seq];
+    const long long fo = (long long)seq * d.cap;
+    if (job.action != 0) {
+        if (tid == 0) write_result(d, seq, job, 0, job.action, 0, 0, s->last_T);
+        return;
+    }
+    Pose P;
+    for (int i = 0; i < 9; ++i) P.R[i] = job.R[i];
+    for (int i = 0; i < 3; ++i) P.t[i] = job.t[i];
+    const int n_in = job.n_in;
+    // ---- LM refit on all inliers (uniform control flow across the block)
+    BlockInlierEval ev{d.X3u + fo * 3, d.in_uv + fo, d.inl_idx + fo, n_in, pc.K, sm_acc};
+    pnp_refine_lm(P, ev, 20);
+    bool finite = true;
+    for (int i = 0; i < 9; ++i) finite &= isfinite(P.R[i]);
+    for (int i = 0; i < 3; ++i) finite &= isfinite(P.t[i]);
+    if (tid != 0) return;
+    if (!finite) {   // cannot happen with >= 5 consistent points; reported as a PnP failure, pose state untouched
+        s->pnp_ok = 0;
+        s->n_inliers = 0;
+        write_result(d, seq, job, 0, SVO_REASON_PNP_FAILED, 0, 0, s->last_T);
+        return;
+    }
+    for (int i = 0; i < 9; ++i) s->R[i] = P.R[i];   // rotation / translation overwritten on PnP success
+    for (int i = 0; i < 3; ++i) s->t[i] = P.t[i];
+    if (!job.enough) {   // vo.cpp:106-113
+        write_result(d, seq, job, 0, SVO_REASON_PNP_FAILED, 1, n_in, s->last_T);
+        return;
+    }
+    const double tn = sqrt(P.t[0] * P.t[0] + P.t[1] * P.t[1] + P.t[2] * P.t[2]);
+    const double ang = rotation_angle(P.R);
+    if (tn > pc.max_t_norm || ang > pc.max_r_norm) {   // vo.cpp:123-132
+        write_result(d, seq, job, 0, SVO_REASON_TOO_BIG, 1, n_in, s->last_T);
+        return;
+    }
+    // getInverseTransform (vo.cpp:246-258): inverse of the rigid [R|t]
+    double T[16];
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) T[i * 4 + j] = P.R[j * 3 + i];
+        T[i * 4 + 3] = -(P.R[0 * 3 + i] * P.t[0] + P.R[1 * 3 + i] * P.t[1] + P.R[2 * 3 + i] * P.t[2]);
+    }
+    T[12] = T[13] = T[14] = 0.0;
+    T[15] = 1.0;
+    for (int i = 0; i < 16; ++i) s->last_T[i] = T[i];
+    write_result(d, seq, job, 1, SVO_REASON_OK, 1, n_in, T);
 }
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     dim3 grid((d.n_hyp + HYP_WARPS - 1) / HYP_WARPS, d.n_seq);
     pnp_hyp_kernel<<<grid, HYP_WARPS * 32, 0, st>>>(d, pc);
 }
+void launch_pnp_final_a(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+    pnp_final_a_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);
+}
+void launch_pnp_final_b(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
+    pnp_final_b_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);
+}
 void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
-    pnp_final_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);
+    launch_pnp_final_a(d, pc, st);
+    launch_pnp_final_b(d, pc, st);
 }
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     launch_pnp_hyp(d, pc, st);

@@ -32,15 +32,25 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
 
 // ---- per-frame pipeline stages (all sequences of the context per launch) ----
 void launch_first_frame(const DevArrays& d, cudaStream_t st);
-void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf,
-                         cudaStream_t st);
+// keybuf: FAST key buffer of the previous left image; specbuf / use_spec: speculative-cache buffer of this frame
+// and whether klt_spec_fast / klt_spec_trk ran for it (0: every bucketed feature is queued for launch_klt)
+void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf, int specbuf,
+                         int use_spec, cudaStream_t st);
+// speculative circular matching of the candidates of the coming frame (results looked up by bucket_merge)
+void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
+                          int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st);
+void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
+                         int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st);
+int klt_resident_blocks_per_sm();   // persistent KLT blocks that fit one SM (occupancy query)
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st);
 void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
                    cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
-void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
+void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);     // a then b
+void launch_pnp_final_a(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);   // RANSAC replay, inliers, feature set
+void launch_pnp_final_b(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);   // LM refit, gates, frame result
 void launch_pnp_samples(const DevArrays& d, cudaStream_t st);   // standalone (select_kernel fuses it)
 
 // ---- stage-level helpers used by the stateless API ----

@@ -89,6 +89,8 @@ static void build_pyr(HostPyr& hp, const uint8_t* img, int w, int h, int stride,
     }
 }
 
+static int* g_iters_out = nullptr;   // optional per-feature iteration counts (analysis scripts)
+void hc_lk_set_iters_out(int* p) { g_iters_out = p; }
 int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, int max_level, int max_iters,
           double eps, float min_eig, const float* pts, int n, float* out, uint8_t* status) {
     HostPyr I, J;
@@ -99,6 +101,7 @@ int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, in
     cfg.max_iters = max_iters;
     cfg.eps_sq = eps * eps;
     cfg.min_eig = min_eig;
+    lk_config_finish(cfg);
     static LkScratch patch;
     int total_iters = 0;
     for (int i = 0; i < n; ++i) {
@@ -109,6 +112,7 @@ int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, in
         out[2 * i] = ox;
         out[2 * i + 1] = oy;
         total_iters += it;
+        if (g_iters_out) g_iters_out[i] = it;
     }
     return total_iters;
 }
