@@ -93,7 +93,9 @@ struct svo_ctx {
     DevArrays d;
     cudaStream_t stream = nullptr;      // dependent chain (bucket .. inliers) and everything synchronous
     cudaStream_t stream_in = nullptr;   // ingest of the next frame (H2D, pyramid, FAST)
-    cudaStream_t stream_k = nullptr;    // speculative KLT
+    cudaStream_t stream_k = nullptr;    // speculative KLT of the FAST-winner candidates (and the un-cached fallback)
+    cudaStream_t stream_k2 = nullptr;   // speculative KLT of the matched-feature candidates (same partition)
+    cudaEvent_t ev_spf[4] = {nullptr, nullptr, nullptr, nullptr};   // FAST-winner candidates of frame f tracked
     cudaStream_t stream_fb = nullptr;   // pose refit + result
     cudaStream_t stream_full = nullptr; // whole-GPU stream for serial frames (== stream when there are no partitions)
     int klt_blocks_full = 0;            // persistent KLT blocks per sequence on the whole GPU
@@ -245,7 +247,7 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
             unsigned ngrp = 32;
             CUgreenCtx gc[3] = {nullptr, nullptr, nullptr};
             CUdevResourceDesc dc[3];
-            CUstream st[4] = {nullptr, nullptr, nullptr, nullptr};
+            CUstream st[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
             const bool dbg = getenv("SVO_DEBUG") != nullptr;
             int step = 0;
             auto TRY = [&](CUresult x) {
@@ -285,11 +287,13 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[1], gc[0], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[2], gc[1], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[3], gc[2], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[4], gc[2], CU_STREAM_NON_BLOCKING, -1));
             if (ok) {
                 c->stream = (cudaStream_t)st[0];
                 c->stream_fb = (cudaStream_t)st[1];
                 c->stream_in = (cudaStream_t)st[2];
                 c->stream_k = (cudaStream_t)st[3];
+                c->stream_k2 = (cudaStream_t)st[4];
                 for (int i = 0; i < 3; ++i) c->green[i] = gc[i];
                 c->sm_chain = (int)sm_cnt[0];
                 c->sm_in = (int)sm_cnt[1];
@@ -307,6 +311,7 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
         CU(cudaStreamCreateWithFlags(&c->stream_fb, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&c->stream_in, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&c->stream_k, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->stream_k2, cudaStreamNonBlocking));
         c->stream_full = c->stream;
     }
     return SVO_OK;
@@ -323,6 +328,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_trk[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_spf[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_fa[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_fb[i], cudaEventDisableTiming));
     }
@@ -464,13 +470,14 @@ extern "C" svo_ctx* svo_create(const svo_params* p) {
 extern "C" void svo_destroy(svo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->p.device);
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb})
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb})
         if (st) cudaStreamSynchronize(st);
     for (void* q : c->allocs) cudaFree(q);
     for (int i = 0; i < 4; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
         if (c->ev_trk[i]) cudaEventDestroy(c->ev_trk[i]);
+        if (c->ev_spf[i]) cudaEventDestroy(c->ev_spf[i]);
         if (c->ev_fa[i]) cudaEventDestroy(c->ev_fa[i]);
         if (c->ev_fb[i]) cudaEventDestroy(c->ev_fb[i]);
     }
@@ -478,7 +485,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
         cudaStreamSynchronize(c->stream_full);
         cudaStreamDestroy(c->stream_full);
     }
-    for (cudaStream_t st : {c->stream_k, c->stream_fb})
+    for (cudaStream_t st : {c->stream_k, c->stream_k2, c->stream_fb})
         if (st) cudaStreamDestroy(st);
     for (int i = 0; i < SVO_RESULT_RING; ++i)
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
@@ -577,13 +584,20 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         CU(cudaStreamWaitEvent(sP, c->ev_in[e], 0));
     }
     if (spec && !first) {
+        // the two candidate classes run side by side, each on half of the partition's block slots: F(f) as soon
+        // as image f is there (typically a frame ahead), T(f) the moment select(f - 1) has produced the matched list
+        const int half = c->klt_blocks_k > 1 ? c->klt_blocks_k / 2 : 1;
+        cudaStream_t sK2 = c->stream_k2;
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
-        launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k, prev, cur, prev, (int)(f & 1), sK);
-        CU(cudaStreamWaitEvent(sK, c->ev_sel[e1], 0));
-        launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k, prev, cur, sK);
-        CU(cudaEventRecord(c->ev_trk[e], sK));
+        launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, half, prev, cur, prev, (int)(f & 1), sK);
+        CU(cudaEventRecord(c->ev_spf[e], sK));
+        CU(cudaStreamWaitEvent(sK2, c->ev_in[e], 0));
+        CU(cudaStreamWaitEvent(sK2, c->ev_sel[e1], 0));
+        launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, sK2);
+        CU(cudaEventRecord(c->ev_trk[e], sK2));
+        CU(cudaStreamWaitEvent(sP, c->ev_spf[e], 0));
         CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
-        c->launches += 2;
+        c->launches += 3;
     }
     if (c->timers) cudaEventRecord(c->ev[1], sP);
     if (first) {
@@ -634,7 +648,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (!tm) {
         CU(cudaEventRecord(c->ev_fb[e], sB));
     } else {   // a later frame may run on the partitions again: it finds every event of this frame signalled
-        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
+        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_spf[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
     }
     CU(cudaGetLastError());
     if (c->timers) {
@@ -751,14 +765,14 @@ extern "C" int svo_process_frame(svo_ctx* c, const uint8_t* left, const uint8_t*
 extern "C" int svo_synchronize(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     CU(cudaSetDevice(c->p.device));
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     return SVO_OK;
 }
 
 extern "C" int svo_pipeline_info(svo_ctx* c, int out[8]) {
     if (!c || !out) return fail(SVO_ERR_INVALID, "NULL argument");
     CU(cudaSetDevice(c->p.device));
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     int n_todo = 0;
     CU(cudaMemcpy(&n_todo, c->d.n_todo, sizeof(int), cudaMemcpyDeviceToHost));
     out[0] = c->spec ? 1 : 0;
@@ -786,7 +800,7 @@ extern "C" int svo_stream_join(svo_ctx* c) {
 extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
     if (!c || !out || seq < 0 || seq >= c->d.n_seq) return fail(SVO_ERR_INVALID, "bad argument");
     CU(cudaSetDevice(c->p.device));
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     CU(cudaMemcpy(out, c->d.result + seq, sizeof(svo_frame_result), cudaMemcpyDeviceToHost));
     return SVO_OK;
 }
@@ -794,7 +808,7 @@ extern "C" int svo_get_result(svo_ctx* c, int seq, svo_frame_result* out) {
 extern "C" int svo_get_tap(svo_ctx* c, int seq, int which, int cap, float* f_out, int* i_out, uint8_t* u8_out) {
     if (!c || seq < 0 || seq >= c->d.n_seq || cap < 0) return fail(SVO_ERR_INVALID, "bad argument");
     CU(cudaSetDevice(c->p.device));
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
     SeqState s;
     CU(cudaMemcpy(&s, c->d.state + seq, sizeof(s), cudaMemcpyDeviceToHost));
     const DevArrays& d = c->d;
