@@ -102,6 +102,9 @@ struct svo_ctx {
     void* green[3] = {nullptr, nullptr, nullptr};   // CUgreenCtx of the chain / ingest / KLT partitions
     int sm_chain = 0, sm_in = 0, sm_k = 0;          // SMs of each partition (0: no partitioning)
     bool spec = false;                  // speculative tracking on
+    struct TraceRec { const char* name; long long frame; int stream; cudaEvent_t a, b; };
+    std::vector<TraceRec> trace;        // SVO_TRACE=<file>: per-kernel timeline of frames 30..45, dumped by svo_destroy
+    const char* trace_path = nullptr;
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
@@ -446,6 +449,7 @@ static svo_ctx* ctx_create(const svo_params* p, int cap_override, bool pipeline_
     }
     svo_ctx* c = new svo_ctx();
     c->pipeline_ctx = pipeline_ctx;
+    c->trace_path = pipeline_ctx ? getenv("SVO_TRACE") : nullptr;
     if (ctx_init(c, p, cap_override) != SVO_OK) {
         std::string keep = g_err;
         svo_destroy(c);
@@ -467,11 +471,13 @@ extern "C" svo_ctx* svo_create(const svo_params* p) {
     return ctx_create(p, 0);
 }
 
+static void trace_dump(svo_ctx* c);
 extern "C" void svo_destroy(svo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->p.device);
     for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb})
         if (st) cudaStreamSynchronize(st);
+    trace_dump(c);
     for (void* q : c->allocs) cudaFree(q);
     for (int i = 0; i < 4; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
@@ -543,6 +549,45 @@ extern "C" int svo_get_stage_time(svo_ctx* c, int stage, double* ms_out, long lo
     return SVO_OK;
 }
 
+// timeline tracing (debug): brackets a launch with timing events on its stream
+struct TraceScope {
+    svo_ctx* c;
+    cudaStream_t st;
+    bool on;
+    size_t idx;
+    TraceScope(svo_ctx* c_, const char* name, int sid, cudaStream_t st_) : c(c_), st(st_), on(false), idx(0) {
+        if (!c->trace_path || c->frames < 30 || c->frames >= 46) return;
+        svo_ctx::TraceRec r{name, c->frames, sid, nullptr, nullptr};
+        cudaEventCreate(&r.a);
+        cudaEventCreate(&r.b);
+        cudaEventRecord(r.a, st);
+        c->trace.push_back(r);
+        idx = c->trace.size() - 1;
+        on = true;
+    }
+    ~TraceScope() {
+        if (on) cudaEventRecord(c->trace[idx].b, st);
+    }
+};
+static void trace_dump(svo_ctx* c) {
+    if (!c->trace_path || c->trace.empty()) return;
+    FILE* fp = fopen(c->trace_path, "w");
+    if (!fp) return;
+    fprintf(fp, "name,frame,stream,start_us,end_us\n");
+    for (const auto& r : c->trace) {
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, c->trace[0].a, r.a);
+        cudaEventElapsedTime(&b, c->trace[0].a, r.b);
+        fprintf(fp, "%s,%lld,%d,%.1f,%.1f\n", r.name, r.frame, r.stream, a * 1e3, b * 1e3);
+    }
+    fclose(fp);
+    for (auto& r : c->trace) {
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    c->trace.clear();
+}
+
 // serial frame: every launch of the frame goes to ONE stream that owns the whole GPU (per-stage timers; a
 // partitioned context whose caller is not streaming)
 static bool serial_frame(const svo_ctx* c, bool speculate) {
@@ -577,7 +622,11 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     cudaStream_t sI = tm ? sP : c->stream_in, sK = tm ? sP : c->stream_k, sB = tm ? sP : c->stream_fb;
     if (tm && !first) CU(cudaStreamWaitEvent(sP, c->ev_fb[e1], 0));   // the previous frame may have run on the partitions
     if (c->timers) cudaEventRecord(c->ev[0], sP);
-    const int n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
+    int n_ingest;
+    {
+        TraceScope ts(c, "ingest", 0, sI);
+        n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
+    }
     c->launches += n_ingest;
     if (!tm) {
         CU(cudaEventRecord(c->ev_in[e], sI));
@@ -589,11 +638,17 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         const int half = c->klt_blocks_k > 1 ? c->klt_blocks_k / 2 : 1;
         cudaStream_t sK2 = c->stream_k2;
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
-        launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, half, prev, cur, prev, (int)(f & 1), sK);
+        {
+            TraceScope ts(c, "spec_fast", 1, sK);
+            launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, half, prev, cur, prev, (int)(f & 1), sK);
+        }
         CU(cudaEventRecord(c->ev_spf[e], sK));
         CU(cudaStreamWaitEvent(sK2, c->ev_in[e], 0));
         CU(cudaStreamWaitEvent(sK2, c->ev_sel[e1], 0));
-        launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, sK2);
+        {
+            TraceScope ts(c, "spec_trk", 2, sK2);
+            launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, sK2);
+        }
         CU(cudaEventRecord(c->ev_trk[e], sK2));
         CU(cudaStreamWaitEvent(sP, c->ev_spf[e], 0));
         CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
@@ -605,12 +660,16 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         c->launches += 1;
         CU(cudaEventRecord(c->ev_sel[e], sP));
     } else {
-        launch_bucket_merge(c->d, c->bg, c->pc, prev, (int)(f & 1), spec ? 1 : 0, sP);   // FAST winners of the PREVIOUS left image
+        {
+            TraceScope ts(c, "bucket", 3, sP);
+            launch_bucket_merge(c->d, c->bg, c->pc, prev, (int)(f & 1), spec ? 1 : 0, sP);   // FAST winners of the PREVIOUS left image
+        }
         if (c->timers) cudaEventRecord(c->ev[2], sP);
         if (tm) {
             launch_klt(c->d, c->pg, c->pc, c->klt_blocks_full, prev, cur, sP);
         } else if (spec) {
             // normally nothing is left to track: a small grid on the chain's own SMs
+            TraceScope ts(c, "klt_todo", 3, sP);
             launch_klt(c->d, c->pg, c->pc, c->klt_blocks, prev, cur, sP);
         } else {
             // no cache: all bucketed features, on the KLT partition
@@ -621,20 +680,32 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
             CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
         }
         if (c->timers) cudaEventRecord(c->ev[3], sP);
-        launch_select(c->d, c->pg, c->pc, prev, cur, sP);
+        {
+            TraceScope ts(c, "select", 3, sP);
+            launch_select(c->d, c->pg, c->pc, prev, cur, sP);
+        }
         if (c->timers) cudaEventRecord(c->ev[4], sP);
         CU(cudaEventRecord(c->ev_sel[e], sP));
-        launch_pnp_hyp(c->d, c->pc, sP);
+        {
+            TraceScope ts(c, "hyp", 3, sP);
+            launch_pnp_hyp(c->d, c->pc, sP);
+        }
         if (c->timers) cudaEventRecord(c->ev[5], sP);
         if (!tm) CU(cudaStreamWaitEvent(sP, c->ev_fb[e1], 0));   // the refit of f - 1 still reads the inlier arrays
-        launch_pnp_final_a(c->d, c->pc, sP);
+        {
+            TraceScope ts(c, "final_a", 3, sP);
+            launch_pnp_final_a(c->d, c->pc, sP);
+        }
         c->launches += 6;
     }
     if (!tm) {
         CU(cudaEventRecord(c->ev_fa[e], sP));
         CU(cudaStreamWaitEvent(sB, c->ev_fa[e], 0));
     }
-    if (!first) launch_pnp_final_b(c->d, c->pc, sB);
+    if (!first) {
+        TraceScope ts(c, "final_b", 4, sB);
+        launch_pnp_final_b(c->d, c->pc, sB);
+    }
     if (c->timers) cudaEventRecord(c->ev[6], sP);
     if (results_dev)
         CU(cudaMemcpyAsync(results_dev, c->d.result, sizeof(svo_frame_result) * c->d.n_seq, cudaMemcpyDeviceToDevice, sB));

@@ -145,7 +145,7 @@ struct SerialRed {
     static SVO_HD int sum(int v) { return v; }
     static SVO_HD long long sum64(long long v) { return v; }
     // exact integer sums of the two mismatch accumulators, converted to float32 (round to nearest)
-    static SVO_HD void sum2f(long long a, long long b, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
+    static SVO_HD void sum2f(long long a, long long b, bool, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
     static SVO_HD void sync() {}
 };
 
@@ -204,7 +204,8 @@ SVO_HD float fsub(float a, float b) {
 // Per-feature scratch shared by the cooperating lanes (shared memory on the device).
 struct LkScratch {
     uint8_t ipatch[SVO_LK_PATCH * SVO_LK_PATCH_PITCH];     // template neighbourhood, u8
-    int dxy[SVO_LK_DW * SVO_LK_DP];                        // Scharr (dx | dy << 16), two int16
+    short dxp[SVO_LK_DW * SVO_LK_DP];                      // Scharr dx of the 11x11 window positions
+    short dyp[SVO_LK_DW * SVO_LK_DP];                      // Scharr dy
     unsigned short jp[SVO_LK_JR * SVO_LK_JC];              // J patch as horizontal pixel pairs p(x) | p(x+1) << 8
 };
 
@@ -253,6 +254,18 @@ SVO_HD int dp2a_lo_su(unsigned a, unsigned b, int c) {
 }
 SVO_HD unsigned pack_weights(int lo, int hi) { return ((unsigned)lo & 0xFFFFu) | ((unsigned)hi << 16); }
 
+// __byte_perm(a, b, sel): byte i of the result = byte sel[4i+3:4i] of the 8-byte pool {b, a}
+SVO_HD unsigned byte_perm(unsigned a, unsigned b, unsigned sel) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(a, b, sel);
+#else
+    const uint64_t pool = ((uint64_t)b << 32) | a;
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= (unsigned)((pool >> (8 * ((sel >> (4 * i)) & 7))) & 0xFFu) << (8 * i);
+    return r;
+#endif
+}
+
 // Stage the J patch whose top-left pixel is (jx0, jy0): jp[y][x] = J(jx0+x, jy0+y) | J(jx0+x+1, jy0+y) << 8
 // with BORDER_REFLECT_101.  jx0 is a multiple of 4, so interior patches are fetched as aligned words.
 template <int LANES>
@@ -272,10 +285,14 @@ SVO_HD void lk_stage_j(const LkLevel& J, int jx0, int jy0, int lane, unsigned sh
             w0 = src[0] | (src[1] << 8) | (src[2] << 16) | ((unsigned)src[3] << 24);
             w1 = src[4] | (src[5] << 8) | (src[6] << 16) | ((unsigned)src[7] << 24);
 #endif
-            const unsigned p0 = w0 & 0xFFFFu, p1 = (w0 >> 8) & 0xFFFFu, p2 = w0 >> 16, p3 = (w0 >> 24) | ((w1 & 0xFFu) << 8);
+            // pairs (b0 b1)(b1 b2) and (b2 b3)(b3 b4): one PRMT each, one 8-byte store
             unsigned* dst = reinterpret_cast<unsigned*>(jp + y * SVO_LK_JC + 4 * k);
-            dst[0] = p0 | (p1 << 16);
-            dst[1] = p2 | (p3 << 16);
+#if defined(__CUDA_ARCH__)
+            *reinterpret_cast<uint2*>(dst) = make_uint2(byte_perm(w0, w0, 0x2110u), byte_perm(w0, w1, 0x4332u));
+#else
+            dst[0] = byte_perm(w0, w0, 0x2110u);
+            dst[1] = byte_perm(w0, w1, 0x4332u);
+#endif
         }
     } else {
         for (int it = lane; it < SVO_LK_JR * SVO_LK_JC; it += LANES) {
@@ -387,17 +404,17 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         const bool dinside = ipx >= 0 && ipx + SVO_LK_DW <= I.w && ipy >= 0 && ipy + SVO_LK_DW <= I.h;
         for (int idx = lane; idx < SVO_LK_DW * SVO_LK_DW; idx += LANES) {
             const int y = idx / SVO_LK_DW, x = idx - y * SVO_LK_DW;
-            int v = 0;
+            int dx = 0, dy = 0;
             if (dinside || (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h)) {
                 const uint8_t* p = sc.ipatch + y * SVO_LK_PATCH_PITCH + x + xo;   // top-left of the 3x3 around patch (x+1, y+1)
                 const int a00 = p[0], a01 = p[1], a02 = p[2];
                 const int a10 = p[SVO_LK_PATCH_PITCH], a12 = p[SVO_LK_PATCH_PITCH + 2];
                 const int a20 = p[2 * SVO_LK_PATCH_PITCH], a21 = p[2 * SVO_LK_PATCH_PITCH + 1], a22 = p[2 * SVO_LK_PATCH_PITCH + 2];
-                const int dx = 3 * (a02 + a22 - a00 - a20) + 10 * (a12 - a10);
-                const int dy = 3 * (a20 + a22 - a00 - a02) + 10 * (a21 - a01);
-                v = (dx & 0xFFFF) | (dy << 16);
+                dx = 3 * (a02 + a22 - a00 - a20) + 10 * (a12 - a10);
+                dy = 3 * (a20 + a22 - a00 - a02) + 10 * (a21 - a01);
             }
-            sc.dxy[y * SVO_LK_DP + x] = v;
+            sc.dxp[y * SVO_LK_DP + x] = (short)dx;
+            sc.dyp[y * SVO_LK_DP + x] = (short)dy;
         }
         Red::sync();
 
@@ -408,10 +425,10 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         for (int s = 0; s < SLOTS; ++s) {
             const uint8_t* p = sc.ipatch + offI[s] + xo;
             const int iv = (p[0] * iw00 + p[1] * iw01 + p[SVO_LK_PATCH_PITCH] * iw10 + p[SVO_LK_PATCH_PITCH + 1] * iw11 + (1 << 8)) >> 9;
-            const int* dq = sc.dxy + offD[s];
-            const int d00 = dq[0], d01 = dq[1], d10 = dq[SVO_LK_DP], d11 = dq[SVO_LK_DP + 1];
-            const int ix = ((int)(short)d00 * iw00 + (int)(short)d01 * iw01 + (int)(short)d10 * iw10 + (int)(short)d11 * iw11 + (1 << 13)) >> 14;
-            const int iy = ((d00 >> 16) * iw00 + (d01 >> 16) * iw01 + (d10 >> 16) * iw10 + (d11 >> 16) * iw11 + (1 << 13)) >> 14;
+            const short* qx = sc.dxp + offD[s];
+            const short* qy = sc.dyp + offD[s];
+            const int ix = ((int)qx[0] * iw00 + (int)qx[1] * iw01 + (int)qx[SVO_LK_DP] * iw10 + (int)qx[SVO_LK_DP + 1] * iw11 + (1 << 13)) >> 14;
+            const int iy = ((int)qy[0] * iw00 + (int)qy[1] * iw01 + (int)qy[SVO_LK_DP] * iw10 + (int)qy[SVO_LK_DP + 1] * iw11 + (1 << 13)) >> 14;
             Iv[s] = val[s] ? (int)(short)iv : 0;
             Ixv[s] = val[s] ? (int)(short)ix : 0;
             Iyv[s] = val[s] ? (int)(short)iy : 0;
@@ -430,25 +447,35 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             continue;
         }
         D = 1.f / D;
+        // |sum diff * Ix| <= 8160 * sum |Ix| <= 8160 * 10 * sqrt(sum Ix^2): below 2^31 the plain 32-bit warp sum
+        // of the mismatch vector cannot overflow and needs no per-iteration check
+        const bool small_grad = sA11 < 690000000 && sA22 < 690000000;
+        // iteration-invariant part of the window test: (inx, iny) inside the staged patch AND not fully outside
+        // the level  <=>  0 <= inx - lox <= rx, 0 <= iny - loy <= ry   (rx / ry < 0: never)
+        int lox = imax(jx0, -SVO_LK_WIN), loy = imax(jy0, -SVO_LK_WIN);
+        int rx = imin(jx0 + SVO_LK_JC - SVO_LK_WIN, J.w - 1) - lox, ry = imin(jy0 + SVO_LK_JR - SVO_LK_WIN - 1, J.h - 1) - loy;
 
         float pdx = 0.f, pdy = 0.f;
         for (int j = 0; j < cfg.max_iters; ++j) {
             const int inx = floor_int(cx), iny = floor_int(cy);
-            if ((unsigned)(inx + SVO_LK_WIN) >= (unsigned)(J.w + SVO_LK_WIN) ||
-                (unsigned)(iny + SVO_LK_WIN) >= (unsigned)(J.h + SVO_LK_WIN)) {   // window fully outside the level
-                if (level == 0) status = 0;
-                break;
-            }
-            ++iters;
-            if ((unsigned)(inx - jx0) > (unsigned)(SVO_LK_JC - SVO_LK_WIN) ||
-                (unsigned)(iny - jy0) > (unsigned)(SVO_LK_JR - SVO_LK_WIN - 1)) {
+            const int ax = inx - lox, ay = iny - loy;
+            if ((ax | (rx - ax) | ay | (ry - ay)) < 0) {   // rare
+                if (inx < -SVO_LK_WIN || inx >= J.w || iny < -SVO_LK_WIN || iny >= J.h) {   // window fully outside the level
+                    if (level == 0) status = 0;
+                    break;
+                }
                 // the window left the staged patch: re-centre it
                 jx0 = (inx - 5) & ~3;
                 jy0 = iny - 3;
                 Red::sync();
                 lk_stage_j<LANES>(J, jx0, jy0, lane, sc.jp);
                 Red::sync();
+                lox = imax(jx0, -SVO_LK_WIN);
+                loy = imax(jy0, -SVO_LK_WIN);
+                rx = imin(jx0 + SVO_LK_JC - SVO_LK_WIN, J.w - 1) - lox;
+                ry = imin(jy0 + SVO_LK_JR - SVO_LK_WIN - 1, J.h - 1) - loy;
             }
+            ++iters;
 #ifdef SVO_LK_TRACE
             printf("L%d j%d c=(%.4f,%.4f) in=(%d,%d) j0=(%d,%d)\n", level, j, cx, cy, inx, iny, jx0, jy0);
 #endif
@@ -465,7 +492,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
                 sb2 += diff * Iyv[s];
             }
             float b1, b2;
-            Red::sum2f(sb1, sb2, b1, b2);
+            Red::sum2f(sb1, sb2, small_grad, b1, b2);
             b1 = fmul(b1, FLT_SCALE);
             b2 = fmul(b2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);

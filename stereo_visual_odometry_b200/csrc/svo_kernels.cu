@@ -11,6 +11,7 @@
 //   pnp_hyp_kernel / pnp_final_kernel   cameraToWorld (vo.cpp:282-313) + the failure gates of
 //                          stereo_callback (vo.cpp:106-136)
 #include <stdio.h>
+#include <string.h>
 
 #include "svo_kernels.cuh"
 #include "svo_epnp.cuh"
@@ -31,9 +32,9 @@ struct WarpRed {
     // exact sums of the two per-lane mismatch accumulators as float32.  A lane holds <= 4 pixels (|v| < 2^27);
     // when every lane is below 2^26 the warp total fits 32 bits and one REDUX each is exact, otherwise the
     // split 64-bit path runs (warp-uniform branch).
-    static __device__ __forceinline__ void sum2f(int a, int b, float& fa, float& fb) {
-        const bool big = max(abs(a), abs(b)) >= (1 << 26);
-        if (__any_sync(0xffffffffu, big)) {
+    // `small`: the caller proved that the totals fit 32 bits (warp-uniform)
+    static __device__ __forceinline__ void sum2f(int a, int b, bool small, float& fa, float& fb) {
+        if (!small && __any_sync(0xffffffffu, max(abs(a), abs(b)) >= (1 << 26))) {
             fa = (float)sum64(a);
             fb = (float)sum64(b);
         } else {
@@ -78,20 +79,65 @@ __device__ __forceinline__ unsigned long long ld_key(const unsigned long long* p
 }
 
 // ============================================================================
-// FAST-9/16 + 3x3 NMS.  One block = 64x16 output pixels; the 72x24 u8 tile and the
-// 66x18 score tile live in shared memory.
-constexpr int FT_W = 64, FT_H = 16, FT_THREADS = 256;
-constexpr int FT_TP = FT_W + 8 + 8;    // tile pitch (80)
-constexpr int FT_SP = FT_W + 2 + 2;    // score pitch (68)
+// FAST-9/16 + 3x3 NMS.  One block = 120 x 14 output pixels; scores are computed on the 128 x 16 region around
+// them from a 136 x 22 byte tile in shared memory.  A thread scores a QUAD of 4 horizontally adjacent pixels as
+// two int16x2 lanes (DPX min / max on packed halves, ring pixels extracted from 12-byte row windows by PRMT):
+//   phase 1  every quad: an upper bound of the arc score from the four compass ring pixels (any 9-arc contains
+//            two adjacent compass points); quads that cannot hold a corner at thr_lo are dropped (~2/3)
+//   phase 2  the surviving quads, compacted through a shared list so no warp idles: the exact arc score
+//   phase 3  strict 3x3 NMS + per-bucket winners (64-bit atomicMax keys) / dense response map
+constexpr int FT_OW = 120, FT_OH = 14, FT_SW = 128, FT_SH = 16, FT_TW = 136, FT_TH = 22, FT_THREADS = 256;
+constexpr int FT_TASKS = (FT_SW / 4) * FT_SH;   // 512 quads
 
-__device__ __forceinline__ bool has_arc9(unsigned m) {
-    // any 9 contiguous (circular) set bits among 16
-    unsigned x = m | (m << 16);
-    x &= x >> 1;
-    x &= x >> 2;
-    x &= x >> 4;    // runs of 8
-    x &= x >> 1;    // runs of 9
-    return (x & 0xFFFFu) != 0;
+// bytes i, i + 1 of the 12-byte window w[0..2] as (b_i) | (b_{i+1} << 16)
+__device__ __forceinline__ unsigned pick2(const unsigned* w, int i) {
+    const int wi = i >> 2, bi = i & 3;
+    if (bi < 3) return __byte_perm(w[wi], 0u, (unsigned)(bi | (4 << 4) | ((bi + 1) << 8) | (4 << 12)));
+    return __byte_perm(w[wi], w[wi + 1], 0x4433u) & 0x00FF00FFu;
+}
+// exact arc scores of the pixel pair whose first pixel is byte `c0` of the row windows; rows[r] = the 12-byte
+// window of tile row (centre row - 3 + r).  Returns the two scores + 256 packed as int16x2.
+template <int C0>
+__device__ __forceinline__ unsigned fast_pair_score(const unsigned (&rows)[7][3]) {
+    constexpr int RDX[16] = SVO_FAST_RING_DX;
+    constexpr int RDY[16] = SVO_FAST_RING_DY;
+    const unsigned vc = pick2(rows[3], C0) + 0x01000100u;   // centre + 256 per half: all differences stay positive
+    unsigned d[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = vc - pick2(rows[3 + RDY[k]], C0 + RDX[k]);
+    unsigned lo2[16], hi2[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo2[k] = __vmins2(d[k], d[(k + 1) & 15]);
+        hi2[k] = __vmaxs2(d[k], d[(k + 1) & 15]);
+    }
+    unsigned lo4[16], hi4[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo4[k] = __vmins2(lo2[k], lo2[(k + 2) & 15]);
+        hi4[k] = __vmaxs2(hi2[k], hi2[(k + 2) & 15]);
+    }
+    unsigned a = 0u, b = 0x7FFF7FFFu;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        a = __vmaxs2(a, __vimin3_s16x2(lo4[k], lo4[(k + 4) & 15], d[(k + 8) & 15]));
+        b = __vmins2(b, __vimax3_s16x2(hi4[k], hi4[(k + 4) & 15], d[(k + 8) & 15]));
+    }
+    // score + 256 = max(a, 512 - b) per half (kept biased: both halves positive, so the packed subtraction cannot
+    // borrow across the halves)
+    return __vmaxs2(a, 0x02000200u - b);
+}
+// upper bound of the arc scores of a pixel pair from the compass ring pixels k = 0, 4, 8, 12
+template <int C0>
+__device__ __forceinline__ unsigned fast_pair_bound(const unsigned* top, const unsigned* mid, const unsigned* bot) {
+    const unsigned vc = pick2(mid, C0) + 0x01000100u;
+    const unsigned d0 = vc - pick2(bot, C0), d4 = vc - pick2(mid, C0 + 3), d8 = vc - pick2(top, C0),
+                   d12 = vc - pick2(mid, C0 - 3);
+    const unsigned a = __vmaxs2(__vmaxs2(__vmins2(d0, d4), __vmins2(d4, d8)),
+                                     __vmaxs2(__vmins2(d8, d12), __vmins2(d12, d0)));
+    const unsigned b = __vmins2(__vmins2(__vmaxs2(d0, d4), __vmaxs2(d4, d8)),
+                                     __vmins2(__vmaxs2(d8, d12), __vmaxs2(d12, d0)));
+    return __vmaxs2(a, 0x02000200u - b);   // bound + 256 per half
 }
 
 __global__ void __launch_bounds__(FT_THREADS)
@@ -99,64 +145,101 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
             BucketGeom bg) {
-    __shared__ __align__(16) uint8_t tile[(FT_H + 8) * FT_TP];
-    __shared__ uint8_t score[(FT_H + 2) * FT_SP];
+    __shared__ __align__(16) uint8_t tile[FT_TH * FT_TW];
+    __shared__ __align__(16) uint8_t score[FT_SH * FT_SW];
+    __shared__ unsigned short list[FT_TASKS];
+    __shared__ int n_list;
     const int z = blockIdx.z;
     const uint8_t* src = img + (long long)z * img_stride;
-    const int x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H;
-    const int tid = threadIdx.x;
-
-    // ---- load tile rows [y0-4, y0+FT_H+4) x cols [x0-4, x0+FT_W+4), clamped (clamped
-    // values are only ever read for pixels whose score is forced to 0)
-    for (int i = tid; i < (FT_H + 8) * (FT_W + 8); i += FT_THREADS) {
-        const int ty = i / (FT_W + 8), tx = i - ty * (FT_W + 8);
-        const int gy = min(max(y0 - 4 + ty, 0), h - 1), gx = min(max(x0 - 4 + tx, 0), w - 1);
-        tile[ty * FT_TP + tx] = __ldg(src + (long long)gy * pitch + gx);
-    }
-    __syncthreads();
-
-    // ---- scores on the (FT_W+2) x (FT_H+2) region
-    constexpr int RDX[16] = SVO_FAST_RING_DX;
-    constexpr int RDY[16] = SVO_FAST_RING_DY;
-    for (int i = tid; i < (FT_H + 2) * (FT_W + 2); i += FT_THREADS) {
-        const int sy = i / (FT_W + 2), sx = i - sy * (FT_W + 2);
-        const int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
-        int resp = 0;
-        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3) {
-            const uint8_t* c = tile + (sy + 3) * FT_TP + (sx + 3);
-            const int v = c[0];
-            int r[16];
-            unsigned mb = 0, md = 0;
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                r[k] = c[RDY[k] * FT_TP + RDX[k]];
-                mb |= (r[k] > v + thr_lo) ? (1u << k) : 0u;
-                md |= (r[k] < v - thr_lo) ? (1u << k) : 0u;
-            }
-            if (has_arc9(mb) || has_arc9(md)) resp = fast9_arc_score(v, r) - 1;
+    const int x0 = blockIdx.x * FT_OW, y0 = blockIdx.y * FT_OH;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid == 0) n_list = 0;
+    // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
+    // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
+    const int tx0 = x0 - 8, ty0 = y0 - 4;
+    const bool fastpath = tx0 >= 0 && ty0 >= 0 && tx0 + FT_TW <= w && ty0 + FT_TH <= h && (pitch & 3) == 0 &&
+                          (((size_t)src) & 3) == 0;
+    if (fastpath) {
+        for (int i = tid; i < FT_TH * (FT_TW / 4); i += FT_THREADS) {
+            const int r = i / (FT_TW / 4), k = i - r * (FT_TW / 4);
+            reinterpret_cast<unsigned*>(tile)[i] =
+                __ldg(reinterpret_cast<const unsigned*>(src + (long long)(ty0 + r) * pitch + tx0) + k);
         }
-        score[sy * FT_SP + sx] = (uint8_t)resp;
+    } else {
+        for (int i = tid; i < FT_TH * FT_TW; i += FT_THREADS) {
+            const int r = i / FT_TW, c = i - r * FT_TW;
+            const int gy = min(max(ty0 + r, 0), h - 1), gx = min(max(tx0 + c, 0), w - 1);
+            tile[i] = __ldg(src + (long long)gy * pitch + gx);
+        }
     }
     __syncthreads();
 
-    // ---- NMS (strict maximum over the 8 neighbours) + outputs
-    for (int i = tid; i < FT_H * FT_W; i += FT_THREADS) {
-        const int oy = i / FT_W, ox = i - oy * FT_W;
+    // ---- phase 1: compass bound.  Task t: score row t / 32, quad t % 32 (score col 4q <-> tile col 4q + 4,
+    // score row r <-> tile row r + 3).  The 12-byte row window of a quad starts at tile col 4q.
+    const unsigned thr2 = (unsigned)(thr_lo + 256) | ((unsigned)(thr_lo + 256) << 16);   // scores are biased by 256
+#pragma unroll
+    for (int s = 0; s < FT_TASKS / FT_THREADS; ++s) {
+        const int t = tid + s * FT_THREADS;
+        const int r = t >> 5, q = t & 31;
+        const unsigned* top = reinterpret_cast<const unsigned*>(tile + (r + 0) * FT_TW) + q;
+        const unsigned* mid = reinterpret_cast<const unsigned*>(tile + (r + 3) * FT_TW) + q;
+        const unsigned* bot = reinterpret_cast<const unsigned*>(tile + (r + 6) * FT_TW) + q;
+        const unsigned wt[3] = {top[0], top[1], top[2]}, wm[3] = {mid[0], mid[1], mid[2]}, wb[3] = {bot[0], bot[1], bot[2]};
+        const unsigned ua = fast_pair_bound<4>(wt, wm, wb), ub = fast_pair_bound<6>(wt, wm, wb);
+        // any half > thr_lo ?
+        const bool pass = (__vmaxs2(ua, ub) != __vmins2(__vmaxs2(ua, ub), thr2));
+        reinterpret_cast<unsigned*>(score)[t] = 0u;
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        int base = 0;
+        if (lane == 0 && m) base = atomicAdd(&n_list, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (pass) list[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)t;
+    }
+    __syncthreads();
+
+    // ---- phase 2: exact scores of the surviving quads
+    const int n = n_list;
+    for (int i = tid; i < n; i += FT_THREADS) {
+        const int t = list[i];
+        const int r = t >> 5, q = t & 31;
+        unsigned rows[7][3];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const unsigned* p = reinterpret_cast<const unsigned*>(tile + (r + k) * FT_TW) + q;
+            rows[k][0] = p[0]; rows[k][1] = p[1]; rows[k][2] = p[2];
+        }
+        const unsigned sa = fast_pair_score<4>(rows), sb = fast_pair_score<6>(rows);
+        const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * q;
+        const bool rowok = gy >= 3 && gy < h - 3;
+        unsigned out = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int sc = (int)(((e < 2 ? sa : sb) >> (16 * (e & 1))) & 0xFFFFu) - 256;
+            const int x = gx + e;
+            if (rowok && x >= 3 && x < w - 3 && sc > thr_lo) out |= (unsigned)(sc - 1) << (8 * e);
+        }
+        reinterpret_cast<unsigned*>(score)[t] = out;
+    }
+    __syncthreads();
+
+    // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs
+    for (int i = tid; i < FT_OH * FT_OW; i += FT_THREADS) {
+        const int oy = i / FT_OW, ox = i - oy * FT_OW;
         const int gx = x0 + ox, gy = y0 + oy;
         if (gx >= w || gy >= h) continue;
-        const uint8_t* s = score + (oy + 1) * FT_SP + (ox + 1);
-        const int v = s[0];
-        const bool keep = v > 0 && v > s[-1] && v > s[1] && v > s[-FT_SP - 1] && v > s[-FT_SP] &&
-                          v > s[-FT_SP + 1] && v > s[FT_SP - 1] && v > s[FT_SP] && v > s[FT_SP + 1];
+        const uint8_t* sp = score + (oy + 1) * FT_SW + (ox + 4);
+        const int v = sp[0];
+        const bool keep = v > 0 && v > sp[-1] && v > sp[1] && v > sp[-FT_SW - 1] && v > sp[-FT_SW] &&
+                          v > sp[-FT_SW + 1] && v > sp[FT_SW - 1] && v > sp[FT_SW] && v > sp[FT_SW + 1];
         if (resp_map) resp_map[(long long)z * map_stride + (long long)gy * map_pitch + gx] = keep ? (uint8_t)v : 0;
         if (keep && keysB) {
             const int br = gy / bg.bh, bc = gx / bg.bw;
             if (br >= bg.start_row && 0 < bg.age_threshold) {
                 const unsigned long long key =
                     bucket_key(bucket_score(0, v, bg.fast_threshold), SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
-                const long long b = (long long)z * bg.nb + br * bg.n_bw + bc;
-                atomicMax(keysB + b, key);
-                if (v >= thr_hi) atomicMax(keysA + b, key);
+                const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
+                atomicMax(keysB + bidx, key);
+                if (v >= thr_hi) atomicMax(keysA + bidx, key);
             }
         }
     }
@@ -165,7 +248,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st) {
-    dim3 grid((w + FT_W - 1) / FT_W, (h + FT_H - 1) / FT_H, n_img);
+    dim3 grid((w + FT_OW - 1) / FT_OW, (h + FT_OH - 1) / FT_OH, n_img);
     fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map,
                                              map_stride, map_pitch, keysA, keysB, bg);
 }
@@ -228,78 +311,149 @@ void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pit
 }
 
 // ============================================================================
-// pyrDown
-struct GlobalImg {
-    const uint8_t* p;
-    int pitch;
-    __device__ __forceinline__ int operator()(int x, int y) const { return __ldg(p + (long long)y * pitch + x); }
+// pyrDown (5x5 binomial, (s + 128) >> 8, BORDER_REFLECT_101): shared-memory tiled, separable, word loads.
+// One block = 64 x 8 output pixels <- a 136 x 20 byte source tile (4 bytes of left margin keep the tile word
+// aligned): horizontal 5-tap pass into int16, vertical pass, packed 4-byte stores.  In copy mode the block also
+// writes the 128 x 16 source pixels it covers into the context's level-0 plane, so a new frame is read from HBM
+// exactly once for both the level-0 copy and level 1.
+constexpr int PD_OW = 64, PD_OH = 8, PD_TW = 2 * PD_OW + 8, PD_TH = 2 * PD_OH + 4, PD_THREADS = 256;
+struct PyrDownJob {
+    const uint8_t* src[2];    // per camera (n_cam == 1: only [0])
+    long long src_seq_stride;
+    int sw, sh, spitch;
+    uint8_t* dst[2];
+    long long dst_seq_stride;
+    int dw, dh, dpitch;
+    uint8_t* copy[2];         // optional level-0 copy of the source (nullptr: none)
+    long long copy_seq_stride;
+    int cpitch;
+    int n_cam;
 };
-__global__ void __launch_bounds__(256)
-pyrdown_kernel(const uint8_t* __restrict__ src, long long src_stride, int sw, int sh, int spitch,
-               uint8_t* __restrict__ dst, long long dst_stride, int dw, int dh, int dpitch) {
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= dw || y >= dh) return;
-    GlobalImg g{src + (long long)blockIdx.z * src_stride, spitch};
-    dst[(long long)blockIdx.z * dst_stride + (long long)y * dpitch + x] = (uint8_t)pyrdown_pixel(g, sw, sh, x, y);
+// the 4 bytes at an arbitrary byte address, from the two aligned words around it
+__device__ __forceinline__ unsigned ld_word_any(const uint8_t* p) {
+    const unsigned sh = (unsigned)((size_t)p & 3);
+    const unsigned* a = reinterpret_cast<const unsigned*>(p - sh);
+    const unsigned w0 = __ldg(a);
+    if (sh == 0) return w0;
+    return __funnelshift_r(w0, __ldg(a + 1), 8 * sh);
+}
+__global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) {
+    __shared__ __align__(16) uint8_t tile[PD_TH * PD_TW];
+    __shared__ short hs[PD_TH * PD_OW];
+    const int cam = j.n_cam == 2 ? (blockIdx.z & 1) : 0, seq = j.n_cam == 2 ? (blockIdx.z >> 1) : blockIdx.z;
+    const uint8_t* src = j.src[cam] + (long long)seq * j.src_seq_stride;
+    uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
+    const int X0 = blockIdx.x * PD_OW, Y0 = blockIdx.y * PD_OH, tid = threadIdx.x;
+    const int sx0 = 2 * X0 - 4, sy0 = 2 * Y0 - 2;   // image position of tile[0][0]
+    // every byte the block uses lies inside the image: plain word loads (also past w up to the tile edge is fine
+    // as long as it stays inside the row's allocation: require it inside w to keep it simple)
+    const bool interior = sx0 >= 0 && sy0 >= 0 && sx0 + PD_TW + 4 <= j.sw && sy0 + PD_TH <= j.sh;
+    if (interior) {
+        for (int i = tid; i < PD_TH * (PD_TW / 4); i += PD_THREADS) {
+            const int r = i / (PD_TW / 4), k = i - r * (PD_TW / 4);
+            reinterpret_cast<unsigned*>(tile)[i] = ld_word_any(src + (long long)(sy0 + r) * j.spitch + sx0 + 4 * k);
+        }
+    } else {
+        for (int i = tid; i < PD_TH * PD_TW; i += PD_THREADS) {
+            const int r = i / PD_TW, c = i - r * PD_TW;
+            tile[i] = __ldg(src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + reflect101(sx0 + c, j.sw));
+        }
+    }
+    __syncthreads();
+    if (j.copy[cam]) {   // source rows 2*Y0 .. 2*Y0+15, columns 2*X0 .. 2*X0+127 = tile rows 2.., columns 4..
+        uint8_t* cp = j.copy[cam] + (long long)seq * j.copy_seq_stride;
+        for (int i = tid; i < 2 * PD_OH * (2 * PD_OW / 4); i += PD_THREADS) {
+            const int r = i >> 5, k = i & 31;
+            const int gy = 2 * Y0 + r, gx = 2 * X0 + 4 * k;
+            if (gy < j.sh && gx < j.sw)   // whole words: the copy plane's pitch is a multiple of 128
+                *reinterpret_cast<unsigned*>(cp + (long long)gy * j.cpitch + gx) =
+                    *reinterpret_cast<const unsigned*>(tile + (r + 2) * PD_TW + 4 + 4 * k);
+        }
+    }
+    // horizontal pass: hs[r][c] = 1 4 6 4 1 over image columns 2x-2 .. 2x+2 = tile columns 2c+2 .. 2c+6
+    for (int i = tid; i < PD_TH * PD_OW; i += PD_THREADS) {
+        const int r = i >> 6, c = i & 63;
+        const uint8_t* t = tile + r * PD_TW + 2 * c + 2;
+        hs[i] = (short)(t[0] + t[4] + 4 * (t[1] + t[3]) + 6 * t[2]);
+    }
+    __syncthreads();
+    // vertical pass: 4 adjacent outputs per thread, one word store
+    if (tid < PD_OH * PD_OW / 4) {
+        const int y = tid >> 4, c0 = (tid & 15) * 4;
+        const int oy = Y0 + y;
+        if (oy < j.dh) {
+            unsigned out = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const short* h = hs + (2 * y) * PD_OW + c0 + q;
+                const int v = (h[0] + h[4 * PD_OW] + 4 * (h[PD_OW] + h[3 * PD_OW]) + 6 * h[2 * PD_OW] + 128) >> 8;
+                out |= (unsigned)v << (8 * q);
+            }
+            const int ox = X0 + c0;
+            uint8_t* o = dst + (long long)oy * j.dpitch + ox;
+            if (ox + 3 < j.dw && (j.dpitch & 3) == 0 && (((size_t)dst) & 3) == 0) {
+                *reinterpret_cast<unsigned*>(o) = out;
+            } else {
+                for (int q = 0; q < 4; ++q)
+                    if (ox + q < j.dw) o[q] = (uint8_t)(out >> (8 * q));
+            }
+        }
+    }
+}
+static void launch_pyrdown_job(const PyrDownJob& j, int n_img, cudaStream_t st) {
+    dim3 grid((j.dw + PD_OW - 1) / PD_OW, (j.dh + PD_OH - 1) / PD_OH, n_img);
+    pyrdown_tile_kernel<<<grid, PD_THREADS, 0, st>>>(j);
 }
 void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch, uint8_t* dst,
                     long long dst_stride, int dw, int dh, int dpitch, int n_img, cudaStream_t st) {
-    dim3 grid((dw + 31) / 32, (dh + 7) / 8, n_img);
-    pyrdown_kernel<<<grid, 256, 0, st>>>(src, src_stride, sw, sh, spitch, dst, dst_stride, dw, dh, dpitch);
+    PyrDownJob j;
+    memset(&j, 0, sizeof(j));
+    j.src[0] = src; j.src_seq_stride = src_stride; j.sw = sw; j.sh = sh; j.spitch = spitch;
+    j.dst[0] = dst; j.dst_seq_stride = dst_stride; j.dw = dw; j.dh = dh; j.dpitch = dpitch;
+    j.n_cam = 1;
+    launch_pyrdown_job(j, n_img, st);
 }
 
 // ---- context ingest into pyramid slot `slot` (host-known ring, frame f -> f % 3)
-// z = seq * 2 + cam
-__global__ void __launch_bounds__(256)
-ctx_copy_level0_kernel(DevArrays d, PyrGeom pg, const uint8_t* __restrict__ left,
-                       const uint8_t* __restrict__ right, int stride, long long seq_stride, int slot) {
-    const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
-    const uint8_t* src = (cam ? right : left) + (long long)seq * seq_stride;
-    uint8_t* dst = d.pyr + pg.base(seq, slot, cam) + pg.off[0];
-    const int y = blockIdx.y;
-    const int w = pg.w[0];
-    const uint8_t* srow = src + (long long)y * stride;
-    uint8_t* drow = dst + (long long)y * pg.pitch[0];
-    const bool vec = ((((unsigned long long)src) | (unsigned long long)stride) & 15ull) == 0;
-    if (vec) {
-        const int nv = w >> 4;
-        for (int i = blockIdx.x * 256 + threadIdx.x; i < nv; i += gridDim.x * 256)
-            reinterpret_cast<uint4*>(drow)[i] = __ldg(reinterpret_cast<const uint4*>(srow) + i);
-        for (int x = (nv << 4) + blockIdx.x * 256 + threadIdx.x; x < w; x += gridDim.x * 256) drow[x] = srow[x];
-    } else {
-        for (int x = blockIdx.x * 256 + threadIdx.x; x < w; x += gridDim.x * 256) drow[x] = srow[x];
-    }
-}
-__global__ void __launch_bounds__(256)
-ctx_pyrdown_kernel(DevArrays d, PyrGeom pg, int level /* destination level >= 1 */, int slot) {
-    const int seq = blockIdx.z >> 1, cam = blockIdx.z & 1;
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= pg.w[level] || y >= pg.h[level]) return;
-    uint8_t* base = d.pyr + pg.base(seq, slot, cam);
-    GlobalImg g{base + pg.off[level - 1], pg.pitch[level - 1]};
-    // plain loads: the source level was written by the previous launch
-    base[pg.off[level] + (long long)y * pg.pitch[level] + x] =
-        (uint8_t)pyrdown_pixel(g, pg.w[level - 1], pg.h[level - 1], x, y);
-}
-
 int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
                   cudaStream_t st) {
     int launches = 0;
-    if (left) {   // images outside the context: copy into level 0 of the slot
-        dim3 grid(1, pg.h[0], d.n_seq * 2);
-        ctx_copy_level0_kernel<<<grid, 256, 0, st>>>(d, pg, left, right, stride, seq_stride, slot);
+    const long long ctx_seq_stride = pg.base(1, 0, 0) - pg.base(0, 0, 0);
+    for (int l = 1; l < pg.nlevels; ++l) {
+        PyrDownJob j;
+        memset(&j, 0, sizeof(j));
+        for (int cam = 0; cam < 2; ++cam) {
+            uint8_t* img = d.pyr + pg.base(0, slot, cam);
+            j.dst[cam] = img + pg.off[l];
+            j.src[cam] = img + pg.off[l - 1];
+            if (l == 1 && left) {   // images outside the context: read once, level-0 copy + level 1 from one tile
+                j.src[cam] = cam ? right : left;
+                j.copy[cam] = img + pg.off[0];
+            }
+        }
+        const bool ext = l == 1 && left;
+        j.src_seq_stride = ext ? seq_stride : ctx_seq_stride;
+        j.spitch = ext ? stride : pg.pitch[l - 1];
+        j.sw = pg.w[l - 1]; j.sh = pg.h[l - 1];
+        j.dst_seq_stride = ctx_seq_stride;
+        j.dw = pg.w[l]; j.dh = pg.h[l]; j.dpitch = pg.pitch[l];
+        j.copy_seq_stride = ctx_seq_stride;
+        j.cpitch = pg.pitch[0];
+        j.n_cam = 2;
+        launch_pyrdown_job(j, d.n_seq * 2, st);
         ++launches;
     }
-    for (int l = 1; l < pg.nlevels; ++l) {
-        dim3 grid((pg.w[l] + 31) / 32, (pg.h[l] + 7) / 8, d.n_seq * 2);
-        ctx_pyrdown_kernel<<<grid, 256, 0, st>>>(d, pg, l, slot);
-        ++launches;
+    if (pg.nlevels == 1 && left) {   // no pyramid level to fuse the copy with
+        cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 0) + pg.off[0], pg.pitch[0], left, stride, pg.w[0], pg.h[0],
+                          cudaMemcpyDeviceToDevice, st);
+        cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 1) + pg.off[0], pg.pitch[0], right, stride, pg.w[0], pg.h[0],
+                          cudaMemcpyDeviceToDevice, st);
     }
     unsigned long long* keysA = d.fastkeys + ((long long)(slot * 2 + 0) * d.n_seq) * bg.nb;
     unsigned long long* keysB = d.fastkeys + ((long long)(slot * 2 + 1) * d.n_seq) * bg.nb;
     // FAST on the left level 0 of the slot (the pitch-aligned copy)
-    launch_fast(d.pyr + pg.base(0, slot, 0) + pg.off[0], pg.base(1, 0, 0) - pg.base(0, 0, 0), pc.width, pc.height,
+    launch_fast(d.pyr + pg.base(0, slot, 0) + pg.off[0], ctx_seq_stride, pc.width, pc.height,
                 pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, keysA, keysB, bg, st);
     return launches + 1;
 }
