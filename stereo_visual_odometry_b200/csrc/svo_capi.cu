@@ -682,7 +682,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         if (c->timers) cudaEventRecord(c->ev[3], sP);
         {
             TraceScope ts(c, "select", 3, sP);
-            launch_select(c->d, c->pg, c->pc, prev, cur, sP);
+            launch_select(c->d, c->pg, c->pc, prev, cur, prev, sP);
         }
         if (c->timers) cudaEventRecord(c->ev[4], sP);
         CU(cudaEventRecord(c->ev_sel[e], sP));
@@ -1166,7 +1166,7 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     }
     CU(cudaMemsetAsync(d.klt_next, 0, sizeof(int), st));
     launch_klt(d, c->pg, c->pc, c->klt_blocks, 0, 1, st);
-    launch_select(d, c->pg, c->pc, 0, 1, st);
+    launch_select(d, c->pg, c->pc, 0, 1, detect ? 0 : -1, st);
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());

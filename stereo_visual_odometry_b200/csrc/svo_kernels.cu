@@ -478,152 +478,147 @@ void launch_first_frame(const DevArrays& d, cudaStream_t st) {
 }
 
 // ============================================================================
-// bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry.
-// One block per sequence.  Buckets are visited in coalesced tiles of 1024 (bucket = tile * 1024 + tid);
-// every key is read once into registers, the ordered compaction uses one ballot per tile and a single
-// block scan over the (tile, warp) popcounts.
-constexpr int BM_TILES = 16;   // nb <= 16384 (checked in svo_create)
+// bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry.  Two kernels:
+//   bucket_keys_kernel   every tracked feature atomicMax-es its key into its bucket (grid over the features)
+//   bucket_merge_kernel  block t owns buckets [1024 t, 1024 t + 1024): it reads ALL keys once (coalesced, L2
+//                        resident, 350 KB) to count the winners before its tile and in total -- the total decides
+//                        the low-threshold retry (vo.cpp:327-332) -- so the blocks need no inter-block hand-off;
+//                        then one ballot + one block scan order its own winners, which are written together with
+//                        their circular-matching result from the speculative cache (or queued for klt_kernel).
+// The key buffers are cleared by select_kernel (every block here reads all of them).
+__global__ void __launch_bounds__(256) bucket_keys_kernel(DevArrays d, BucketGeom bg) {
+    const int seq = blockIdx.y;
+    SeqState* s = d.state + seq;
+    const long long fo = (long long)seq * d.cap;
+    unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
+    const int n = s->n_feat;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i == 0) {   // per-frame accumulators of bucket_merge_kernel / klt_kernel
+        s->lk_iters = 0;
+        d.n_todo[seq] = 0;
+        d.klt_next[seq] = 0;
+    }
+    if (i >= n) return;
+    const float2 p = d.fs_xy[fo + i];
+    const int age = d.fs_age[fo + i], str = d.fs_str[fo + i];
+    const int br = (int)__fdiv_rn(p.y, (float)bg.bh), bc = (int)__fdiv_rn(p.x, (float)bg.bw);
+    if (br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw && age < bg.age_threshold)
+        atomicMax(keyT + br * bg.n_bw + bc, bucket_key(bucket_score(age, str, bg.fast_threshold), (unsigned)i, str));
+}
 __global__ void __launch_bounds__(1024)
 bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int specbuf, int use_spec) {
     __shared__ int sm[33];
-    __shared__ int wcount[BM_TILES * 32];
-    __shared__ int sm_todo, sm_iters;
-    const int seq = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    __shared__ int sm_iters;
+    const int seq = blockIdx.y, tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     SeqState* s = d.state + seq;
-    if (tid == 0) {
-        sm_todo = 0;
-        sm_iters = 0;
-    }
     const long long fo = (long long)seq * d.cap;
-    unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
-    unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
-    unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
-    const int n = s->n_feat;
+    const unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
+    const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
+    const unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
     const bool spec_ok = use_spec != 0 && s->spec_bad == 0;
     const bool trk_ok = s->fs_from_inliers != 0;
+    if (tid == 0) sm_iters = 0;
 
-    for (int i = tid; i < n; i += 1024) {
-        const float2 p = d.fs_xy[fo + i];
-        const int age = d.fs_age[fo + i], str = d.fs_str[fo + i];
-        const int br = (int)__fdiv_rn(p.y, (float)bg.bh), bc = (int)__fdiv_rn(p.x, (float)bg.bw);
-        if (br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw && age < bg.age_threshold)
-            atomicMax(keyT + br * bg.n_bw + bc, bucket_key(bucket_score(age, str, bg.fast_threshold), (unsigned)i, str));
-    }
-    __threadfence();
-    __syncthreads();
-
+    // winners without / with the thr/4 FAST set: in total and before this tile (low 16 bits | high 16 bits)
     const int ntiles = (bg.nb + 1023) >> 10;
-    unsigned long long w1[BM_TILES], kbv[BM_TILES];
-    unsigned isA = 0;   // bit j: the winner of tile j is this bucket's thr-20 FAST winner (cached by klt_spec_fast_kernel)
-    int c1 = 0;
-#pragma unroll
-    for (int j = 0; j < BM_TILES; ++j) {
-        w1[j] = 0ull;
-        kbv[j] = 0ull;
+    int tot = 0, pre = 0;   // packed: count(w1 != 0) | count(w1 != 0 || kb != 0) << 16
+    unsigned long long my_w1 = 0ull, my_kb = 0ull;
+    bool my_isA = false;
+#pragma unroll 4
+    for (int j = 0; j < ntiles; ++j) {
         const int b = (j << 10) + tid;
-        if (j < ntiles && b < bg.nb) {
-            const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
-            kbv[j] = ld_key(keyB + b);
-            w1[j] = kt > ka ? kt : ka;
-            isA |= (ka != 0ull && !(kt > ka)) ? (1u << j) : 0u;
-            c1 += (w1[j] != 0ull) ? 1 : 0;
-            keyT[b] = 0ull;   // consumed: ready for the next frame / the next FAST pass of this parity
-            keyA[b] = 0ull;
-            keyB[b] = 0ull;
+        if (b < bg.nb) {
+            const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b), kb = ld_key(keyB + b);
+            const unsigned long long w1 = kt > ka ? kt : ka;
+            const int c = ((w1 != 0ull) ? 1 : 0) | (((w1 != 0ull || kb != 0ull) ? 1 : 0) << 16);
+            tot += c;
+            if (j < tile) pre += c;
+            if (j == tile) {
+                my_w1 = w1;
+                my_kb = kb;
+                my_isA = ka != 0ull && !(kt > ka);   // the winner is this bucket's thr-20 FAST winner (cached)
+            }
         }
     }
-    int n1;
-    block_excl_scan<1024>(c1, &n1, sm);
+    int tot_all, pre_all;
+    block_excl_scan<1024>(tot, &tot_all, sm);
+    block_excl_scan<1024>(pre, &pre_all, sm);
+    const int n1 = tot_all & 0xFFFF;
     const bool retry = n1 < pc.pre_matching_threshold;   // vo.cpp:327-332
+    const int total = retry ? (tot_all >> 16) : n1;
+    const int base = retry ? (pre_all >> 16) : (pre_all & 0xFFFF);
 
-    unsigned ballots[BM_TILES];
-#pragma unroll
-    for (int j = 0; j < BM_TILES; ++j) {
-        unsigned long long wv = w1[j];
-        const unsigned long long kb = kbv[j];
-        // second append: the survivors come first in the feature order, so a thr/4 FAST feature only wins
-        // with a strictly greater score
-        if (retry && kb != 0ull && (wv == 0ull || bucket_key_score(kb) > bucket_key_score(wv))) {
-            // a thr-5 winner that differs from the cached thr-20 one was not tracked ahead of time
-            // (a bucket with a thr-20 corner has kb == ka, which never replaces: only un-cached winners get here)
-            isA &= ~(1u << j);
-            wv = kb;
-        }
-        w1[j] = wv;
-        ballots[j] = __ballot_sync(0xffffffffu, wv != 0ull);
-        if (lane == 0) wcount[j * 32 + wid] = __popc(ballots[j]);
+    unsigned long long wv = my_w1;
+    // second append: the survivors come first in the feature order, so a thr/4 FAST feature only wins with a
+    // strictly greater score (a bucket with a thr-20 corner has kb == ka, which never replaces)
+    if (retry && my_kb != 0ull && (wv == 0ull || bucket_key_score(my_kb) > bucket_key_score(wv))) {
+        my_isA = false;
+        wv = my_kb;
     }
-    __syncthreads();
-    int total;
-    const int my = (tid < BM_TILES * 32) ? wcount[tid] : 0;
-    const int pre = block_excl_scan<1024>(my, &total, sm);
-    if (tid < BM_TILES * 32) wcount[tid] = pre;
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < BM_TILES; ++j) {
-        const unsigned long long wv = w1[j];
-        if (wv != 0ull) {
-            const int off = wcount[j * 32 + wid] + __popc(ballots[j] & ((1u << lane) - 1u));
-            const unsigned order = bucket_key_order(wv);
-            float2 p;
-            int age, str;
+    int tile_total;
+    const int off = base + block_excl_scan<1024>(wv != 0ull ? 1 : 0, &tile_total, sm);
+    if (wv != 0ull && off < d.cap) {
+        const unsigned order = bucket_key_order(wv);
+        float2 p;
+        int age, str;
+        if (order >= SVO_FAST_ORDER_BASE) {
+            const int pix = (int)(order - SVO_FAST_ORDER_BASE);
+            const int y = pix / pc.width;
+            p = make_float2((float)(pix - y * pc.width), (float)y);
+            age = 0;
+            str = bucket_key_strength(wv);
+        } else {
+            p = d.fs_xy[fo + order];
+            age = d.fs_age[fo + order];
+            str = d.fs_str[fo + order];
+        }
+        d.bk_xy[fo + off] = p;
+        d.bk_age[fo + off] = age;
+        d.bk_str[fo + off] = str;
+        // circular-matching result from the speculative cache, else queue the feature for klt_kernel
+        long long src = -1;
+        const float2* sp = nullptr;
+        const uint8_t* sst = nullptr;
+        const int* sit = nullptr;
+        if (spec_ok) {
             if (order >= SVO_FAST_ORDER_BASE) {
-                const int pix = (int)(order - SVO_FAST_ORDER_BASE);
-                const int y = pix / pc.width;
-                p = make_float2((float)(pix - y * pc.width), (float)y);
-                age = 0;
-                str = bucket_key_strength(wv);
-            } else {
-                p = d.fs_xy[fo + order];
-                age = d.fs_age[fo + order];
-                str = d.fs_str[fo + order];
-            }
-            if (off < d.cap) {
-                d.bk_xy[fo + off] = p;
-                d.bk_age[fo + off] = age;
-                d.bk_str[fo + off] = str;
-                // circular-matching result from the speculative cache, else queue the feature for klt_kernel
-                long long src = -1;
-                const float2* sp = nullptr;
-                const uint8_t* sst = nullptr;
-                const int* sit = nullptr;
-                if (spec_ok) {
-                    if (order >= SVO_FAST_ORDER_BASE) {
-                        if ((isA >> j) & 1u) {
-                            src = ((long long)specbuf * d.n_seq + seq) * bg.nb + (j << 10) + tid;
-                            sp = d.specF_pts; sst = d.specF_st; sit = d.specF_it;
-                        }
-                    } else if (trk_ok) {
-                        src = fo + d.inl_idx[fo + order];
-                        sp = d.specT_pts; sst = d.specT_st; sit = d.specT_it;
-                    }
+                if (my_isA) {
+                    src = ((long long)specbuf * d.n_seq + seq) * bg.nb + (tile << 10) + tid;
+                    sp = d.specF_pts; sst = d.specF_st; sit = d.specF_it;
                 }
-                if (src >= 0) {
-                    d.lk_L1[fo + off] = sp[src * 4 + 0];
-                    d.lk_R1[fo + off] = sp[src * 4 + 1];
-                    d.lk_R0[fo + off] = sp[src * 4 + 2];
-                    d.lk_C[fo + off] = sp[src * 4 + 3];
-                    d.lk_status[fo + off] = sst[src];
-                    atomicAdd(&sm_iters, sit[src]);
-                } else {
-                    d.todo[fo + atomicAdd(&sm_todo, 1)] = off;
-                }
+            } else if (trk_ok) {
+                src = fo + d.inl_idx[fo + order];
+                sp = d.specT_pts; sst = d.specT_st; sit = d.specT_it;
             }
+        }
+        if (src >= 0) {
+            const float4 ab = *reinterpret_cast<const float4*>(sp + src * 4);
+            const float4 ce = *reinterpret_cast<const float4*>(sp + src * 4 + 2);
+            d.lk_L1[fo + off] = make_float2(ab.x, ab.y);
+            d.lk_R1[fo + off] = make_float2(ab.z, ab.w);
+            d.lk_R0[fo + off] = make_float2(ce.x, ce.y);
+            d.lk_C[fo + off] = make_float2(ce.z, ce.w);
+            d.lk_status[fo + off] = sst[src];
+            atomicAdd(&sm_iters, sit[src]);
+        } else {
+            d.todo[fo + atomicAdd(d.n_todo + seq, 1)] = off;
         }
     }
     __syncthreads();
     if (tid == 0) {
-        s->n_bucketed = min(total, d.cap);
-        s->retry = retry ? 1 : 0;
-        s->lk_iters = sm_iters;
-        s->frame_id += 1;
-        d.klt_next[seq] = 0;
-        d.n_todo[seq] = sm_todo;
+        if (sm_iters) atomicAdd(&s->lk_iters, sm_iters);
+        if (tile == 0) {
+            s->n_bucketed = min(total, d.cap);
+            s->retry = retry ? 1 : 0;
+            s->frame_id += 1;
+        }
     }
+    (void)lane;
 }
 void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf, int specbuf,
                          int use_spec, cudaStream_t st) {
-    bucket_merge_kernel<<<d.n_seq, 1024, 0, st>>>(d, bg, pc, keybuf, specbuf, use_spec);
+    bucket_keys_kernel<<<dim3((d.cap + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg);
+    bucket_merge_kernel<<<dim3((bg.nb + 1023) / 1024, d.n_seq), 1024, 0, st>>>(d, bg, pc, keybuf, specbuf, use_spec);
 }
 
 // ============================================================================
@@ -916,7 +911,7 @@ void launch_pnp_samples(const DevArrays& d, cudaStream_t st) { pnp_samples_kerne
 // inter-block dependency exists; the last block only counts, builds the RANSAC samples and updates the state.
 constexpr int SEL_T = 256;
 __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev,
-                                                       int slot_cur) {
+                                                       int slot_cur, int nb, int keybuf) {
     __shared__ int sm[SEL_T / 32 + 1];
     __shared__ int mods[SVO_RNG_TABLE];
     const int seq = blockIdx.y, tid = threadIdx.x;
@@ -925,6 +920,18 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
     const int n = s->n_bucketed;
     const bool tail = blockIdx.x == gridDim.x - 1;
     const int t0 = tail ? n : blockIdx.x * SEL_T;
+    if (keybuf >= 0) {
+        // the bucket keys of this frame are consumed (every block of bucket_merge_kernel read all of them):
+        // ready for the next frame / the next FAST pass into this ring buffer
+        unsigned long long* kT = d.trackkeys + (long long)seq * nb;
+        unsigned long long* kA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * nb;
+        unsigned long long* kB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * nb;
+        for (int i = blockIdx.x * SEL_T + tid; i < nb; i += gridDim.x * SEL_T) {
+            kT[i] = 0ull;
+            kA[i] = 0ull;
+            kB[i] = 0ull;
+        }
+    }
     if (n == 0) {
         // circularMatching returns before lastLeft/RightPyramid are replaced (vo.cpp:179-181): keep the old
         // pyramids as "previous" by copying them into this frame's ring slot
@@ -986,9 +993,9 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
     }
 }
 void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
-                   cudaStream_t st) {
+                   int keybuf, cudaStream_t st) {
     dim3 grid((d.cap + SEL_T - 1) / SEL_T + 1, d.n_seq);
-    select_kernel<<<grid, SEL_T, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
+    select_kernel<<<grid, SEL_T, 0, st>>>(d, pg, pc, slot_prev, slot_cur, d.nb, keybuf);
 }
 
 // ============================================================================

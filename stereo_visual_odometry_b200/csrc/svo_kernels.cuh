@@ -44,8 +44,9 @@ void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig
 int klt_resident_blocks_per_sm();   // persistent KLT blocks that fit one SM (occupancy query)
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st);
+// keybuf >= 0: also clears the FAST key buffer `keybuf` and the tracked-key scratch (consumed by bucket_merge)
 void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
-                   cudaStream_t st);
+                   int keybuf, cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);     // a then b
