@@ -96,6 +96,7 @@ struct svo_ctx {
     cudaStream_t stream_k = nullptr;    // speculative KLT of the FAST-winner candidates (and the un-cached fallback)
     cudaStream_t stream_k2 = nullptr;   // speculative KLT of the matched-feature candidates (same partition)
     cudaEvent_t ev_spf[4] = {nullptr, nullptr, nullptr, nullptr};   // FAST-winner candidates of frame f tracked
+    cudaEvent_t ev_bm[4] = {nullptr, nullptr, nullptr, nullptr};    // bucket merge of frame f done (predictions for f + 1)
     cudaStream_t stream_fb = nullptr;   // pose refit + result
     cudaStream_t stream_full = nullptr; // whole-GPU stream for serial frames (== stream when there are no partitions)
     int klt_blocks_full = 0;            // persistent KLT blocks per sequence on the whole GPU
@@ -216,10 +217,10 @@ static int validate_params(const svo_params* p) {
 // Streams of a context.  A single-sequence context is latency bound: its pose chain (a few small blocks) must
 // never wait for a block slot behind the persistent tracking kernels, so the SMs are split with CUDA green
 // contexts into chain / ingest / KLT partitions (SVO_PARTITION="chain,ingest" SM counts, "0" = off; default
-// 24,16 of the 148 SMs).  Batched contexts are throughput bound and use plain streams on the whole GPU.
+// 16,8 of the 148 SMs).  Batched contexts are throughput bound and use plain streams on the whole GPU.
 // SVO_SPEC=0/1 overrides whether the speculative tracking runs (default: single-sequence contexts only).
 static int create_streams(svo_ctx* c, const svo_params* p) {
-    int want_chain = 24, want_in = 16;
+    int want_chain = 16, want_in = 8;
     c->spec = p->n_seq == 1 && c->pipeline_ctx;
     if (const char* e = getenv("SVO_SPEC"))
         if (c->pipeline_ctx) c->spec = atoi(e) != 0;
@@ -332,6 +333,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_trk[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_spf[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_bm[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_fa[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_fb[i], cudaEventDisableTiming));
     }
@@ -399,6 +401,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.cntT, S));
     CU(dev_alloc(c, &d.listF, S * c->bg.nb));
     CU(dev_alloc(c, &d.nF, S));
+    CU(dev_alloc(c, &d.predT, (size_t)2 * S * c->bg.nb));
     CU(dev_alloc(c, &d.todo, C));
     CU(dev_alloc(c, &d.n_todo, S));
     CU(dev_alloc(c, &d.job, S));
@@ -432,7 +435,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         const int sm_k = c->sm_k > 0 ? c->sm_k : prop.multiProcessorCount;
         int per_seq = (sm_chain * per_sm + p->n_seq - 1) / p->n_seq;
         c->klt_blocks = per_seq < 1 ? 1 : per_seq;
-        per_seq = (sm_k * per_sm + p->n_seq - 1) / p->n_seq;
+        per_seq = (sm_k * klt_spec_resident_blocks_per_sm() + p->n_seq - 1) / p->n_seq;
         c->klt_blocks_k = per_seq < 1 ? 1 : per_seq;
         per_seq = (prop.multiProcessorCount * per_sm + p->n_seq - 1) / p->n_seq;
         c->klt_blocks_full = per_seq < 1 ? 1 : per_seq;
@@ -484,6 +487,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
         if (c->ev_trk[i]) cudaEventDestroy(c->ev_trk[i]);
         if (c->ev_spf[i]) cudaEventDestroy(c->ev_spf[i]);
+        if (c->ev_bm[i]) cudaEventDestroy(c->ev_bm[i]);
         if (c->ev_fa[i]) cudaEventDestroy(c->ev_fa[i]);
         if (c->ev_fb[i]) cudaEventDestroy(c->ev_fb[i]);
     }
@@ -665,6 +669,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
             launch_bucket_merge(c->d, c->bg, c->pc, prev, (int)(f & 1), spec ? 1 : 0, sP);   // FAST winners of the PREVIOUS left image
         }
         if (c->timers) cudaEventRecord(c->ev[2], sP);
+        if (!tm) CU(cudaEventRecord(c->ev_bm[e], sP));
         if (tm) {
             launch_klt(c->d, c->pg, c->pc, c->klt_blocks_full, prev, cur, sP);
         } else if (spec) {
@@ -682,7 +687,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         if (c->timers) cudaEventRecord(c->ev[3], sP);
         {
             TraceScope ts(c, "select", 3, sP);
-            launch_select(c->d, c->pg, c->pc, prev, cur, prev, sP);
+            launch_select(c->d, c->pg, c->pc, prev, cur, prev, (int)(f & 1), sP);
         }
         if (c->timers) cudaEventRecord(c->ev[4], sP);
         CU(cudaEventRecord(c->ev_sel[e], sP));
@@ -719,7 +724,9 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (!tm) {
         CU(cudaEventRecord(c->ev_fb[e], sB));
     } else {   // a later frame may run on the partitions again: it finds every event of this frame signalled
-        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_spf[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
+        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_spf[e], c->ev_bm[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
+        // no speculative pass consumed / refreshed the FAST-pruning predictions: drop them
+        if (c->spec) CU(cudaMemsetAsync(c->d.predT, 0, sizeof(int) * 2 * c->d.n_seq * c->d.nb, sP));
     }
     CU(cudaGetLastError());
     if (c->timers) {
@@ -1166,7 +1173,7 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     }
     CU(cudaMemsetAsync(d.klt_next, 0, sizeof(int), st));
     launch_klt(d, c->pg, c->pc, c->klt_blocks, 0, 1, st);
-    launch_select(d, c->pg, c->pc, 0, 1, detect ? 0 : -1, st);
+    launch_select(d, c->pg, c->pc, 0, 1, detect ? 0 : -1, -1, st);
     CU(cudaMemcpyAsync(&s, d.state, sizeof(s), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());

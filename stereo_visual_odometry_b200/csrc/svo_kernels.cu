@@ -517,6 +517,7 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
     const unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
     const bool spec_ok = use_spec != 0 && s->spec_bad == 0;
     const bool trk_ok = s->fs_from_inliers != 0;
+    int* pred_out = use_spec ? d.predT + ((long long)(specbuf ^ 1) * d.n_seq + seq) * bg.nb : nullptr;
     if (tid == 0) sm_iters = 0;
 
     // winners without / with the thr/4 FAST set: in total and before this tile (low 16 bits | high 16 bits)
@@ -591,6 +592,11 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
                 sp = d.specT_pts; sst = d.specT_st; sit = d.specT_it;
             }
         }
+        uint8_t cst = 0;
+        if (src >= 0) {
+            cst = sst[src];
+            if (cst & 0x80) src = -1;   // pruned from the speculative pass
+        }
         if (src >= 0) {
             const float4 ab = *reinterpret_cast<const float4*>(sp + src * 4);
             const float4 ce = *reinterpret_cast<const float4*>(sp + src * 4 + 2);
@@ -598,8 +604,15 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
             d.lk_R1[fo + off] = make_float2(ab.z, ab.w);
             d.lk_R0[fo + off] = make_float2(ce.x, ce.y);
             d.lk_C[fo + off] = make_float2(ce.z, ce.w);
-            d.lk_status[fo + off] = sst[src];
+            d.lk_status[fo + off] = cst;
             atomicAdd(&sm_iters, sit[src]);
+            // prediction for the next frame's FAST pruning: this feature, if kept, is tracked there one frame older
+            if (pred_out && (cst & 16) && age + pc.age_increment < bg.age_threshold) {
+                const int br = (int)__fdiv_rn(ab.y, (float)bg.bh), bc = (int)__fdiv_rn(ab.x, (float)bg.bw);
+                if (br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw)
+                    atomicMax(pred_out + br * bg.n_bw + bc,
+                              bucket_score(age + pc.age_increment, str, bg.fast_threshold) + 0x8000);
+            }
         } else {
             d.todo[fo + atomicAdd(d.n_todo + seq, 1)] = off;
         }
@@ -724,6 +737,7 @@ int klt_resident_blocks_per_sm() {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, klt_kernel, KLT_WARPS * 32, 0) != cudaSuccess || nb < 1) nb = 3;
     return nb;
 }
+int klt_spec_resident_blocks_per_sm();
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st) {
     dim3 grid(blocks_per_seq, d.n_seq);
@@ -739,7 +753,7 @@ void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int
 // looks its winners up in this cache.  Anything not cached (low-threshold retry, failed PnP, ...) goes through
 // klt_kernel afterwards, so the cache never changes a result, only when it is computed.
 // the buckets that hold a thr-20 FAST winner, as an unordered list (one warp-aggregated atomic per 32 buckets)
-__global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, BucketGeom bg, int keybuf) {
+__global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, BucketGeom bg, int keybuf, int specbuf) {
     const int seq = blockIdx.y, lane = threadIdx.x & 31;
     const int b = blockIdx.x * 256 + threadIdx.x;
     const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
@@ -749,8 +763,9 @@ __global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, Bucket
     if (lane == 0 && m) base = atomicAdd(d.nF + seq, __popc(m));
     base = __shfl_sync(0xffffffffu, base, 0);
     if (has) d.listF[(long long)seq * bg.nb + base + __popc(m & ((1u << lane) - 1u))] = b;
+    (void)specbuf;
 }
-__global__ void __launch_bounds__(KLT_WARPS * 32)
+__global__ void __launch_bounds__(KLT_WARPS * 32, 4)
 klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int keybuf,
                      int specbuf) {
     __shared__ LkScratch patch[KLT_WARPS];
@@ -761,6 +776,7 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
     const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
     const long long so = ((long long)specbuf * d.n_seq + seq) * bg.nb;
     const int* list = d.listF + (long long)seq * bg.nb;
+    const int* pred = d.predT + ((long long)specbuf * d.n_seq + seq) * bg.nb;
     const int n = d.nF[seq];
     int* counter = d.cntF + seq;
     for (;;) {
@@ -769,7 +785,17 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
         t = __shfl_sync(0xffffffffu, t, 0);
         if (t >= n) break;
         const int b = list[t];
-        const unsigned order = bucket_key_order(ld_key(keyA + b));
+        const unsigned long long ka = ld_key(keyA + b);
+        // A FAST winner only enters circular matching when it beats every tracked feature of its bucket (strictly
+        // greater score).  bucket_merge_kernel of the previous frame predicts, per bucket, the best score a tracked
+        // feature will have there; once that prediction is in (it arrives while this kernel runs), FAST winners
+        // that cannot beat it are skipped and flagged "not computed".  A wrong prediction (the tracked feature
+        // turns out a PnP outlier) is only a cache miss: the FAST winner then goes through klt_kernel.
+        if (bucket_key_score(ka) + 0x8000 <= __ldcg(pred + b)) {
+            if (lane == 0) d.specF_st[so + b] = 0x80;
+            continue;
+        }
+        const unsigned order = bucket_key_order(ka);
         const int pix = (int)(order - SVO_FAST_ORDER_BASE);
         const int y = pix / pc.width;
         const float2 p0 = make_float2((float)(pix - y * pc.width), (float)y);
@@ -785,7 +811,7 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
         }
     }
 }
-__global__ void __launch_bounds__(KLT_WARPS * 32)
+__global__ void __launch_bounds__(KLT_WARPS * 32, 4)
 klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
@@ -813,11 +839,16 @@ klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int s
         }
     }
 }
+int klt_spec_resident_blocks_per_sm() {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, klt_spec_trk_kernel, KLT_WARPS * 32, 0) != cudaSuccess || nb < 1) nb = 3;
+    return nb;
+}
 void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
                           int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st) {
     cudaMemsetAsync(d.cntF, 0, sizeof(int) * d.n_seq, st);
     cudaMemsetAsync(d.nF, 0, sizeof(int) * d.n_seq, st);
-    spec_fast_list_kernel<<<dim3((bg.nb + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg, keybuf);
+    spec_fast_list_kernel<<<dim3((bg.nb + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg, keybuf, specbuf);
     dim3 grid(blocks_per_seq, d.n_seq);
     klt_spec_fast_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur, keybuf, specbuf);
 }
@@ -911,7 +942,7 @@ void launch_pnp_samples(const DevArrays& d, cudaStream_t st) { pnp_samples_kerne
 // inter-block dependency exists; the last block only counts, builds the RANSAC samples and updates the state.
 constexpr int SEL_T = 256;
 __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev,
-                                                       int slot_cur, int nb, int keybuf) {
+                                                       int slot_cur, int nb, int keybuf, int predbuf) {
     __shared__ int sm[SEL_T / 32 + 1];
     __shared__ int mods[SVO_RNG_TABLE];
     const int seq = blockIdx.y, tid = threadIdx.x;
@@ -920,6 +951,10 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
     const int n = s->n_bucketed;
     const bool tail = blockIdx.x == gridDim.x - 1;
     const int t0 = tail ? n : blockIdx.x * SEL_T;
+    if (predbuf >= 0) {   // FAST-pruning predictions of two frames ahead start from "none"
+        int* pr = d.predT + ((long long)predbuf * d.n_seq + seq) * nb;
+        for (int i = blockIdx.x * SEL_T + tid; i < nb; i += gridDim.x * SEL_T) pr[i] = 0;
+    }
     if (keybuf >= 0) {
         // the bucket keys of this frame are consumed (every block of bucket_merge_kernel read all of them):
         // ready for the next frame / the next FAST pass into this ring buffer
@@ -993,9 +1028,9 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
     }
 }
 void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
-                   int keybuf, cudaStream_t st) {
+                   int keybuf, int predbuf, cudaStream_t st) {
     dim3 grid((d.cap + SEL_T - 1) / SEL_T + 1, d.n_seq);
-    select_kernel<<<grid, SEL_T, 0, st>>>(d, pg, pc, slot_prev, slot_cur, d.nb, keybuf);
+    select_kernel<<<grid, SEL_T, 0, st>>>(d, pg, pc, slot_prev, slot_cur, d.nb, keybuf, predbuf);
 }
 
 // ============================================================================

@@ -41,12 +41,14 @@ void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfi
                           int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st);
 void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
                          int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st);
-int klt_resident_blocks_per_sm();   // persistent KLT blocks that fit one SM (occupancy query)
+int klt_resident_blocks_per_sm();
+int klt_spec_resident_blocks_per_sm();   // same for the speculative kernels   // persistent KLT blocks that fit one SM (occupancy query)
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st);
 // keybuf >= 0: also clears the FAST key buffer `keybuf` and the tracked-key scratch (consumed by bucket_merge)
+// predbuf >= 0: also resets that buffer of FAST-pruning predictions (the one the frame after next reads)
 void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int slot_prev, int slot_cur,
-                   int keybuf, cudaStream_t st);
+                   int keybuf, int predbuf, cudaStream_t st);
 void launch_pnp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);
 void launch_pnp_final(const DevArrays& d, const PipeConfig& pc, cudaStream_t st);     // a then b
