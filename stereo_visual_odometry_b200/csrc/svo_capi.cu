@@ -108,6 +108,7 @@ struct svo_ctx {
     const char* trace_path = nullptr;
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
+    int f_share = 50;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
     cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
     cudaEvent_t ev_trk[4] = {nullptr, nullptr, nullptr, nullptr};   // speculative KLT of frame f complete
@@ -227,6 +228,10 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
     if (const char* e = getenv("SVO_PARTITION")) {
         want_chain = want_in = 0;
         sscanf(e, "%d,%d", &want_chain, &want_in);
+    }
+    if (const char* e = getenv("SVO_FSHARE")) {
+        const int v = atoi(e);
+        if (v >= 10 && v <= 90) c->f_share = v;
     }
     if (!c->spec || p->n_seq != 1) want_chain = want_in = 0;
     cudaDeviceProp prop;
@@ -639,7 +644,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (spec && !first) {
         // the two candidate classes run side by side, each on half of the partition's block slots: F(f) as soon
         // as image f is there (typically a frame ahead), T(f) the moment select(f - 1) has produced the matched list
-        const int half = c->klt_blocks_k > 1 ? c->klt_blocks_k / 2 : 1;
+        const int half = c->klt_blocks_k > 1 ? (int)((long long)c->klt_blocks_k * c->f_share / 100) : 1;
         cudaStream_t sK2 = c->stream_k2;
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
         {

@@ -157,13 +157,16 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
     // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
     const int tx0 = x0 - 8, ty0 = y0 - 4;
-    const bool fastpath = tx0 >= 0 && ty0 >= 0 && tx0 + FT_TW <= w && ty0 + FT_TH <= h && (pitch & 3) == 0 &&
-                          (((size_t)src) & 3) == 0;
+    // Out-of-image bytes only ever feed pixels whose score is forced to 0 (the 3-pixel border), so whole words
+    // are fetched with the word column / row clamped into the plane (needs a word-aligned plane whose pitch
+    // covers the last word that holds valid pixels).
+    const bool fastpath = (pitch & 3) == 0 && (((size_t)src) & 3) == 0 && ((w + 3) & ~3) <= pitch;
     if (fastpath) {
+        const int wmax = ((w + 3) >> 2) - 1;
         for (int i = tid; i < FT_TH * (FT_TW / 4); i += FT_THREADS) {
             const int r = i / (FT_TW / 4), k = i - r * (FT_TW / 4);
-            reinterpret_cast<unsigned*>(tile)[i] =
-                __ldg(reinterpret_cast<const unsigned*>(src + (long long)(ty0 + r) * pitch + tx0) + k);
+            const int gy = min(max(ty0 + r, 0), h - 1), gk = min(max((tx0 >> 2) + k, 0), wmax);
+            reinterpret_cast<unsigned*>(tile)[i] = __ldg(reinterpret_cast<const unsigned*>(src + (long long)gy * pitch) + gk);
         }
     } else {
         for (int i = tid; i < FT_TH * FT_TW; i += FT_THREADS) {
@@ -222,24 +225,47 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     }
     __syncthreads();
 
-    // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs
-    for (int i = tid; i < FT_OH * FT_OW; i += FT_THREADS) {
-        const int oy = i / FT_OW, ox = i - oy * FT_OW;
-        const int gx = x0 + ox, gy = y0 + oy;
-        if (gx >= w || gy >= h) continue;
-        const uint8_t* sp = score + (oy + 1) * FT_SW + (ox + 4);
-        const int v = sp[0];
-        const bool keep = v > 0 && v > sp[-1] && v > sp[1] && v > sp[-FT_SW - 1] && v > sp[-FT_SW] &&
-                          v > sp[-FT_SW + 1] && v > sp[FT_SW - 1] && v > sp[FT_SW] && v > sp[FT_SW + 1];
-        if (resp_map) resp_map[(long long)z * map_stride + (long long)gy * map_pitch + gx] = keep ? (uint8_t)v : 0;
-        if (keep && keysB) {
-            const int br = gy / bg.bh, bc = gx / bg.bw;
-            if (br >= bg.start_row && 0 < bg.age_threshold) {
-                const unsigned long long key =
-                    bucket_key(bucket_score(0, v, bg.fast_threshold), SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
-                const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
-                atomicMax(keysB + bidx, key);
-                if (v >= thr_hi) atomicMax(keysA + bidx, key);
+    // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs, one output quad per task: most score
+    // words are zero and are dismissed with one load
+    const float inv_bh = 1.f / (float)bg.bh, inv_bw = 1.f / (float)bg.bw;
+    for (int i = tid; i < FT_OH * (FT_OW / 4); i += FT_THREADS) {
+        const int oy = i / (FT_OW / 4), oq = i - oy * (FT_OW / 4);
+        const int gx0 = x0 + 4 * oq, gy = y0 + oy;
+        if (gx0 >= w || gy >= h) continue;
+        const uint8_t* sp0 = score + (oy + 1) * FT_SW + 4 * (oq + 1);
+        const unsigned sw = *reinterpret_cast<const unsigned*>(sp0);
+        unsigned outw = 0;
+        if (sw != 0u) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int v = (sw >> (8 * e)) & 0xFF;
+                if (v == 0) continue;
+                const uint8_t* sp = sp0 + e;
+                const bool keep = v > sp[-1] && v > sp[1] && v > sp[-FT_SW - 1] && v > sp[-FT_SW] && v > sp[-FT_SW + 1] &&
+                                  v > sp[FT_SW - 1] && v > sp[FT_SW] && v > sp[FT_SW + 1];
+                const int gx = gx0 + e;
+                if (!keep || gx >= w) continue;
+                outw |= (unsigned)v << (8 * e);
+                if (keysB) {
+                    // exact for these small integers: the quotient is never within an ulp of an integer from below
+                    const int br = (int)(((float)gy + 0.5f) * inv_bh), bc = (int)(((float)gx + 0.5f) * inv_bw);
+                    if (br >= bg.start_row && 0 < bg.age_threshold) {
+                        const unsigned long long key = bucket_key(bucket_score(0, v, bg.fast_threshold),
+                                                                  SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
+                        const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
+                        atomicMax(keysB + bidx, key);
+                        if (v >= thr_hi) atomicMax(keysA + bidx, key);
+                    }
+                }
+            }
+        }
+        if (resp_map) {
+            uint8_t* o = resp_map + (long long)z * map_stride + (long long)gy * map_pitch + gx0;
+            if (gx0 + 3 < w && (map_pitch & 3) == 0 && ((size_t)(resp_map + (long long)z * map_stride) & 3) == 0) {
+                *reinterpret_cast<unsigned*>(o) = outw;
+            } else {
+                for (int e = 0; e < 4; ++e)
+                    if (gx0 + e < w) o[e] = (uint8_t)(outw >> (8 * e));
             }
         }
     }
