@@ -273,6 +273,7 @@ inline cv::Mat getInverseTransform(const cv::Mat& rotation, const cv::Mat& trans
 class VisualOdometry {
    private:
     int frame_id = 0;
+    cv::Mat pendingLeft_, pendingRight_;     /* last submitted frame (streaming calls) */
     svo_ctx* ctx_ = nullptr;                 /* device-resident state (pyramids, currentVOFeatures, R|t, last_transform) */
     cv::Mat imageRightT0_, imageLeftT0_;     /* host copies kept only for the stateless public circularMatching() */
     cv::Mat_<float64> last_transform = cv::Mat_<float64>::eye(4, 4);
@@ -344,6 +345,40 @@ class VisualOdometry {
         ++frame_id;
         if (ok) last_transform = T;
         return std::make_pair(ok != 0, T);
+    }
+
+    /* Streaming form of stereo_callback (not in the reference): submit_frame enqueues a frame and returns at
+     * once, collect_frame returns the result of the oldest submitted frame -- exactly what stereo_callback would
+     * have returned, in order.  With a few frames in flight the ingest and the speculative tracking of the next
+     * frame overlap the pose chain of the current one (svo_submit_frame / svo_collect in svo.h).  The images must
+     * stay alive (ideally in pinned memory) until the frame is collected; 8UC1 with equal strides. */
+    void submit_frame(const cv::Mat& image_left, const cv::Mat& image_right) {
+        int sl, sr;
+        const uint8_t* L = detail::gray(image_left, sl);
+        const uint8_t* R = detail::gray(image_right, sr);
+        if (image_left.rows != image_right.rows || image_left.cols != image_right.cols || sl != sr)
+            throw std::runtime_error("svo: submit_frame needs equally sized images with equal strides");
+        ensure_ctx(image_left);
+        if (leftCameraProjection_.empty()) {
+            float z[12] = {0};
+            detail::check(svo_set_projection(ctx_, z, z));
+        }
+        detail::check(svo_submit_frame(ctx_, L, R, sl));
+        pendingLeft_ = image_left;   /* shallow references: keep the buffers alive */
+        pendingRight_ = image_right;
+    }
+    std::pair<bool, cv::Mat_<float64>> collect_frame() {
+        svo_frame_result r;
+        detail::check(svo_collect(ctx_, &r));
+        cv::Mat_<float64> T(4, 4);
+        std::memcpy(T.ptr<double>(0), r.transform, sizeof(double) * 16);
+        ++frame_id;
+        if (r.success) last_transform = T;
+        if (svo_pending(ctx_) == 0) {
+            pendingLeft_.copyTo(imageLeftT0_);
+            pendingRight_.copyTo(imageRightT0_);
+        }
+        return std::make_pair(r.success != 0, T);
     }
 
     /* vo.h:354-362 / vo.cpp:315-366 */

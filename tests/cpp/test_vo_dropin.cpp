@@ -158,6 +158,33 @@ static void first_frame_contract() {
     REQUIRE(r1.first == false && r1.second(0, 0) == 1.0 && r1.second(0, 3) == 0.0);
 }
 
+// streaming calls return what the synchronous ones return, in order
+static void streaming_matches_sync() {
+    cv::Mat imgs[5];
+    for (int k = 0; k < 5; ++k) {
+        imgs[k] = blank(200, 320);
+        for (int y = 40; y < 180; y += 24)
+            for (int x = 30 + 2 * k; x < 300; x += 28) stamp(imgs[k], x, y, 6);
+    }
+    VisualOdometry a, b;
+    cv::Mat_<float> P(3, 4);
+    const float pv[12] = {300.f, 0.f, 160.f, 0.f, 0.f, 300.f, 100.f, 0.f, 0.f, 0.f, 1.f, 0.f};
+    for (int i = 0; i < 12; ++i) P(i / 4, i % 4) = pv[i];
+    cv::Mat_<float> Pr = P.clone();
+    Pr(0, 3) = -30.f;
+    a.initalize_projection_matricies(P, Pr);
+    b.initalize_projection_matricies(P, Pr);
+    std::pair<bool, cv::Mat_<double>> ref[5];
+    for (int k = 0; k < 5; ++k) ref[k] = a.stereo_callback(imgs[k], imgs[k]);
+    for (int k = 0; k < 5; ++k) b.submit_frame(imgs[k], imgs[k]);
+    for (int k = 0; k < 5; ++k) {
+        auto r = b.collect_frame();
+        REQUIRE(r.first == ref[k].first);
+        for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 4; ++j) REQUIRE(r.second(i, j) == ref[k].second(i, j));
+    }
+}
+
 int main() {
     std::printf("TEST BUCKET POLICY\n");        bucket_policy();
     std::printf("TEST FEATURE SET\n");          featureset_counts();
@@ -166,6 +193,7 @@ int main() {
     std::printf("TEST CIRCULAR MATCHING\n");    circular_matching();
     std::printf("TEST CAMERA TO WORLD\n");      camera_to_world();
     std::printf("TEST FIRST FRAME\n");          first_frame_contract();
+    std::printf("TEST STREAMING\n");            streaming_matches_sync();
     std::printf("ALL TESTS PASS\n");
     return 0;
 }

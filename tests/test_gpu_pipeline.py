@@ -172,6 +172,13 @@ def test_streaming_submit_collect_matches_synchronous_calls():
         assert ok0 == ok1 and np.array_equal(T0, T1)
     with pytest.raises(V.SvoError):
         b.collect()   # nothing pending
+    # the streaming context really ran the speculative path: the last frame found (nearly) all of its
+    # circular-matching results in the cache
+    import ctypes as C
+    info = (C.c_int * 8)()
+    V.check(V.lib().svo_pipeline_info(b._ctx, info))
+    assert info[0] == 1, "speculative tracking is off"
+    assert info[4] <= 0.02 * b.last_result().n_bucketed + 3, f"cache misses: {info[4]}"
 
 
 def test_empty_frame_keeps_the_previous_pyramids():
