@@ -12,7 +12,8 @@
  *     call), < 0 is an `svo_status` error.  There is NO CPU fallback: without
  *     a CUDA device every compute call returns SVO_ERR_NO_DEVICE.
  *   - all pointers are HOST pointers unless the name ends in `_dev`.
- *   - images are 8-bit single channel, row stride in bytes given explicitly.
+ *   - images are 8-bit single channel (or interleaved 3-channel when svo_params.channels == 3; the stage-level
+ *     entry points other than svo_lk_track are single channel), row stride in bytes given explicitly.
  *   - points are interleaved float32 (x, y); 3-D points interleaved (x, y, z).
  *
  * Reference citations (file:line) are relative to Alex7Li/stereo_visual_odometry.
@@ -62,6 +63,9 @@ typedef struct svo_params {
     double max_rotation_norm;     /* .5   vo.h MAX_ROTATION_NORM                 */
     uint64_t ransac_seed;         /* seed of the hypothesis sample stream        */
     int device;                   /* CUDA device ordinal                         */
+    int channels;                 /* 1 = 8UC1 (default); 3 = interleaved 8UC3 exactly as the reference CLI feeds
+                                     cv::imread's BGR images (src/main.cpp:37-46): FAST scans the first `width`
+                                     bytes of every row, pyramids and LK run on all three channels        */
 } svo_params;
 
 /* Per-frame result of the pipeline (one per sequence). */

@@ -64,15 +64,19 @@ inline int check(int rc) {
     if (rc < 0) throw std::runtime_error(std::string("svo: ") + svo_last_error());
     return rc;
 }
-/* 8-bit single-channel view of a cv::Mat (the 8UC1 contract) */
+/* 8-bit view of a cv::Mat: 8UC1 (the contract) or 8UC3 exactly as the reference's CLI passes cv::imread's BGR
+ * images through (main.cpp:37-46): FAST then scans the first `cols` bytes of every row, the pyramids and
+ * LK use all three channels -- svo_params.channels = 3 */
 inline const uint8_t* gray(const cv::Mat& m, int& stride) {
-    if (m.empty() || m.type() != CV_8UC1) throw std::runtime_error("svo: images must be CV_8UC1");
+    if (m.empty() || (m.type() != CV_8UC1 && m.type() != CV_8UC3))
+        throw std::runtime_error("svo: images must be CV_8UC1 (or CV_8UC3, CLI-faithful mode)");
     stride = (int)m.step;
     return m.data;
 }
 inline svo_params params_for(const cv::Mat& img) {
     svo_params p;
     svo_default_params(&p, img.cols, img.rows);
+    p.channels = img.channels();
     return p;
 }
 }  // namespace detail
@@ -321,15 +325,17 @@ class VisualOdometry {
         int sl, sr;
         const uint8_t* L = detail::gray(image_left, sl);
         const uint8_t* R = detail::gray(image_right, sr);
-        if (image_left.rows != image_right.rows || image_left.cols != image_right.cols)
-            throw std::runtime_error("svo: left / right image sizes differ");
+        if (image_left.rows != image_right.rows || image_left.cols != image_right.cols ||
+            image_left.type() != image_right.type())
+            throw std::runtime_error("svo: left / right image sizes or types differ");
         cv::Mat rtmp;
         if (sl != sr) {   /* the C ABI takes one stride: repack the right image */
-            rtmp = cv::Mat(image_right.rows, image_right.cols, CV_8UC1);
-            cv::Mat ltmp(image_left.rows, image_left.cols, CV_8UC1);
+            rtmp = cv::Mat(image_right.rows, image_right.cols, image_left.type());
+            cv::Mat ltmp(image_left.rows, image_left.cols, image_left.type());
+            const size_t row_bytes = (size_t)image_left.cols * image_left.channels();
             for (int r = 0; r < image_left.rows; ++r) {
-                std::memcpy(ltmp.data + (size_t)r * ltmp.step, L + (size_t)r * sl, image_left.cols);
-                std::memcpy(rtmp.data + (size_t)r * rtmp.step, R + (size_t)r * sr, image_left.cols);
+                std::memcpy(ltmp.data + (size_t)r * ltmp.step, L + (size_t)r * sl, row_bytes);
+                std::memcpy(rtmp.data + (size_t)r * rtmp.step, R + (size_t)r * sr, row_bytes);
             }
             return stereo_callback(ltmp, rtmp);
         }

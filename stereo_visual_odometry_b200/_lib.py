@@ -33,7 +33,7 @@ class Params(C.Structure):
         ("ransac_reproj_error", C.c_float), ("ransac_iterations", C.c_int),
         ("ransac_hypotheses", C.c_int), ("ransac_confidence", C.c_float),
         ("max_translation_norm", C.c_double), ("max_rotation_norm", C.c_double),
-        ("ransac_seed", C.c_uint64), ("device", C.c_int),
+        ("ransac_seed", C.c_uint64), ("device", C.c_int), ("channels", C.c_int),
     ]
 
 

@@ -82,6 +82,7 @@ extern "C" void svo_default_params(svo_params* p, int width, int height) {
     p->max_rotation_norm = 0.5;
     p->ransac_seed = 0x5eed5eedULL;
     p->device = 0;
+    p->channels = 1;
 }
 
 // ---------------------------------------------------------------------------
@@ -148,9 +149,11 @@ static BucketGeom make_bucket_geom(int height, int width, int n_bh, int n_bw, in
 }
 
 // cv::buildOpticalFlowPyramid stops when a level would be <= winSize in either dimension
-static PyrGeom make_pyr_geom(int w, int h, int max_level, int win) {
+static int channels_of(const svo_params& p) { return p.channels == 3 ? 3 : 1; }
+static PyrGeom make_pyr_geom(int w, int h, int max_level, int win, int cn = 1) {
     PyrGeom pg;
     memset(&pg, 0, sizeof(pg));
+    pg.cn = cn;
     long long off = 0;
     int lw = w, lh = h, l = 0;
     for (; l <= max_level && l < SVO_MAX_LEVELS; ++l) {
@@ -162,7 +165,7 @@ static PyrGeom make_pyr_geom(int w, int h, int max_level, int win) {
         }
         pg.w[l] = lw;
         pg.h[l] = lh;
-        pg.pitch[l] = (lw + 127) & ~127;
+        pg.pitch[l] = (lw * cn + 127) & ~127;
         pg.off[l] = off;
         off += (long long)pg.pitch[l] * lh;
     }
@@ -206,6 +209,8 @@ static int validate_params(const svo_params* p) {
         return fail(SVO_ERR_INVALID, "image size out of range (16..8192)");
     if ((long long)p->width * p->height >= (1ll << 24)) return fail(SVO_ERR_INVALID, "image has >= 2^24 pixels");
     if (p->n_seq < 1) return fail(SVO_ERR_INVALID, "n_seq < 1");
+    if (p->channels != 0 && p->channels != 1 && p->channels != 3)
+        return fail(SVO_ERR_INVALID, "channels must be 1 (8UC1) or 3 (interleaved 8UC3, the reference CLI's images)");
     if (p->win_size != SVO_LK_WIN) return fail(SVO_ERR_INVALID, "only winSize 10x10 (vo.h:251) is built");
     if (p->max_level < 0 || p->max_level >= SVO_MAX_LEVELS) return fail(SVO_ERR_INVALID, "max_level must be 0..3");
     if (p->buckets_along_height < 1 || p->buckets_along_width < 1) return fail(SVO_ERR_INVALID, "bad bucket grid");
@@ -222,9 +227,9 @@ static int validate_params(const svo_params* p) {
 // SVO_SPEC=0/1 overrides whether the speculative tracking runs (default: single-sequence contexts only).
 static int create_streams(svo_ctx* c, const svo_params* p) {
     int want_chain = 16, want_in = 8;
-    c->spec = p->n_seq == 1 && c->pipeline_ctx;
+    c->spec = p->n_seq == 1 && c->pipeline_ctx && channels_of(*p) == 1;   // 8UC3 mode: plain serial frames
     if (const char* e = getenv("SVO_SPEC"))
-        if (c->pipeline_ctx) c->spec = atoi(e) != 0;
+        if (c->pipeline_ctx && channels_of(*p) == 1) c->spec = atoi(e) != 0;
     if (const char* e = getenv("SVO_PARTITION")) {
         want_chain = want_in = 0;
         sscanf(e, "%d,%d", &want_chain, &want_in);
@@ -346,7 +351,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         c->ev_done[i] = nullptr;
         CU(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
     }
-    c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size);
+    c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size, channels_of(*p));
     c->bg = make_bucket_geom(p->height, p->width, p->buckets_along_height, p->buckets_along_width,
                              p->bucket_start_row, p->age_threshold, p->fast_threshold);
     PipeConfig& pc = c->pc;
@@ -760,7 +765,7 @@ extern "C" int svo_process_frame_batch_dev(svo_ctx* c, const uint8_t* left_dev, 
                                            long long seq_stride, svo_frame_result* results_dev) {
     if (!c || !left_dev || !right_dev) return fail(SVO_ERR_INVALID, "NULL argument");
     if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
-    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    if (stride < c->p.width * c->pg.cn) return fail(SVO_ERR_INVALID, "stride < width * channels");
     CU(cudaSetDevice(c->p.device));
     int rc = wait_ring(c, true);
     if (rc != SVO_OK) return rc;
@@ -771,14 +776,14 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
                                       long long seq_stride) {
     if (!c || !left || !right) return fail(SVO_ERR_INVALID, "NULL argument");
     if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
-    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    if (stride < c->p.width * c->pg.cn) return fail(SVO_ERR_INVALID, "stride < width * channels");
     if (c->tracked - c->collected >= SVO_RESULT_RING)
         return fail(SVO_ERR_STATE, "result ring full: call svo_collect before submitting more frames");
     CU(cudaSetDevice(c->p.device));
     const bool in_flight = c->tracked > c->collected;   // streaming caller: an earlier frame is still uncollected
     int rc = wait_ring(c, in_flight);
     if (rc != SVO_OK) return rc;
-    const int S = c->d.n_seq, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
+    const int S = c->d.n_seq, W = c->p.width * c->pg.cn /* row bytes */, H = c->p.height, P0 = c->pg.pitch[0];
     const long long plane = (long long)P0 * H;
     cudaStream_t sI = ingest_stream(c, in_flight);
     if (S == 1) {
@@ -1052,11 +1057,15 @@ struct DevPyr {
         return p;
     }
 };
-int build_dev_pyr(Scratch& s, DevPyr& out, const uint8_t* img, int w, int h, int stride, int max_level, int win) {
-    out.pg = make_pyr_geom(w, h, max_level, win);
+int build_dev_pyr(Scratch& s, DevPyr& out, const uint8_t* img, int w, int h, int stride, int max_level, int win,
+                  int cn = 1) {
+    out.pg = make_pyr_geom(w, h, max_level, win, cn);
     CU(s.alloc(&out.base, (size_t)out.pg.image_bytes));
-    CU(cudaMemcpy2DAsync(out.base, out.pg.pitch[0], img, stride, w, h, cudaMemcpyHostToDevice, s.st));
-    for (int l = 1; l < out.pg.nlevels; ++l)
+    CU(cudaMemcpy2DAsync(out.base, out.pg.pitch[0], img, stride, (size_t)w * cn, h, cudaMemcpyHostToDevice, s.st));
+    for (int l = 1; l < out.pg.nlevels && cn != 1; ++l)
+        launch_pyrdown_cn(out.base + out.pg.off[l - 1], out.pg.w[l - 1], out.pg.h[l - 1], out.pg.pitch[l - 1],
+                          out.base + out.pg.off[l], out.pg.w[l], out.pg.h[l], out.pg.pitch[l], cn, s.st);
+    for (int l = 1; l < out.pg.nlevels && cn == 1; ++l)
         launch_pyrdown(out.base + out.pg.off[l - 1], 0, out.pg.w[l - 1], out.pg.h[l - 1], out.pg.pitch[l - 1],
                        out.base + out.pg.off[l], 0, out.pg.w[l], out.pg.h[l], out.pg.pitch[l], 1, s.st);
     return SVO_OK;
@@ -1092,7 +1101,8 @@ extern "C" int svo_lk_track(const svo_params* p, const uint8_t* prev_img, const 
                             const float* pts_in, int n, float* pts_out, uint8_t* status_out) {
     int rc = validate_params(p);
     if (rc != SVO_OK) return rc;
-    if (!prev_img || !next_img || n < 0 || (n > 0 && (!pts_in || !pts_out || !status_out)) || stride < p->width)
+    if (!prev_img || !next_img || n < 0 || (n > 0 && (!pts_in || !pts_out || !status_out)) ||
+        stride < p->width * channels_of(*p))
         return fail(SVO_ERR_INVALID, "bad argument");
     rc = need_device();
     if (rc != SVO_OK) return rc;
@@ -1100,9 +1110,10 @@ extern "C" int svo_lk_track(const svo_params* p, const uint8_t* prev_img, const 
     Scratch s;
     CU(cudaStreamCreate(&s.st));
     DevPyr I, J;
-    rc = build_dev_pyr(s, I, prev_img, p->width, p->height, stride, p->max_level, p->win_size);
+    const int cn = channels_of(*p);
+    rc = build_dev_pyr(s, I, prev_img, p->width, p->height, stride, p->max_level, p->win_size, cn);
     if (rc != SVO_OK) return rc;
-    rc = build_dev_pyr(s, J, next_img, p->width, p->height, stride, p->max_level, p->win_size);
+    rc = build_dev_pyr(s, J, next_img, p->width, p->height, stride, p->max_level, p->win_size, cn);
     if (rc != SVO_OK) return rc;
     float2 *din, *dout;
     uint8_t* dst;
@@ -1110,7 +1121,8 @@ extern "C" int svo_lk_track(const svo_params* p, const uint8_t* prev_img, const 
     CU(s.alloc(&dout, (size_t)n));
     CU(s.alloc(&dst, (size_t)n));
     CU(cudaMemcpyAsync(din, pts_in, sizeof(float2) * n, cudaMemcpyHostToDevice, s.st));
-    launch_lk_single(I.lk(), J.lk(), make_lk_config(*p, I.pg.nlevels), din, n, dout, dst, s.st);
+    if (cn != 1) launch_lk_single_cn(I.lk(), J.lk(), make_lk_config(*p, I.pg.nlevels), cn, din, n, dout, dst, s.st);
+    else launch_lk_single(I.lk(), J.lk(), make_lk_config(*p, I.pg.nlevels), din, n, dout, dst, s.st);
     CU(cudaMemcpyAsync(pts_out, dout, sizeof(float2) * n, cudaMemcpyDeviceToHost, s.st));
     CU(cudaMemcpyAsync(status_out, dst, n, cudaMemcpyDeviceToHost, s.st));
     CU(cudaStreamSynchronize(s.st));
@@ -1136,7 +1148,7 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     } guard{c};
     c->pc.check_bounds = check_bounds ? 1 : 0;
     c->pc.age_increment = 0;
-    const int W = q.width, H = q.height, P0 = c->pg.pitch[0];
+    const int W = q.width * c->pg.cn /* row bytes */, H = q.height, P0 = c->pg.pitch[0];
     const long long plane = (long long)P0 * H;
     DevArrays& d = c->d;
     cudaStream_t st = c->stream;
@@ -1211,7 +1223,7 @@ extern "C" int svo_circular_match(const svo_params* p, const uint8_t* L0, const 
                                   uint8_t* keep_out) {
     int rc = validate_params(p);
     if (rc != SVO_OK) return rc;
-    if (!L0 || !R0 || !L1 || !R1 || n < 0 || (n > 0 && !pL0) || stride < p->width)
+    if (!L0 || !R0 || !L1 || !R1 || n < 0 || (n > 0 && !pL0) || stride < p->width * channels_of(*p))
         return fail(SVO_ERR_INVALID, "bad argument");
     rc = need_device();
     if (rc != SVO_OK) return rc;
@@ -1226,7 +1238,7 @@ extern "C" int svo_matching_features(const svo_params* p, const uint8_t* L0, con
     int rc = validate_params(p);
     if (rc != SVO_OK) return rc;
     if (!L0 || !R0 || !L1 || !R1 || !n_fs || *n_fs < 0 || fs_cap < *n_fs || !fs_xy || !fs_age || !fs_str ||
-        stride < p->width)
+        stride < p->width * channels_of(*p))
         return fail(SVO_ERR_INVALID, "bad argument");
     rc = need_device();
     if (rc != SVO_OK) return rc;

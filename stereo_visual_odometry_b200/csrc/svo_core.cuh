@@ -144,6 +144,7 @@ SVO_HD void lk_config_finish(LkConfig& c) {
 struct SerialRed {
     static SVO_HD int sum(int v) { return v; }
     static SVO_HD long long sum64(long long v) { return v; }
+    static SVO_HD long long sum64g(long long v) { return v; }
     // exact integer sums of the two mismatch accumulators, converted to float32 (round to nearest)
     static SVO_HD void sum2f(long long a, long long b, bool, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
     static SVO_HD void sync() {}
@@ -519,6 +520,173 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
     }
     // err is requested by the reference (vo.cpp:203-215) without
     // OPTFLOW_LK_GET_MIN_EIGENVALS: OpenCV re-checks the final window position.
+    if (status) {
+        const int fx = floor_int(fsub(nx, half_win)), fy = floor_int(fsub(ny, half_win));
+        const LkLevel J0 = Jpyr.lv[0];
+        if (fx < -SVO_LK_WIN || fx >= J0.w || fy < -SVO_LK_WIN || fy >= J0.h) status = 0;
+    }
+    outx = nx;
+    outy = ny;
+    iters_out = iters;
+    return status;
+}
+
+// ---------------------------------------------------------------------------
+// Multi-channel variant (interleaved 8UCn images, n <= 3): what cv::calcOpticalFlowPyrLK does when the
+// reference's CLI feeds it the BGR images cv::imread returns (src/main.cpp:37-46).  Same arithmetic
+// as lk_track_feature with the window widened to 10 x 10n interleaved samples (horizontal neighbour = +n bytes,
+// Scharr per channel, the 2 x 2 system summed over all samples, minEig still divided by 2 * 100).  This path
+// serves the CLI-faithful mode only and is written for clarity: samples are distributed round-robin over the
+// lanes, the next image is read through the cache instead of a staged patch.
+#define SVO_LK_CN_MAX 3
+#define SVO_LK_CN_IP (SVO_LK_PATCH * SVO_LK_CN_MAX + 1)   // template neighbourhood pitch (bytes)
+#define SVO_LK_CN_DP (SVO_LK_DW * SVO_LK_CN_MAX + 1)      // derivative patch pitch (samples)
+#define SVO_LK_CN_N (SVO_LK_NPIX * SVO_LK_CN_MAX)         // samples of the window
+struct LkScratchCn {
+    uint8_t ipatch[SVO_LK_PATCH * SVO_LK_CN_IP];
+    short dxp[SVO_LK_DW * SVO_LK_CN_DP];
+    short dyp[SVO_LK_DW * SVO_LK_CN_DP];
+    short iv[SVO_LK_CN_N], ixv[SVO_LK_CN_N], iyv[SVO_LK_CN_N];
+};
+
+template <int LANES, class Red>
+SVO_HD int lk_track_feature_cn(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const LkConfig& cfg, int cn,
+                               float ptx, float pty, int lane, LkScratchCn& sc, float& outx, float& outy,
+                               int& iters_out) {
+    const float half_win = 4.5f;
+    const float FLT_SCALE = 1.f / (1 << 20);
+    const int wn = SVO_LK_WIN * cn;          // samples per window row
+    const int nsamp = SVO_LK_WIN * wn;
+    int status = 1;
+    float nx = 0.f, ny = 0.f;
+    int iters = 0;
+    for (int level = cfg.nlevels - 1; level >= 0; --level) {
+        const LkLevel I = Ipyr.lv[level];
+        const LkLevel J = Jpyr.lv[level];
+        const float scale = 1.f / (float)(1 << level);
+        float prx = fmul(ptx, scale), pry = fmul(pty, scale);
+        if (level == cfg.nlevels - 1) {
+            nx = prx;
+            ny = pry;
+        } else {
+            nx = fmul(nx, 2.f);
+            ny = fmul(ny, 2.f);
+        }
+        prx = fsub(prx, half_win);
+        pry = fsub(pry, half_win);
+        const int ipx = floor_int(prx), ipy = floor_int(pry);
+        if (ipx < -SVO_LK_WIN || ipx >= I.w || ipy < -SVO_LK_WIN || ipy >= I.h) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        int iw00, iw01, iw10, iw11;
+        lk_weights(fsub(prx, (float)ipx), fsub(pry, (float)ipy), iw00, iw01, iw10, iw11);
+
+        // 13 x 13 pixel neighbourhood of the template window, BORDER_REFLECT_101 per pixel
+        Red::sync();
+        const int pn = SVO_LK_PATCH * cn;
+        for (int idx = lane; idx < SVO_LK_PATCH * pn; idx += LANES) {
+            const int py = idx / pn, pb = idx - py * pn;
+            const int px = pb / cn, ch = pb - px * cn;
+            sc.ipatch[py * SVO_LK_CN_IP + pb] =
+                I.img[(size_t)reflect101(ipy - 1 + py, I.h) * I.pitch + reflect101(ipx - 1 + px, I.w) * cn + ch];
+        }
+        Red::sync();
+        // Scharr per channel on the 11 x 11 pixel positions (zero outside the level)
+        const int dn = SVO_LK_DW * cn;
+        for (int idx = lane; idx < SVO_LK_DW * dn; idx += LANES) {
+            const int y = idx / dn, xb = idx - y * dn;
+            const int px = xb / cn;
+            int dx = 0, dy = 0;
+            if (ipx + px >= 0 && ipx + px < I.w && ipy + y >= 0 && ipy + y < I.h) {
+                const uint8_t* p = sc.ipatch + y * SVO_LK_CN_IP + xb;
+                const int a00 = p[0], a01 = p[cn], a02 = p[2 * cn];
+                const int a10 = p[SVO_LK_CN_IP], a12 = p[SVO_LK_CN_IP + 2 * cn];
+                const int a20 = p[2 * SVO_LK_CN_IP], a21 = p[2 * SVO_LK_CN_IP + cn], a22 = p[2 * SVO_LK_CN_IP + 2 * cn];
+                dx = 3 * (a02 + a22 - a00 - a20) + 10 * (a12 - a10);
+                dy = 3 * (a20 + a22 - a00 - a02) + 10 * (a21 - a01);
+            }
+            sc.dxp[y * SVO_LK_CN_DP + xb] = (short)dx;
+            sc.dyp[y * SVO_LK_CN_DP + xb] = (short)dy;
+        }
+        Red::sync();
+        long long sA11 = 0, sA12 = 0, sA22 = 0;
+        for (int e = lane; e < nsamp; e += LANES) {
+            const int wy = e / wn, xb = e - wy * wn;
+            const uint8_t* p = sc.ipatch + (wy + 1) * SVO_LK_CN_IP + xb + cn;
+            const int iv = (p[0] * iw00 + p[cn] * iw01 + p[SVO_LK_CN_IP] * iw10 + p[SVO_LK_CN_IP + cn] * iw11 + (1 << 8)) >> 9;
+            const short* qx = sc.dxp + wy * SVO_LK_CN_DP + xb;
+            const short* qy = sc.dyp + wy * SVO_LK_CN_DP + xb;
+            const int ix = ((int)qx[0] * iw00 + (int)qx[cn] * iw01 + (int)qx[SVO_LK_CN_DP] * iw10 + (int)qx[SVO_LK_CN_DP + cn] * iw11 + (1 << 13)) >> 14;
+            const int iy = ((int)qy[0] * iw00 + (int)qy[cn] * iw01 + (int)qy[SVO_LK_CN_DP] * iw10 + (int)qy[SVO_LK_CN_DP + cn] * iw11 + (1 << 13)) >> 14;
+            sc.iv[e] = (short)iv;
+            sc.ixv[e] = (short)ix;
+            sc.iyv[e] = (short)iy;
+            const int sx = (short)ix, sy = (short)iy;
+            sA11 += sx * sx; sA12 += sx * sy; sA22 += sy * sy;
+        }
+        sA11 = Red::sum64g(sA11); sA12 = Red::sum64g(sA12); sA22 = Red::sum64g(sA22);
+        Red::sync();
+        const float A11 = fmul((float)sA11, FLT_SCALE);
+        const float A12 = fmul((float)sA12, FLT_SCALE);
+        const float A22 = fmul((float)sA22, FLT_SCALE);
+        float D = fsub(fmul(A11, A22), fmul(A12, A12));
+        const float dA = fsub(A11, A22);
+        const float disc = fadd(fmul(dA, dA), fmul(fmul(4.f, A12), A12));
+        const float min_eig = fsub(fadd(A22, A11), sqrtf(disc)) / (float)(2 * SVO_LK_NPIX);
+        if (min_eig < cfg.min_eig || D < FLT_EPSILON) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        D = 1.f / D;
+        float cx = fsub(nx, half_win), cy = fsub(ny, half_win);
+        float pdx = 0.f, pdy = 0.f;
+        for (int j = 0; j < cfg.max_iters; ++j) {
+            const int inx = floor_int(cx), iny = floor_int(cy);
+            if (inx < -SVO_LK_WIN || inx >= J.w || iny < -SVO_LK_WIN || iny >= J.h) {
+                if (level == 0) status = 0;
+                break;
+            }
+            ++iters;
+            lk_weights(fsub(cx, (float)inx), fsub(cy, (float)iny), iw00, iw01, iw10, iw11);
+            const bool interior = inx >= 0 && iny >= 0 && inx + SVO_LK_WIN <= J.w - 1 && iny + SVO_LK_WIN <= J.h - 1;
+            long long sb1 = 0, sb2 = 0;
+            for (int e = lane; e < nsamp; e += LANES) {
+                const int wy = e / wn, xb = e - wy * wn;
+                int j00, j01, j10, j11;
+                if (interior) {
+                    const uint8_t* q = J.img + (size_t)(iny + wy) * J.pitch + inx * cn + xb;
+                    j00 = q[0]; j01 = q[cn]; j10 = q[J.pitch]; j11 = q[J.pitch + cn];
+                } else {
+                    const int px = xb / cn, ch = xb - px * cn;
+                    const uint8_t* r0 = J.img + (size_t)reflect101(iny + wy, J.h) * J.pitch + ch;
+                    const uint8_t* r1 = J.img + (size_t)reflect101(iny + wy + 1, J.h) * J.pitch + ch;
+                    const int x0 = reflect101(inx + px, J.w) * cn, x1 = reflect101(inx + px + 1, J.w) * cn;
+                    j00 = r0[x0]; j01 = r0[x1]; j10 = r1[x0]; j11 = r1[x1];
+                }
+                const int v = (j00 * iw00 + j01 * iw01 + j10 * iw10 + j11 * iw11 + (1 << 8)) >> 9;
+                const int diff = v - (int)sc.iv[e];
+                sb1 += diff * (int)sc.ixv[e];
+                sb2 += diff * (int)sc.iyv[e];
+            }
+            const float b1 = fmul((float)Red::sum64g(sb1), FLT_SCALE);
+            const float b2 = fmul((float)Red::sum64g(sb2), FLT_SCALE);
+            const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);
+            const float ddy = fmul(fsub(fmul(A12, b1), fmul(A11, b2)), D);
+            cx = fadd(cx, ddx);
+            cy = fadd(cy, ddy);
+            nx = fadd(cx, half_win);
+            ny = fadd(cy, half_win);
+            if ((double)ddx * (double)ddx + (double)ddy * (double)ddy <= cfg.eps_sq) break;
+            if (j > 0 && fabsf(fadd(ddx, pdx)) <= 0.01f && fabsf(fadd(ddy, pdy)) <= 0.01f) {
+                nx = fsub(nx, fmul(ddx, 0.5f));
+                ny = fsub(ny, fmul(ddy, 0.5f));
+                break;
+            }
+            pdx = ddx;
+            pdy = ddy;
+        }
+    }
     if (status) {
         const int fx = floor_int(fsub(nx, half_win)), fy = floor_int(fsub(ny, half_win));
         const LkLevel J0 = Jpyr.lv[0];

@@ -22,6 +22,7 @@ namespace svo {
 
 struct PyrGeom {
     int nlevels;
+    int cn;                          // interleaved channels per pixel (1; 3 = CLI-faithful 8UC3 mode): w in pixels, pitch in bytes
     int w[SVO_MAX_LEVELS], h[SVO_MAX_LEVELS], pitch[SVO_MAX_LEVELS];
     long long off[SVO_MAX_LEVELS];   // byte offset of each level inside one image pyramid
     long long image_bytes;           // bytes of one image pyramid (all levels)

@@ -42,6 +42,12 @@ struct WarpRed {
             fb = (float)__reduce_add_sync(0xffffffffu, b);
         }
     }
+    // any 64-bit per-lane value (multi-channel windows)
+    static __device__ __forceinline__ long long sum64g(long long v) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    }
     static __device__ __forceinline__ void sync() { __syncwarp(); }
 };
 
@@ -440,13 +446,80 @@ void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, in
     launch_pyrdown_job(j, n_img, st);
 }
 
+// ---- interleaved multi-channel images (CLI-faithful 8UC3 mode): pyrDown per channel, one thread per
+// output sample.  Small images, off the benchmarked path: written for clarity.
+struct ImgCn {
+    const uint8_t* p;
+    int pitch, cn, ch;
+    __device__ int operator()(int x, int y) const { return __ldg(p + (long long)y * pitch + x * cn + ch); }
+};
+__global__ void __launch_bounds__(256) pyrdown_cn_kernel(PyrDownJob j, int cn) {
+    const int cam = blockIdx.z & 1, seq = blockIdx.z >> 1;
+    const int xb = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
+    if (xb >= j.dw * cn) return;
+    const int x = xb / cn, ch = xb - x * cn;
+    ImgCn g{j.src[cam] + (long long)seq * j.src_seq_stride, j.spitch, cn, ch};
+    uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
+    dst[(long long)y * j.dpitch + xb] = (uint8_t)pyrdown_pixel(g, j.sw, j.sh, x, y);
+}
+__global__ void __launch_bounds__(256) copy_rows_kernel(PyrDownJob j, int row_bytes) {
+    const int cam = blockIdx.z & 1, seq = blockIdx.z >> 1;
+    const int xb = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
+    if (xb >= row_bytes) return;
+    j.copy[cam][(long long)seq * j.copy_seq_stride + (long long)y * j.cpitch + xb] =
+        __ldg(j.src[cam] + (long long)seq * j.src_seq_stride + (long long)y * j.spitch + xb);
+}
+static int launch_ingest_cn(const DevArrays& d, const PyrGeom& pg, const uint8_t* left, const uint8_t* right,
+                            int stride, long long seq_stride, int slot, cudaStream_t st) {
+    int launches = 0;
+    const long long ctx_seq_stride = pg.base(1, 0, 0) - pg.base(0, 0, 0);
+    PyrDownJob j;
+    memset(&j, 0, sizeof(j));
+    if (left) {
+        for (int cam = 0; cam < 2; ++cam) {
+            j.src[cam] = cam ? right : left;
+            j.copy[cam] = d.pyr + pg.base(0, slot, cam) + pg.off[0];
+        }
+        j.src_seq_stride = seq_stride;
+        j.spitch = stride;
+        j.copy_seq_stride = ctx_seq_stride;
+        j.cpitch = pg.pitch[0];
+        const int rb = pg.w[0] * pg.cn;
+        copy_rows_kernel<<<dim3((rb + 255) / 256, pg.h[0], d.n_seq * 2), 256, 0, st>>>(j, rb);
+        ++launches;
+    }
+    for (int l = 1; l < pg.nlevels; ++l) {
+        memset(&j, 0, sizeof(j));
+        for (int cam = 0; cam < 2; ++cam) {
+            uint8_t* img = d.pyr + pg.base(0, slot, cam);
+            j.src[cam] = img + pg.off[l - 1];
+            j.dst[cam] = img + pg.off[l];
+        }
+        j.src_seq_stride = j.dst_seq_stride = ctx_seq_stride;
+        j.sw = pg.w[l - 1]; j.sh = pg.h[l - 1]; j.spitch = pg.pitch[l - 1];
+        j.dw = pg.w[l]; j.dh = pg.h[l]; j.dpitch = pg.pitch[l];
+        pyrdown_cn_kernel<<<dim3((j.dw * pg.cn + 255) / 256, j.dh, d.n_seq * 2), 256, 0, st>>>(j, pg.cn);
+        ++launches;
+    }
+    return launches;
+}
+void launch_pyrdown_cn(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh, int dpitch, int cn,
+                       cudaStream_t st) {
+    PyrDownJob j;
+    memset(&j, 0, sizeof(j));
+    j.src[0] = src; j.sw = sw; j.sh = sh; j.spitch = spitch;
+    j.dst[0] = dst; j.dw = dw; j.dh = dh; j.dpitch = dpitch;
+    pyrdown_cn_kernel<<<dim3((dw * cn + 255) / 256, dh, 1), 256, 0, st>>>(j, cn);
+}
+
 // ---- context ingest into pyramid slot `slot` (host-known ring, frame f -> f % 3)
 int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
                   cudaStream_t st) {
     int launches = 0;
     const long long ctx_seq_stride = pg.base(1, 0, 0) - pg.base(0, 0, 0);
-    for (int l = 1; l < pg.nlevels; ++l) {
+    if (pg.cn != 1) launches = launch_ingest_cn(d, pg, left, right, stride, seq_stride, slot, st);
+    for (int l = 1; l < pg.nlevels && pg.cn == 1; ++l) {
         PyrDownJob j;
         memset(&j, 0, sizeof(j));
         for (int cam = 0; cam < 2; ++cam) {
@@ -470,7 +543,7 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
         launch_pyrdown_job(j, d.n_seq * 2, st);
         ++launches;
     }
-    if (pg.nlevels == 1 && left) {   // no pyramid level to fuse the copy with
+    if (pg.nlevels == 1 && left && pg.cn == 1) {   // no pyramid level to fuse the copy with
         cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 0) + pg.off[0], pg.pitch[0], left, stride, pg.w[0], pg.h[0],
                           cudaMemcpyDeviceToDevice, st);
         cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 1) + pg.off[0], pg.pitch[0], right, stride, pg.w[0], pg.h[0],
@@ -764,10 +837,64 @@ int klt_resident_blocks_per_sm() {
     return nb;
 }
 int klt_spec_resident_blocks_per_sm();
+// interleaved multi-channel pyramids (CLI-faithful 8UC3 mode): same work distribution, generic LK core
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+klt_cn_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
+    __shared__ LkScratchCn patch[KLT_WARPS];
+    const int seq = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    SeqState* s = d.state + seq;
+    const int n = d.n_todo[seq];
+    if (n <= 0) return;
+    long long base[4];
+    circ_bases(pg, seq, slot_prev, slot_cur, base);
+    int* counter = d.klt_next + seq;
+    const int* todo = d.todo + (long long)seq * d.cap;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(counter, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n) break;
+        const int f = todo[t];
+        const long long o = (long long)seq * d.cap + f;
+        const float2 p0 = d.bk_xy[o];
+        float2 pts[5];
+        pts[0] = p0;
+        int iters = 0;
+        unsigned st = 0;
+#pragma unroll 1
+        for (int leg = 0; leg < 4; ++leg) {
+            const LkPyramid I = make_pyr(d.pyr + base[leg], pg);
+            const LkPyramid J = make_pyr(d.pyr + base[(leg + 1) & 3], pg);
+            int it;
+            float ox, oy;
+            const int ok = lk_track_feature_cn<32, WarpRed>(I, J, pc.lk, pg.cn, pts[leg].x, pts[leg].y, lane,
+                                                            patch[wid], ox, oy, it);
+            st |= ok ? (1u << leg) : 0u;
+            iters += it;
+            pts[leg + 1] = make_float2(ox, oy);
+        }
+        bool ok = st == 15u && close_points(p0.x, p0.y, pts[4].x, pts[4].y, pc.circular_threshold);
+        if (pc.check_bounds) {
+            const int W = pc.width, H = pc.height;
+            ok = ok && in_bounds(p0.x, p0.y, W, H) && in_bounds(pts[1].x, pts[1].y, W, H) &&
+                 in_bounds(pts[3].x, pts[3].y, W, H) && in_bounds(pts[2].x, pts[2].y, W, H);
+        }
+        if (lane == 0) {
+            d.lk_L1[o] = pts[1];
+            d.lk_R1[o] = pts[2];
+            d.lk_R0[o] = pts[3];
+            d.lk_C[o] = pts[4];
+            d.lk_status[o] = (uint8_t)(st | (ok ? 16u : 0u));
+            atomicAdd(&s->lk_iters, iters);
+        }
+    }
+}
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,
                 int slot_cur, cudaStream_t st) {
     dim3 grid(blocks_per_seq, d.n_seq);
-    klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
+    if (pg.cn != 1) klt_cn_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
+    else klt_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, slot_prev, slot_cur);
 }
 
 // ---- speculative tracking -------------------------------------------------------------------------------------
@@ -899,6 +1026,27 @@ lk_single_kernel(LkPyramid I, LkPyramid J, LkConfig cfg, const float2* __restric
         out[f] = q;
         status[f] = (uint8_t)ok;
     }
+}
+__global__ void __launch_bounds__(KLT_WARPS * 32)
+lk_single_cn_kernel(LkPyramid I, LkPyramid J, LkConfig cfg, int cn, const float2* __restrict__ pts, int n,
+                    float2* __restrict__ out, uint8_t* __restrict__ status) {
+    __shared__ LkScratchCn patch[KLT_WARPS];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f = blockIdx.x * KLT_WARPS + wid;
+    if (f >= n) return;
+    const float2 p = pts[f];
+    float2 q;
+    int it;
+    const int ok = lk_track_feature_cn<32, WarpRed>(I, J, cfg, cn, p.x, p.y, lane, patch[wid], q.x, q.y, it);
+    if (lane == 0) {
+        out[f] = q;
+        status[f] = (uint8_t)ok;
+    }
+}
+void launch_lk_single_cn(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, int cn, const float2* pts, int n,
+                         float2* out, uint8_t* status, cudaStream_t st) {
+    if (n <= 0) return;
+    lk_single_cn_kernel<<<(n + KLT_WARPS - 1) / KLT_WARPS, KLT_WARPS * 32, 0, st>>>(I, J, cfg, cn, pts, n, out, status);
 }
 void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, const float2* pts, int n, float2* out,
                       uint8_t* status, cudaStream_t st) {

@@ -59,6 +59,11 @@ void launch_pnp_samples(const DevArrays& d, cudaStream_t st);   // standalone (s
 // ---- stage-level helpers used by the stateless API ----
 void launch_lk_single(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, const float2* pts, int n,
                       float2* out, uint8_t* status, cudaStream_t st);
+// interleaved multi-channel variants (CLI-faithful 8UC3 mode)
+void launch_lk_single_cn(const LkPyramid& I, const LkPyramid& J, LkConfig cfg, int cn, const float2* pts, int n,
+                         float2* out, uint8_t* status, cudaStream_t st);
+void launch_pyrdown_cn(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh, int dpitch,
+                       int cn, cudaStream_t st);
 void launch_bucket_generic(float2* xy, int* ages, int* strengths, int n, BucketGeom bg,
                            int per_bucket, int* scratch /* see svo_capi.cu */, float2* xy_out,
                            int* age_out, int* str_out, int* n_out, cudaStream_t st);

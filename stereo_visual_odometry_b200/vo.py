@@ -32,8 +32,12 @@ MAX_ROTATION_NORM = 0.5
 
 def _img(a) -> np.ndarray:
     a = np.asarray(a)
+    if a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 3:   # CV_8UC3 as the reference CLI feeds it (F4)
+        if a.strides[2] != 1 or a.strides[1] != 3:
+            a = np.ascontiguousarray(a)
+        return a
     if a.dtype != np.uint8 or a.ndim != 2:
-        raise SvoError("images must be 2-D uint8 (CV_8UC1)")
+        raise SvoError("images must be 2-D uint8 (CV_8UC1) or HxWx3 uint8 (CV_8UC3, CLI-faithful mode)")
     if a.strides[1] != 1:
         a = np.ascontiguousarray(a)
     return a
@@ -131,8 +135,8 @@ def calcOpticalFlowPyrLK(prev_img, next_img, prev_pts, params: Params | None = N
     a, b = _img(prev_img), _img(next_img)
     if a.shape != b.shape or a.strides[0] != b.strides[0]:
         a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
-    h, w = a.shape
-    p = params or default_params(w, h)
+    h, w = a.shape[:2]
+    p = params or default_params(w, h, channels=3 if a.ndim == 3 else 1)
     pts = _pts(prev_pts)
     out = np.zeros_like(pts)
     st = np.zeros((len(pts),), np.uint8)
@@ -206,8 +210,10 @@ class VisualOdometry:
         if width is not None and height is not None:
             self._create(width, height)
 
-    def _create(self, width, height):
-        self.params = default_params(width, height, n_seq=self._n_seq, **self._overrides)
+    def _create(self, width, height, channels=1):
+        kw = dict(self._overrides)
+        kw.setdefault("channels", channels)
+        self.params = default_params(width, height, n_seq=self._n_seq, **kw)
         ctx = lib().svo_create(C.byref(self.params))
         if not ctx:
             raise SvoError("svo_create failed: " + lib().svo_last_error().decode())
@@ -244,8 +250,8 @@ class VisualOdometry:
         if L.strides[0] != R.strides[0]:
             L, R = np.ascontiguousarray(L), np.ascontiguousarray(R)
         if self._ctx is None:
-            self._create(L.shape[1], L.shape[0])
-        if (L.shape[1], L.shape[0]) != self._size:
+            self._create(L.shape[1], L.shape[0], 3 if L.ndim == 3 else 1)
+        if (L.shape[1], L.shape[0]) != self._size or (3 if L.ndim == 3 else 1) != self.params.channels:
             raise SvoError("image size changed")
         T = np.zeros((4, 4), np.float64)
         ok = check(lib().svo_process_frame(self._ctx, ptr(L), ptr(R), L.strides[0], ptr(T, C.c_double)))
@@ -259,7 +265,7 @@ class VisualOdometry:
         if L.shape != R.shape or L.strides[0] != R.strides[0]:
             raise SvoError("left / right image layouts differ")
         if self._ctx is None:
-            self._create(L.shape[1], L.shape[0])
+            self._create(L.shape[1], L.shape[0], 3 if L.ndim == 3 else 1)
         check(lib().svo_submit_frame(self._ctx, ptr(L), ptr(R), L.strides[0]))
         self._inflight = getattr(self, "_inflight", [])
         self._inflight.append((L, R))

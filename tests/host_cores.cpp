@@ -117,6 +117,67 @@ int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, in
     return total_iters;
 }
 
+// ---- interleaved multi-channel images (the CLI-faithful 8UC3 mode)
+struct HostImgCn {
+    const uint8_t* p;
+    int pitch, cn, ch;
+    int operator()(int x, int y) const { return p[(size_t)y * pitch + x * cn + ch]; }
+};
+void hc_pyrdown_cn(const uint8_t* src, int sw, int sh, int spitch, int cn, uint8_t* dst, int dpitch) {
+    const int dw = (sw + 1) / 2, dh = (sh + 1) / 2;
+    for (int ch = 0; ch < cn; ++ch) {
+        HostImgCn g{src, spitch, cn, ch};
+        for (int y = 0; y < dh; ++y)
+            for (int x = 0; x < dw; ++x) dst[(size_t)y * dpitch + x * cn + ch] = (uint8_t)pyrdown_pixel(g, sw, sh, x, y);
+    }
+}
+static void build_pyr_cn(HostPyr& hp, const uint8_t* img, int w, int h, int stride, int cn, int max_level, int win) {
+    hp.lv.clear();
+    hp.lv.emplace_back((size_t)w * cn * h);
+    for (int y = 0; y < h; ++y) memcpy(&hp.lv[0][(size_t)y * w * cn], img + (size_t)y * stride, (size_t)w * cn);
+    int lw = w, lh = h, l = 1;
+    std::vector<int> ws{w}, hs{h};
+    for (; l <= max_level && l < SVO_MAX_LEVELS; ++l) {
+        const int nw = (lw + 1) / 2, nh = (lh + 1) / 2;
+        if (nw <= win || nh <= win) break;
+        hp.lv.emplace_back((size_t)nw * cn * nh);
+        hc_pyrdown_cn(hp.lv[l - 1].data(), lw, lh, lw * cn, cn, hp.lv[l].data(), nw * cn);
+        lw = nw;
+        lh = nh;
+        ws.push_back(nw);
+        hs.push_back(nh);
+    }
+    hp.nlevels = l;
+    for (int k = 0; k < SVO_MAX_LEVELS; ++k) {
+        const int q = k < l ? k : l - 1;
+        hp.p.lv[k] = LkLevel{hp.lv[q].data(), ws[q], hs[q], ws[q] * cn};
+    }
+}
+int hc_lk_cn(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, int cn, int max_level, int max_iters,
+             double eps, float min_eig, const float* pts, int n, float* out, uint8_t* status) {
+    HostPyr I, J;
+    build_pyr_cn(I, prev, w, h, stride, cn, max_level, SVO_LK_WIN);
+    build_pyr_cn(J, next, w, h, stride, cn, max_level, SVO_LK_WIN);
+    LkConfig cfg;
+    cfg.nlevels = I.nlevels;
+    cfg.max_iters = max_iters;
+    cfg.eps_sq = eps * eps;
+    cfg.min_eig = min_eig;
+    lk_config_finish(cfg);
+    static LkScratchCn patch;
+    int total_iters = 0;
+    for (int i = 0; i < n; ++i) {
+        float ox, oy;
+        int it;
+        status[i] = (uint8_t)lk_track_feature_cn<1, SerialRed>(I.p, J.p, cfg, cn, pts[2 * i], pts[2 * i + 1], 0, patch,
+                                                               ox, oy, it);
+        out[2 * i] = ox;
+        out[2 * i + 1] = oy;
+        total_iters += it;
+    }
+    return total_iters;
+}
+
 void hc_triangulate(const float* Pl, const float* Pr, const float* pL, const float* pR, int n, float* X3) {
     for (int i = 0; i < n; ++i)
         triangulate_dlt(Pl, Pr, pL[2 * i], pL[2 * i + 1], pR[2 * i], pR[2 * i + 1], X3 + 3 * i);

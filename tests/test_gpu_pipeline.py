@@ -14,10 +14,10 @@ def rot_angle(R):
     return float(np.arccos(np.clip((np.trace(R) - 1) / 2, -1, 1)))
 
 
-def run_both(frames, Pl, Pr, width, height, check_stages=True):
-    vo = V.VisualOdometry(width, height)
+def run_both(frames, Pl, Pr, width, height, check_stages=True, mode="gray"):
+    vo = V.VisualOdometry(width, height, channels=3 if mode == "cli_bgr" else 1)
     vo.initalize_projection_matricies(Pl, Pr)
-    ref = O.RefVO(Pl, Pr)
+    ref = O.RefVO(Pl, Pr, mode=mode)
     stats = dict(frames=0, lk_close=[], status_eq=[], pose_ok=0, pose_n=0, flags_eq=0, inl_symdiff=[])
     pose_g, pose_r = np.eye(4), np.eye(4)
     for i, (L, R) in enumerate(frames):
@@ -52,6 +52,7 @@ def run_both(frames, Pl, Pr, width, height, check_stages=True):
             stats["status_eq"].append((st == rst).all(1).mean())
             d = np.max([np.abs(lk[k][g] - tp.lk[k][r]).max(1) for k in ("pL1", "pR1", "pR0", "pC")], 0)
             stats["lk_close"].append((d <= 0.05).mean())
+            stats.setdefault("lk_n", []).append(len(d))
             keep = ((lk["status"] & 16) != 0)
             stats.setdefault("keep_eq", []).append((keep[g] == tp.keep[r]).mean())
         if ok and rok:
@@ -68,11 +69,12 @@ def run_both(frames, Pl, Pr, width, height, check_stages=True):
     return stats
 
 
-def check(stats, pose_frac=0.9):
+def check(stats, pose_frac=0.9, lk_min=0.98):
     assert stats["flags_eq"] == stats["frames"], "success flags differ from the oracle"
     assert np.mean(stats["bucket_match"]) >= 0.99 and np.min(stats["bucket_match"]) >= 0.98
     assert np.mean(stats["status_eq"]) >= 0.99 and np.min(stats["status_eq"]) >= 0.98
-    assert np.mean(stats["lk_close"]) >= 0.99 and np.min(stats["lk_close"]) >= 0.98
+    # north_star: <= 0.05 px on >= 99 % of the features (all four legs of the chain); per frame lk_min
+    assert np.mean(stats["lk_close"]) >= 0.99 and np.min(stats["lk_close"]) >= lk_min, stats["lk_close"]
     assert np.mean(stats["keep_eq"]) >= 0.99
     # pose: north_star tolerance (1e-3 rad, 1e-3 relative translation) whenever the RANSAC inlier set equals the
     # oracle's; OpenCV's own EPnP hypotheses depend on the LAPACK null-space basis of a rank-deficient 12x12 system,
@@ -89,6 +91,30 @@ def test_run1_gray(run1):
     Pl, Pr = O.CLI_P_LEFT, O.CLI_P_RIGHT
     s = run_both(iter(run1["gray"]), Pl, Pr, 512, 288)
     check(s)
+
+
+def test_run1_cli_bgr_reproduces_the_reference_result_csv(run1):
+    """CLI-faithful 8UC3 mode on the GPU (SURVEY F4 / 8f-2): the BGR images cv::imread returns go through
+    unchanged -- FAST on the first W bytes of each row, pyramids and LK on three channels -- and the trajectory
+    is the reference's own committed output, run1/result.csv (rows 0..7, identity initial pose)."""
+    Pl, Pr = O.CLI_P_LEFT, O.CLI_P_RIGHT
+    s = run_both(iter(run1["bgr"]), Pl, Pr, 512, 288, mode="cli_bgr")
+    # FAST on the byte view puts "corners" at pixel x = byte index, i.e. mostly on untextured windows: the chain of
+    # four LK legs is ill-conditioned there and amplifies the 1e-4 px float noise of the tracked positions, so a
+    # single frame may have up to 3 % of its chains further than 0.05 px from the oracle's (mean stays >= 99 %)
+    check(s, lk_min=0.97)
+    vo = V.VisualOdometry()
+    vo.initalize_projection_matricies(Pl, Pr)
+    pose, xyz = np.eye(4), []
+    for L, R in run1["bgr"]:
+        ok, T = vo.stereo_callback(L, R)
+        pose = pose @ T
+        xyz.append(pose[:3, 3].copy())
+    xyz = np.array(xyz)
+    gold = run1["xyz"]
+    # north_star: per-frame pose within 1e-3 relative; the CSV holds 6 significant digits
+    step = np.linalg.norm(np.diff(gold, axis=0), axis=1).max()
+    assert np.abs(xyz - gold).max() <= 1e-3 * max(step, 1e-3) * len(gold) + 2e-5, np.abs(xyz - gold).max()
 
 
 def test_synthetic_kitti():

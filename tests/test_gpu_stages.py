@@ -145,6 +145,22 @@ def test_lk_leg_matches_opencv(run1):
         assert (np.abs(o - ro).max(1) <= 0.05).mean() >= 0.99
 
 
+def test_lk_leg_three_channel_matches_opencv(run1):
+    """calcOpticalFlowPyrLK on interleaved 8UC3 images (what the reference CLI passes)."""
+    import cv2
+    b = run1["bgr"]
+    rng = np.random.default_rng(3)
+    border = np.array([[1.2, 1.7], [510.5, 286.9], [0, 0], [511, 287], [3.3, 150.2], [508.8, 10.1], [-3, 5], [600, 100]],
+                      np.float32)
+    for (I, J) in [(b[0][0], b[1][0]), (b[3][0], b[3][1]), (b[5][1], b[4][1])]:
+        pts, _ = O.fast_detect(cv2.cvtColor(I, cv2.COLOR_BGR2GRAY), 5)
+        pts = np.concatenate([pts + rng.uniform(-0.5, 0.5, pts.shape).astype(np.float32), border])
+        o, s = V.calcOpticalFlowPyrLK(I, J, pts)
+        ro, rs = O.lk_leg(I, J, pts)
+        assert (s == rs).mean() >= 0.99
+        assert (np.abs(o - ro).max(1) <= 0.05).mean() >= 0.99
+
+
 def test_lk_kitti_shape():
     seq = synth.make_sequence(n_frames=2, seed=2)
     (L0, R0), (L1, R1) = seq.render(0), seq.render(1)

@@ -75,6 +75,40 @@ def test_lk_matches_opencv(hostcores, run1):
         assert (d <= 0.05).mean() >= 0.99
 
 
+def host_lk_cn(hc, I, J, pts):
+    hc.hc_lk_cn.argtypes = [u8p, u8p] + [C.c_int] * 6 + [C.c_double, C.c_float, fp, C.c_int, fp, u8p]
+    pts = np.ascontiguousarray(pts, np.float32)
+    n = len(pts)
+    out = np.zeros((n, 2), np.float32)
+    st = np.zeros(n, np.uint8)
+    h, w, cn = I.shape
+    hc.hc_lk_cn(P(I, u8p), P(J, u8p), w, h, w * cn, cn, 3, 30, 1e-4, 1e-3, P(pts, fp), n, P(out, fp), P(st, u8p))
+    return out, st
+
+
+def test_lk_three_channel_matches_opencv(hostcores, run1):
+    """The CLI-faithful mode (SURVEY F4): calcOpticalFlowPyrLK on the BGR images cv::imread returns."""
+    import cv2
+    b = run1["bgr"]
+    rng = np.random.default_rng(3)
+    border = np.array([[1.2, 1.7], [510.5, 286.9], [0, 0], [511, 287], [3.3, 150.2], [508.8, 10.1], [-3, 5], [600, 100]],
+                      np.float32)
+    for (I, J) in [(b[0][0], b[1][0]), (b[3][0], b[3][1]), (b[5][1], b[4][1])]:
+        I, J = np.ascontiguousarray(I), np.ascontiguousarray(J)
+        pts, _ = O.fast_detect(cv2.cvtColor(I, cv2.COLOR_BGR2GRAY), 5)
+        pts = np.concatenate([pts + rng.uniform(-0.5, 0.5, pts.shape).astype(np.float32), border])
+        o, s = host_lk_cn(hostcores, I, J, pts)
+        ro, rs = O.lk_leg(I, J, pts)
+        assert (s == rs).mean() >= 0.99
+        d = np.abs(o - ro).max(1)
+        assert (d <= 0.05).mean() >= 0.99
+        # three-channel pyrDown is per channel
+    d = np.zeros((144, 256, 3), np.uint8)
+    I = np.ascontiguousarray(b[2][0])
+    hostcores.hc_pyrdown_cn(P(I, u8p), 512, 288, 512 * 3, 3, P(d, u8p), 256 * 3)
+    assert np.array_equal(d, cv2.pyrDown(I))
+
+
 def test_triangulate_matches_opencv(hostcores):
     rng = np.random.default_rng(3)
     Pl, Pr = synth.projection_matrices("kitti00")
