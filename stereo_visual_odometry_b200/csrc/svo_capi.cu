@@ -99,6 +99,8 @@ struct svo_ctx {
     cudaEvent_t ev_spf[4] = {nullptr, nullptr, nullptr, nullptr};   // FAST-winner candidates of frame f tracked
     cudaEvent_t ev_bm[4] = {nullptr, nullptr, nullptr, nullptr};    // bucket merge of frame f done (predictions for f + 1)
     cudaStream_t stream_fb = nullptr;   // pose refit + result
+    cudaStream_t stream_h2d = nullptr;  // host frames -> staging ring (copy engine only)
+    cudaEvent_t ev_h2d[4] = {nullptr, nullptr, nullptr, nullptr};   // staging copy of frame f complete
     cudaStream_t stream_full = nullptr; // whole-GPU stream for serial frames (== stream when there are no partitions)
     int klt_blocks_full = 0;            // persistent KLT blocks per sequence on the whole GPU
     void* green[3] = {nullptr, nullptr, nullptr};   // CUgreenCtx of the chain / ingest / KLT partitions
@@ -340,6 +342,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     }
     for (int i = 0; i < 4; ++i) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_trk[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_spf[i], cudaEventDisableTiming));
@@ -347,6 +350,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaEventCreateWithFlags(&c->ev_fa[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_fb[i], cudaEventDisableTiming));
     }
+    CU(cudaStreamCreateWithFlags(&c->stream_h2d, cudaStreamNonBlocking));
     for (int i = 0; i < SVO_RESULT_RING; ++i) {
         c->ev_done[i] = nullptr;
         CU(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
@@ -410,7 +414,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.cntF, S));
     CU(dev_alloc(c, &d.cntT, S));
     CU(dev_alloc(c, &d.listF, S * c->bg.nb));
-    CU(dev_alloc(c, &d.nF, S));
+    CU(dev_alloc(c, &d.nF, 2 * S));
     CU(dev_alloc(c, &d.predT, (size_t)2 * S * c->bg.nb));
     CU(dev_alloc(c, &d.todo, C));
     CU(dev_alloc(c, &d.n_todo, S));
@@ -424,8 +428,9 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaMemcpyAsync(d.rng_raw, raw.data(), sizeof(unsigned) * SVO_RNG_TABLE, cudaMemcpyHostToDevice, c->stream));
         CU(cudaStreamSynchronize(c->stream));
     }
-    CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S, false));
-    CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S, false));
+    // staging ring for host frames: slot f % 3 (the copy of frame f + 1 runs while frame f is being ingested)
+    CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S * SVO_PYR_SLOTS, false));
+    CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S * SVO_PYR_SLOTS, false));
     CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S * SVO_RESULT_RING));
     // initial state: rotation = I, translation = 0, last_transform = I (vo.h:262-264)
     std::vector<SeqState> init(S);
@@ -488,12 +493,13 @@ static void trace_dump(svo_ctx* c);
 extern "C" void svo_destroy(svo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->p.device);
-    for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb})
+    for (cudaStream_t st : {c->stream_h2d, c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb})
         if (st) cudaStreamSynchronize(st);
     trace_dump(c);
     for (void* q : c->allocs) cudaFree(q);
     for (int i = 0; i < 4; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
+        if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
         if (c->ev_trk[i]) cudaEventDestroy(c->ev_trk[i]);
         if (c->ev_spf[i]) cudaEventDestroy(c->ev_spf[i]);
@@ -505,7 +511,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
         cudaStreamSynchronize(c->stream_full);
         cudaStreamDestroy(c->stream_full);
     }
-    for (cudaStream_t st : {c->stream_k, c->stream_k2, c->stream_fb})
+    for (cudaStream_t st : {c->stream_k, c->stream_k2, c->stream_fb, c->stream_h2d})
         if (st) cudaStreamDestroy(st);
     for (int i = 0; i < SVO_RESULT_RING; ++i)
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
@@ -781,31 +787,29 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
         return fail(SVO_ERR_STATE, "result ring full: call svo_collect before submitting more frames");
     CU(cudaSetDevice(c->p.device));
     const bool in_flight = c->tracked > c->collected;   // streaming caller: an earlier frame is still uncollected
-    int rc = wait_ring(c, in_flight);
-    if (rc != SVO_OK) return rc;
+    const long long f = c->frames;
     const int S = c->d.n_seq, W = c->p.width * c->pg.cn /* row bytes */, H = c->p.height, P0 = c->pg.pitch[0];
     const long long plane = (long long)P0 * H;
-    cudaStream_t sI = ingest_stream(c, in_flight);
-    if (S == 1) {
-        // straight into level 0 of the frame's pyramid slot: no staging copy
-        const int cur = (int)(c->frames % SVO_PYR_SLOTS);
-        uint8_t* l0 = c->d.pyr + c->pg.base(0, cur, 0) + c->pg.off[0];
-        uint8_t* r0 = c->d.pyr + c->pg.base(0, cur, 1) + c->pg.off[0];
-        CU(cudaMemcpy2DAsync(l0, P0, left, stride, W, H, cudaMemcpyHostToDevice, sI));
-        CU(cudaMemcpy2DAsync(r0, P0, right, stride, W, H, cudaMemcpyHostToDevice, sI));
-        return enqueue_frame(c, nullptr, nullptr, P0, plane, nullptr, true, in_flight);
-    }
-    // the staging planes are read by the ingest of the previous frame: same stream, so ordered
-    if (seq_stride == (long long)stride * H) {
-        CU(cudaMemcpy2DAsync(c->stage_L, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sI));
-        CU(cudaMemcpy2DAsync(c->stage_R, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sI));
+    // host -> staging slot f % 3 on the copy stream: waits only for the ingest of frame f - 3 (the slot's last
+    // reader), so the copy of the next frame runs ahead of everything the GPU is still doing for this one
+    uint8_t* sl = c->stage_L + (f % SVO_PYR_SLOTS) * plane * S;
+    uint8_t* sr = c->stage_R + (f % SVO_PYR_SLOTS) * plane * S;
+    cudaStream_t sH = c->stream_h2d;
+    if (f >= SVO_PYR_SLOTS) CU(cudaStreamWaitEvent(sH, c->ev_in[(f - SVO_PYR_SLOTS) & 3], 0));
+    if (S == 1 || seq_stride == (long long)stride * H) {
+        CU(cudaMemcpy2DAsync(sl, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sH));
+        CU(cudaMemcpy2DAsync(sr, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sH));
     } else {
         for (int s = 0; s < S; ++s) {
-            CU(cudaMemcpy2DAsync(c->stage_L + s * plane, P0, left + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sI));
-            CU(cudaMemcpy2DAsync(c->stage_R + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sI));
+            CU(cudaMemcpy2DAsync(sl + s * plane, P0, left + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sH));
+            CU(cudaMemcpy2DAsync(sr + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sH));
         }
     }
-    return enqueue_frame(c, c->stage_L, c->stage_R, P0, plane, nullptr, true, in_flight);
+    CU(cudaEventRecord(c->ev_h2d[f & 3], sH));
+    int rc = wait_ring(c, in_flight);
+    if (rc != SVO_OK) return rc;
+    CU(cudaStreamWaitEvent(ingest_stream(c, in_flight), c->ev_h2d[f & 3], 0));
+    return enqueue_frame(c, sl, sr, P0, plane, nullptr, true, in_flight);
 }
 
 extern "C" int svo_submit_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride) {

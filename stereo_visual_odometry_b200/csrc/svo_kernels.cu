@@ -906,17 +906,31 @@ void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int
 // looks its winners up in this cache.  Anything not cached (low-threshold retry, failed PnP, ...) goes through
 // klt_kernel afterwards, so the cache never changes a result, only when it is computed.
 // the buckets that hold a thr-20 FAST winner, as an unordered list (one warp-aggregated atomic per 32 buckets)
+// The list has two ends: candidates that the pruning prediction of the PREVIOUS frame would not have skipped go
+// to the front (they almost certainly have to be tracked), the others to the back -- the warps reach those last,
+// by which time this frame's prediction has arrived and most of them are skipped (klt_spec_fast_kernel).
+// d.nF[seq] / d.nF[n_seq + seq] count the two ends.  Order only: which candidates are tracked never changes a result.
 __global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, BucketGeom bg, int keybuf, int specbuf) {
     const int seq = blockIdx.y, lane = threadIdx.x & 31;
     const int b = blockIdx.x * 256 + threadIdx.x;
     const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
-    const bool has = b < bg.nb && ld_key(keyA + b) != 0ull;
-    const unsigned m = __ballot_sync(0xffffffffu, has);
-    int base = 0;
-    if (lane == 0 && m) base = atomicAdd(d.nF + seq, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (has) d.listF[(long long)seq * bg.nb + base + __popc(m & ((1u << lane) - 1u))] = b;
-    (void)specbuf;
+    const int* pold = d.predT + ((long long)(specbuf ^ 1) * d.n_seq + seq) * bg.nb;
+    const int* pnow = d.predT + ((long long)specbuf * d.n_seq + seq) * bg.nb;
+    const unsigned long long ka = b < bg.nb ? ld_key(keyA + b) : 0ull;
+    const bool has = ka != 0ull;
+    const bool late = has && bucket_key_score(ka) + 0x8000 <= max(__ldcg(pold + b), __ldcg(pnow + b));
+    const unsigned mf = __ballot_sync(0xffffffffu, has && !late), ml = __ballot_sync(0xffffffffu, late);
+    int bf = 0, bl = 0;
+    if (lane == 0) {
+        if (mf) bf = atomicAdd(d.nF + seq, __popc(mf));
+        if (ml) bl = atomicAdd(d.nF + d.n_seq + seq, __popc(ml));
+    }
+    bf = __shfl_sync(0xffffffffu, bf, 0);
+    bl = __shfl_sync(0xffffffffu, bl, 0);
+    int* list = d.listF + (long long)seq * bg.nb;
+    const unsigned below = (1u << lane) - 1u;
+    if (has && !late) list[bf + __popc(mf & below)] = b;
+    if (late) list[bg.nb - 1 - (bl + __popc(ml & below))] = b;
 }
 __global__ void __launch_bounds__(KLT_WARPS * 32, 4)
 klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int keybuf,
@@ -930,14 +944,14 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
     const long long so = ((long long)specbuf * d.n_seq + seq) * bg.nb;
     const int* list = d.listF + (long long)seq * bg.nb;
     const int* pred = d.predT + ((long long)specbuf * d.n_seq + seq) * bg.nb;
-    const int n = d.nF[seq];
+    const int n_front = d.nF[seq], n = n_front + d.nF[d.n_seq + seq];
     int* counter = d.cntF + seq;
     for (;;) {
         int t = 0;
         if (lane == 0) t = atomicAdd(counter, 1);
         t = __shfl_sync(0xffffffffu, t, 0);
         if (t >= n) break;
-        const int b = list[t];
+        const int b = list[t < n_front ? t : bg.nb - 1 - (t - n_front)];
         const unsigned long long ka = ld_key(keyA + b);
         // A FAST winner only enters circular matching when it beats every tracked feature of its bucket (strictly
         // greater score).  bucket_merge_kernel of the previous frame predicts, per bucket, the best score a tracked
@@ -1000,7 +1014,7 @@ int klt_spec_resident_blocks_per_sm() {
 void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
                           int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st) {
     cudaMemsetAsync(d.cntF, 0, sizeof(int) * d.n_seq, st);
-    cudaMemsetAsync(d.nF, 0, sizeof(int) * d.n_seq, st);
+    cudaMemsetAsync(d.nF, 0, sizeof(int) * 2 * d.n_seq, st);
     spec_fast_list_kernel<<<dim3((bg.nb + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg, keybuf, specbuf);
     dim3 grid(blocks_per_seq, d.n_seq);
     klt_spec_fast_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur, keybuf, specbuf);
