@@ -113,6 +113,7 @@ struct svo_ctx {
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     int f_share = 50;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
+    cudaEvent_t ev_td[4] = {nullptr, nullptr, nullptr, nullptr};    // every bucketed feature of f has its circular-matching result
     cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
     cudaEvent_t ev_trk[4] = {nullptr, nullptr, nullptr, nullptr};   // speculative KLT of frame f complete
     cudaEvent_t ev_fa[4] = {nullptr, nullptr, nullptr, nullptr};    // chain of frame f complete
@@ -344,6 +345,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_td[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_trk[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_spf[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_bm[i], cudaEventDisableTiming));
@@ -403,6 +405,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.hyp_pose, S * d.n_hyp * 12));
     CU(dev_alloc(c, &d.hyp_count, S * d.n_hyp));
     CU(dev_alloc(c, &d.inl_idx, C));
+    CU(dev_alloc(c, &d.m_src, C));
     CU(dev_alloc(c, &d.klt_next, S));
     d.nb = c->bg.nb;
     CU(dev_alloc(c, &d.specF_pts, (size_t)2 * S * c->bg.nb * 4));
@@ -501,6 +504,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
         if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
+        if (c->ev_td[i]) cudaEventDestroy(c->ev_td[i]);
         if (c->ev_trk[i]) cudaEventDestroy(c->ev_trk[i]);
         if (c->ev_spf[i]) cudaEventDestroy(c->ev_spf[i]);
         if (c->ev_bm[i]) cudaEventDestroy(c->ev_bm[i]);
@@ -620,7 +624,7 @@ static cudaStream_t ingest_stream(const svo_ctx* c, bool speculate) {
 // One frame = a fixed set of launches on four streams (see the file header).  Dependencies of frame f:
 //   ingest(f)    [stream_in]  after select(f - 2): pyramid slot / FAST key buffer f % 3 are free again
 //   F(f), T(f)   [stream_k]   speculative circular matching of the candidates of frame f: F needs ingest(f),
-//                             T needs select(f - 1) (the matched list); results are a cache keyed by bucket /
+//                             T needs the bucketed list of f - 1 with its keep bits (klt(f - 1) done); results are a cache keyed by bucket /
 //                             matched index that bucket_merge(f) looks up
 //   chain(f)     [stream]     bucket_merge (needs the inliers of f - 1 and the cache) -> klt (only what the cache
 //                             missed) -> select -> hypotheses -> inliers / feature set
@@ -654,7 +658,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     }
     if (spec && !first) {
         // the two candidate classes run side by side, each on half of the partition's block slots: F(f) as soon
-        // as image f is there (typically a frame ahead), T(f) the moment select(f - 1) has produced the matched list
+        // as image f is there (typically a frame ahead), T(f) the moment every bucketed feature of f - 1 has its keep bit
         const int half = c->klt_blocks_k > 1 ? (int)((long long)c->klt_blocks_k * c->f_share / 100) : 1;
         cudaStream_t sK2 = c->stream_k2;
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
@@ -664,7 +668,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         }
         CU(cudaEventRecord(c->ev_spf[e], sK));
         CU(cudaStreamWaitEvent(sK2, c->ev_in[e], 0));
-        CU(cudaStreamWaitEvent(sK2, c->ev_sel[e1], 0));
+        CU(cudaStreamWaitEvent(sK2, c->ev_td[e1], 0));   // the bucketed list of f - 1 with its keep bits
         {
             TraceScope ts(c, "spec_trk", 2, sK2);
             launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, sK2);
@@ -679,6 +683,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         launch_first_frame(c->d, sP);
         c->launches += 1;
         CU(cudaEventRecord(c->ev_sel[e], sP));
+        CU(cudaEventRecord(c->ev_td[e], sP));
     } else {
         {
             TraceScope ts(c, "bucket", 3, sP);
@@ -700,6 +705,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
             CU(cudaEventRecord(c->ev_trk[e], sK));
             CU(cudaStreamWaitEvent(sP, c->ev_trk[e], 0));
         }
+        if (!tm) CU(cudaEventRecord(c->ev_td[e], sP));   // T(f + 1) may start: it reads the bucketed list + keep bits
         if (c->timers) cudaEventRecord(c->ev[3], sP);
         {
             TraceScope ts(c, "select", 3, sP);
@@ -740,7 +746,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (!tm) {
         CU(cudaEventRecord(c->ev_fb[e], sB));
     } else {   // a later frame may run on the partitions again: it finds every event of this frame signalled
-        for (cudaEvent_t ev : {c->ev_in[e], c->ev_sel[e], c->ev_trk[e], c->ev_spf[e], c->ev_bm[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
+        for (cudaEvent_t ev : {c->ev_in[e], c->ev_td[e], c->ev_sel[e], c->ev_trk[e], c->ev_spf[e], c->ev_bm[e], c->ev_fa[e], c->ev_fb[e]}) CU(cudaEventRecord(ev, sP));
         // no speculative pass consumed / refreshed the FAST-pruning predictions: drop them
         if (c->spec) CU(cudaMemsetAsync(c->d.predT, 0, sizeof(int) * 2 * c->d.n_seq * c->d.nb, sP));
     }

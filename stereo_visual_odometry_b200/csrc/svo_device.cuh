@@ -85,6 +85,7 @@ struct DevArrays {
     float2* lk_L1; float2* lk_R1; float2* lk_R0; float2* lk_C; uint8_t* lk_status;
     // matched (compacted) sets
     float2* m_L0; float2* m_L1; float2* m_R0; float2* m_R1; int* m_age; int* m_str;
+    int* m_src;                       // [cap] bucketed-list index of each matched feature
     float* X3;                        // [cap][3] matched (compacted)
     float* X3u;                       // [cap][3] inlier 3-D points, compacted for the LM refit
     float2* in_uv;                    // [cap] inlier image points, compacted for the LM refit
@@ -97,7 +98,8 @@ struct DevArrays {
     int* klt_next;                    // [n_seq] next todo index for the persistent KLT warps
     // speculative KLT cache (see svo_kernels.cu "speculative tracking"): circular-matching results of
     //   F: the FAST winner of every bucket of the previous left image   [frame & 1][n_seq][nb]
-    //   T: every matched feature of the previous frame at its t1 position [n_seq][cap]
+    //   T: every matched feature of the previous frame at its t1 position [n_seq][cap], indexed by its position in
+    //      the previous frame's BUCKETED list (m_src maps matched -> bucketed)
     // entry = 4 leg outputs + status bits (bit 4 = keep) + LK iteration count
     float2* specF_pts; uint8_t* specF_st; int* specF_it;
     float2* specT_pts; uint8_t* specT_st; int* specT_it;

@@ -596,6 +596,7 @@ __global__ void __launch_bounds__(256) bucket_keys_kernel(DevArrays d, BucketGeo
         s->lk_iters = 0;
         d.n_todo[seq] = 0;
         d.klt_next[seq] = 0;
+        d.cntT[seq] = 0;   // klt_spec_trk_kernel of the NEXT frame (this frame's has finished)
     }
     if (i >= n) return;
     const float2 p = d.fs_xy[fo + i];
@@ -687,7 +688,7 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
                     sp = d.specF_pts; sst = d.specF_st; sit = d.specF_it;
                 }
             } else if (trk_ok) {
-                src = fo + d.inl_idx[fo + order];
+                src = fo + d.m_src[fo + d.inl_idx[fo + order]];   // feature -> matched -> bucketed index of the last frame
                 sp = d.specT_pts; sst = d.specT_st; sit = d.specT_it;
             }
         }
@@ -901,7 +902,7 @@ void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int
 // Which features enter circular matching of frame f is only known after the PnP of frame f - 1 (inliers) --
 // but every candidate is known earlier and tracking one feature does not depend on any other:
 //   F(f): the FAST winner of each bucket of left image f - 1   (known once image f - 1 and f are ingested)
-//   T(f): every feature matched in frame f - 1, at its t1 position, young enough (known after select(f - 1))
+//   T(f): every feature matched in frame f - 1, at its t1 position, young enough (the keep bits of the bucketed list of f - 1)
 // Both are tracked ahead of time on their own SM partition while PnP(f - 1) runs; bucket_merge_kernel(f) then
 // looks its winners up in this cache.  Anything not cached (low-threshold retry, failed PnP, ...) goes through
 // klt_kernel afterwards, so the cache never changes a result, only when it is computed.
@@ -985,7 +986,9 @@ klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int s
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     long long base[4];
     circ_bases(pg, seq, slot_prev, slot_cur, base);
-    const int n = d.state[seq].n_matched;
+    // work list = the bucketed list of the frame that has just been matched: every entry with the keep bit becomes
+    // a matched feature (select_kernel only compacts), so this kernel need not wait for the compaction
+    const int n = d.state[seq].n_bucketed;
     const long long fo = (long long)seq * d.cap;
     int* counter = d.cntT + seq;
     for (;;) {
@@ -993,8 +996,9 @@ klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int s
         if (lane == 0) k = atomicAdd(counter, 1);
         k = __shfl_sync(0xffffffffu, k, 0);
         if (k >= n) break;
-        if (d.m_age[fo + k] >= bg.age_threshold) continue;   // bucketing drops it (feature_set.cpp:24)
-        const Circ r = track_circular(d, pg, pc, base, d.m_L1[fo + k], lane, patch[wid]);
+        if (!(d.lk_status[fo + k] & 16)) continue;                                    // not matched
+        if (d.bk_age[fo + k] + pc.age_increment >= bg.age_threshold) continue;        // bucketing drops it (feature_set.cpp:24)
+        const Circ r = track_circular(d, pg, pc, base, d.lk_L1[fo + k], lane, patch[wid]);
         if (lane == 0) {
             const long long o = fo + k;
             d.specT_pts[o * 4 + 0] = r.a;
@@ -1021,7 +1025,7 @@ void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfi
 }
 void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
                          int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st) {
-    dim3 grid(blocks_per_seq, d.n_seq);   // d.cntT was reset by select_kernel
+    dim3 grid(blocks_per_seq, d.n_seq);   // d.cntT was reset by bucket_keys_kernel
     klt_spec_trk_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur);
 }
 
@@ -1191,6 +1195,7 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
         d.m_R1[fo + off] = d.lk_R1[fo + i];
         d.m_age[fo + off] = age;
         d.m_str[fo + off] = str;
+        d.m_src[fo + off] = i;
         // currentVOFeatures after matchingFeatures: t0 coordinates (vo.cpp:360)
         d.fs_xy[fo + off] = p0;
         d.fs_age[fo + off] = age;
@@ -1211,7 +1216,6 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
             s->pnp_ok = 0;
             s->spec_bad = n == 0 ? 1 : 0;   // the old pyramids stay: what was tracked ahead for the next frame is void
             s->fs_from_inliers = 0;         // the feature set now holds the matched set at t0 positions
-            d.cntT[seq] = 0;
         }
     }
 }
