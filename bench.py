@@ -210,10 +210,16 @@ def run_gpu(args, rank, world, local_rank):
     fsz = C.sizeof(FrameResult)
     k = 0
 
+    # buffer addresses of the frames (device-resident and pinned-host copies), looked up once
+    Ld_ptr = [Ld[j].data_ptr() for j in range(n_unique)]
+    Rd_ptr = [Rd[j].data_ptr() for j in range(n_unique)]
+    Lp_ptr = [Lp[j].data_ptr() for j in range(n_unique)]
+    Rp_ptr = [Rp[j].data_ptr() for j in range(n_unique)]
+    res_ptr = res_dev.data_ptr()
+
     def enqueue(ctx_, i):
         j = pingpong(i, n_unique)
-        check(L_.svo_process_frame_batch_dev(ctx_, Ld[j].data_ptr(), Rd[j].data_ptr(), W, W * H,
-                                             res_dev.data_ptr() + i * fsz))
+        check(L_.svo_process_frame_batch_dev(ctx_, Ld_ptr[j], Rd_ptr[j], W, W * H, res_ptr + i * fsz))
 
     enqueue(ctx, 0)
     k = 1
@@ -303,7 +309,7 @@ def run_gpu(args, rank, world, local_rank):
             ok = 0
             for _ in range(n):
                 j = pingpong(kk, n_unique)
-                check(L_.svo_submit_frame(ctx2, Lp[j].data_ptr(), Rp[j].data_ptr(), W))
+                check(L_.svo_submit_frame(ctx2, Lp_ptr[j], Rp_ptr[j], W))
                 kk += 1
                 if L_.svo_pending(ctx2) > E2E_DEPTH:
                     ok += check(L_.svo_collect(ctx2, C.byref(fr)))
@@ -322,7 +328,7 @@ def run_gpu(args, rank, world, local_rank):
         n_sync = min(n_e2e, 300)
         for _ in range(n_sync):
             j = pingpong(kk, n_unique)
-            check(L_.svo_process_frame(ctx2, Lp[j].data_ptr(), Rp[j].data_ptr(), W, ptr(T, C.c_double)))
+            check(L_.svo_process_frame(ctx2, Lp_ptr[j], Rp_ptr[j], W, ptr(T, C.c_double)))
             kk += 1
         dt_sync = time.perf_counter() - t0
         e2e = {"value": world * n_e2e / dt, "unit": "frames/s", "h2d_bytes_per_step": 2 * W * H * FRAMES_PER_STEP,

@@ -137,7 +137,8 @@ int svo_pending(svo_ctx* ctx);                  /* submitted, not yet collected 
 int svo_stream_join(svo_ctx* ctx);
 /* Pipeline introspection (synchronises): out = { speculative tracking on, SMs of the chain / ingest / KLT
  * partitions (0 = whole GPU, no partitioning), features of sequence 0 the last frame had to track outside the
- * speculative cache, persistent KLT blocks per sequence (chain side / KLT partition), 0 }. */
+ * speculative cache, persistent KLT blocks per sequence (chain side / KLT partition), FAST-winner candidates of the
+ * last speculative pass: tracked | skipped << 16 }. */
 int svo_pipeline_info(svo_ctx* ctx, int out[8]);
 int svo_synchronize(svo_ctx* ctx);
 /* Last frame's result for sequence `seq` (host copy; synchronises). */

@@ -814,7 +814,8 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
     CU(cudaEventRecord(c->ev_h2d[f & 3], sH));
     int rc = wait_ring(c, in_flight);
     if (rc != SVO_OK) return rc;
-    CU(cudaStreamWaitEvent(ingest_stream(c, in_flight), c->ev_h2d[f & 3], 0));
+    cudaStream_t sI = ingest_stream(c, in_flight);
+    CU(cudaStreamWaitEvent(sI, c->ev_h2d[f & 3], 0));
     return enqueue_frame(c, sl, sr, P0, plane, nullptr, true, in_flight);
 }
 
@@ -881,6 +882,20 @@ extern "C" int svo_pipeline_info(svo_ctx* c, int out[8]) {
     out[5] = c->klt_blocks;
     out[6] = c->klt_blocks_k;
     out[7] = 0;
+    if (c->spec && c->frames > 1) {   // FAST candidates of the last speculative pass: tracked | skipped << 16
+        const long long nb = c->d.nb;
+        const int buf = (int)((c->frames - 1) & 1);
+        std::vector<int> list(nb);
+        std::vector<uint8_t> st(nb);
+        int nf[2] = {0, 0};
+        CU(cudaMemcpy(&nf[0], c->d.nF, sizeof(int), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(&nf[1], c->d.nF + c->d.n_seq, sizeof(int), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(list.data(), c->d.listF, sizeof(int) * nb, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(st.data(), c->d.specF_st + (long long)buf * c->d.n_seq * nb, nb, cudaMemcpyDeviceToHost));
+        int skipped = 0;
+        for (int t = 0; t < nf[0] + nf[1] && t < nb; ++t) skipped += (st[list[t < nf[0] ? t : nb - 1 - (t - nf[0])]] & 0x80) ? 1 : 0;
+        out[7] = (nf[0] + nf[1] - skipped) | (skipped << 16);
+    }
     return SVO_OK;
 }
 

@@ -1,18 +1,32 @@
-import sys, time, ctypes as C, numpy as np
+"""Debug tool: per-frame counters of the streaming pipeline (cache misses, FAST candidates tracked / skipped)."""
+import ctypes as C
+import sys
+
+import numpy as np
+
 sys.path.insert(0, '.')
-from oracle import synth
-from stereo_visual_odometry_b200 import vo as V
-from stereo_visual_odometry_b200._lib import lib, check
-W, H = 1241, 376
-seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=12, seed=0)
-fr = [seq.render(i) for i in range(12)]
-vo = V.VisualOdometry(W, H)
-vo.initalize_projection_matricies(seq.Pl, seq.Pr)
+import torch  # noqa: E402
+
+from oracle import synth  # noqa: E402
+from stereo_visual_odometry_b200._lib import FrameResult, check, default_params, lib, ptr  # noqa: E402
+
+W, H, N = 1241, 376, 40
+seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=N, seed=0)
+Ls, Rs = zip(*[seq.render(i) for i in range(N)])
+Lp = torch.from_numpy(np.stack(Ls)).pin_memory()
+Rp = torch.from_numpy(np.stack(Rs)).pin_memory()
+L_ = lib()
+ctx = L_.svo_create(C.byref(default_params(W, H)))
+Pl, Pr = np.ascontiguousarray(seq.Pl), np.ascontiguousarray(seq.Pr)
+check(L_.svo_set_projection(ctx, ptr(Pl, C.c_float), ptr(Pr, C.c_float)))
+fr = FrameResult()
 info = (C.c_int * 8)()
-for i, (L, R) in enumerate(fr):
-    t0 = time.perf_counter()
-    ok, T = vo.stereo_callback(L, R)
-    dt = time.perf_counter() - t0
-    check(lib().svo_pipeline_info(vo._ctx, info))
-    r = vo.last_result()
-    print(i, ok, 'bucketed', r.n_bucketed, 'matched', r.n_matched, 'inl', r.n_inliers, 'info', list(info), 'ms %.3f' % (dt * 1e3))
+for k in range(N):
+    check(L_.svo_submit_frame(ctx, Lp[k].data_ptr(), Rp[k].data_ptr(), W))
+    if k % 4 == 3:   # a few frames in flight, then look at the last one
+        while L_.svo_pending(ctx) > 0:
+            check(L_.svo_collect(ctx, C.byref(fr)))
+        check(L_.svo_pipeline_info(ctx, info))
+        print(f"frame {k}: bucketed {fr.n_bucketed} matched {fr.n_matched} inliers {fr.n_inliers} cache misses {info[4]} "
+              f"FAST candidates tracked {info[7] & 0xFFFF} skipped {info[7] >> 16}")
+L_.svo_destroy(ctx)
