@@ -225,17 +225,24 @@ static int validate_params(const svo_params* p) {
 
 // Streams of a context.  A single-sequence context is latency bound: its pose chain (a few small blocks) must
 // never wait for a block slot behind the persistent tracking kernels, so the SMs are split with CUDA green
-// contexts into chain / ingest / KLT partitions (SVO_PARTITION="chain,ingest" SM counts, "0" = off; default
-// 16,8 of the 148 SMs).  Batched contexts are throughput bound and use plain streams on the whole GPU.
+// contexts into chain / ingest / KLT partitions (SVO_PARTITION="chain,ingest" SM counts, "0" = off, ingest 0 =
+// the ingest shares the chain partition; default 16,0 of the 148 SMs: the rest tracks).  Batched contexts are throughput bound and use plain streams on the whole GPU.
 // SVO_SPEC=0/1 overrides whether the speculative tracking runs (default: single-sequence contexts only).
 static int create_streams(svo_ctx* c, const svo_params* p) {
-    int want_chain = 16, want_in = 8;
+    int want_chain = 16, want_in = 0;
     c->spec = p->n_seq == 1 && c->pipeline_ctx && channels_of(*p) == 1;   // 8UC3 mode: plain serial frames
     if (const char* e = getenv("SVO_SPEC"))
         if (c->pipeline_ctx && channels_of(*p) == 1) c->spec = atoi(e) != 0;
     if (const char* e = getenv("SVO_PARTITION")) {
         want_chain = want_in = 0;
         sscanf(e, "%d,%d", &want_chain, &want_in);
+    } else if (getenv("NV_COMPUTE_PROFILER_PERFWORKS_DIR")) {
+        // Nsight Compute cannot always set up kernels launched into green contexts ("Failed to prepare kernel for
+        // profiling"): under ncu the context runs unpartitioned unless SVO_PARTITION asks for it explicitly
+        want_chain = want_in = 0;
+        static bool told = false;
+        if (!told) fprintf(stderr, "svo: running under Nsight Compute, SM partitions off (set SVO_PARTITION to force them)\n");
+        told = true;
     }
     if (const char* e = getenv("SVO_FSHARE")) {
         const int v = atoi(e);
@@ -245,7 +252,8 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, p->device));
     bool ok = false;
-    if (want_chain >= 8 && want_in >= 8 && want_chain + want_in + 16 <= prop.multiProcessorCount) {
+    // want_in == 0: the ingest shares the chain partition (its stream is created there)
+    if (want_chain >= 8 && (want_in >= 8 || want_in == 0) && want_chain + want_in + 16 <= prop.multiProcessorCount) {
 #define DRV(name)                                                                                      \
     decltype(&name) p_##name = nullptr;                                                                \
     {                                                                                                  \
@@ -290,7 +298,7 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
                 for (int i = 0; i < n_in; ++i) sm_cnt[1] += grp[n_chain + i].sm.smCount;
                 for (int i = 0; i < nk; ++i) sm_cnt[2] += kl[i].sm.smCount;
                 TRY(p_cuDevResourceGenerateDesc(&dc[0], grp, n_chain));
-                if (ok) TRY(p_cuDevResourceGenerateDesc(&dc[1], grp + n_chain, n_in));
+                if (ok && n_in > 0) TRY(p_cuDevResourceGenerateDesc(&dc[1], grp + n_chain, n_in));
                 if (ok && p_cuDevResourceGenerateDesc(&dc[2], kl, nk) != CUDA_SUCCESS) {
                     // the remainder may not combine with full groups: leave it unused
                     nk -= rem.sm.smCount > 0 ? 1 : 0;
@@ -299,10 +307,11 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
                 }
             }
             if (dbg) fprintf(stderr, "svo: SM partitions chain %u ingest %u klt %u (groups %u, ok %d)\n", sm_cnt[0], sm_cnt[1], sm_cnt[2], ngrp, (int)ok);
-            for (int i = 0; i < 3 && ok; ++i) TRY(p_cuGreenCtxCreate(&gc[i], dc[i], p->device, CU_GREEN_CTX_DEFAULT_STREAM));
+            for (int i = 0; i < 3 && ok; ++i)
+                if (i != 1 || n_in > 0) TRY(p_cuGreenCtxCreate(&gc[i], dc[i], p->device, CU_GREEN_CTX_DEFAULT_STREAM));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[0], gc[0], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[1], gc[0], CU_STREAM_NON_BLOCKING, 0));
-            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[2], gc[1], CU_STREAM_NON_BLOCKING, 0));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[2], n_in > 0 ? gc[1] : gc[0], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[3], gc[2], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[4], gc[2], CU_STREAM_NON_BLOCKING, -1));
             if (ok) {
@@ -671,7 +680,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         CU(cudaStreamWaitEvent(sK2, c->ev_td[e1], 0));   // the bucketed list of f - 1 with its keep bits
         {
             TraceScope ts(c, "spec_trk", 2, sK2);
-            launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, sK2);
+            launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, (int)(f & 1), sK2);
         }
         CU(cudaEventRecord(c->ev_trk[e], sK2));
         CU(cudaStreamWaitEvent(sP, c->ev_spf[e], 0));

@@ -980,7 +980,7 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
     }
 }
 __global__ void __launch_bounds__(KLT_WARPS * 32, 4)
-klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur) {
+klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int specbuf) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -990,6 +990,7 @@ klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int s
     // a matched feature (select_kernel only compacts), so this kernel need not wait for the compaction
     const int n = d.state[seq].n_bucketed;
     const long long fo = (long long)seq * d.cap;
+    const int* pred = d.predT + ((long long)specbuf * d.n_seq + seq) * bg.nb;
     int* counter = d.cntT + seq;
     for (;;) {
         int k = 0;
@@ -997,8 +998,21 @@ klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int s
         k = __shfl_sync(0xffffffffu, k, 0);
         if (k >= n) break;
         if (!(d.lk_status[fo + k] & 16)) continue;                                    // not matched
-        if (d.bk_age[fo + k] + pc.age_increment >= bg.age_threshold) continue;        // bucketing drops it (feature_set.cpp:24)
-        const Circ r = track_circular(d, pg, pc, base, d.lk_L1[fo + k], lane, patch[wid]);
+        const int age1 = d.bk_age[fo + k] + pc.age_increment;
+        if (age1 >= bg.age_threshold) continue;                                       // bucketing drops it (feature_set.cpp:24)
+        const float2 p0 = d.lk_L1[fo + k];
+        {
+            // bucketing of the coming frame only keeps the best tracked feature of a bucket: a feature that the
+            // prediction (best score per bucket, complete by now) beats is not tracked ahead.  If the predicted
+            // winner then turns out a PnP outlier, this one is a cache miss and goes through klt_kernel.
+            const int br = (int)__fdiv_rn(p0.y, (float)bg.bh), bc = (int)__fdiv_rn(p0.x, (float)bg.bw);
+            const bool in_grid = br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw;
+            if (!in_grid || bucket_score(age1, d.bk_str[fo + k], bg.fast_threshold) + 0x8000 < __ldcg(pred + br * bg.n_bw + bc)) {
+                if (lane == 0) d.specT_st[fo + k] = 0x80;
+                continue;
+            }
+        }
+        const Circ r = track_circular(d, pg, pc, base, p0, lane, patch[wid]);
         if (lane == 0) {
             const long long o = fo + k;
             d.specT_pts[o * 4 + 0] = r.a;
@@ -1024,9 +1038,9 @@ void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfi
     klt_spec_fast_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur, keybuf, specbuf);
 }
 void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
-                         int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st) {
+                         int blocks_per_seq, int slot_prev, int slot_cur, int specbuf, cudaStream_t st) {
     dim3 grid(blocks_per_seq, d.n_seq);   // d.cntT was reset by bucket_keys_kernel
-    klt_spec_trk_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur);
+    klt_spec_trk_kernel<<<grid, KLT_WARPS * 32, 0, st>>>(d, pg, pc, bg, slot_prev, slot_cur, specbuf);
 }
 
 __global__ void __launch_bounds__(KLT_WARPS * 32)

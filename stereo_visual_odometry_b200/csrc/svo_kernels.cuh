@@ -40,7 +40,7 @@ void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeCon
 void launch_klt_spec_fast(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
                           int blocks_per_seq, int slot_prev, int slot_cur, int keybuf, int specbuf, cudaStream_t st);
 void launch_klt_spec_trk(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, const BucketGeom& bg,
-                         int blocks_per_seq, int slot_prev, int slot_cur, cudaStream_t st);
+                         int blocks_per_seq, int slot_prev, int slot_cur, int specbuf, cudaStream_t st);
 int klt_resident_blocks_per_sm();
 int klt_spec_resident_blocks_per_sm();   // same for the speculative kernels   // persistent KLT blocks that fit one SM (occupancy query)
 void launch_klt(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, int blocks_per_seq, int slot_prev,

@@ -1,4 +1,4 @@
-"""Debug tool: per-frame counters of the streaming pipeline (cache misses, FAST candidates tracked / skipped)."""
+"""Debug tool: counters of the streaming pipeline in steady state (cache misses, FAST candidates tracked / skipped)."""
 import ctypes as C
 import sys
 
@@ -16,17 +16,19 @@ Ls, Rs = zip(*[seq.render(i) for i in range(N)])
 Lp = torch.from_numpy(np.stack(Ls)).pin_memory()
 Rp = torch.from_numpy(np.stack(Rs)).pin_memory()
 L_ = lib()
-ctx = L_.svo_create(C.byref(default_params(W, H)))
-Pl, Pr = np.ascontiguousarray(seq.Pl), np.ascontiguousarray(seq.Pr)
-check(L_.svo_set_projection(ctx, ptr(Pl, C.c_float), ptr(Pr, C.c_float)))
 fr = FrameResult()
 info = (C.c_int * 8)()
-for k in range(N):
-    check(L_.svo_submit_frame(ctx, Lp[k].data_ptr(), Rp[k].data_ptr(), W))
-    if k % 4 == 3:   # a few frames in flight, then look at the last one
-        while L_.svo_pending(ctx) > 0:
+for stop in (25, 30, 35, 40):   # stream `stop` frames with 3 in flight, then look at the counters of the last one
+    ctx = L_.svo_create(C.byref(default_params(W, H)))
+    Pl, Pr = np.ascontiguousarray(seq.Pl), np.ascontiguousarray(seq.Pr)
+    check(L_.svo_set_projection(ctx, ptr(Pl, C.c_float), ptr(Pr, C.c_float)))
+    for k in range(stop):
+        check(L_.svo_submit_frame(ctx, Lp[k].data_ptr(), Rp[k].data_ptr(), W))
+        if L_.svo_pending(ctx) > 3:
             check(L_.svo_collect(ctx, C.byref(fr)))
-        check(L_.svo_pipeline_info(ctx, info))
-        print(f"frame {k}: bucketed {fr.n_bucketed} matched {fr.n_matched} inliers {fr.n_inliers} cache misses {info[4]} "
-              f"FAST candidates tracked {info[7] & 0xFFFF} skipped {info[7] >> 16}")
-L_.svo_destroy(ctx)
+    while L_.svo_pending(ctx) > 0:
+        check(L_.svo_collect(ctx, C.byref(fr)))
+    check(L_.svo_pipeline_info(ctx, info))
+    print(f"frame {stop - 1}: bucketed {fr.n_bucketed} matched {fr.n_matched} inliers {fr.n_inliers} cache misses {info[4]} "
+          f"FAST candidates tracked {info[7] & 0xFFFF} skipped {info[7] >> 16}")
+    L_.svo_destroy(ctx)
