@@ -55,3 +55,19 @@ def test_no_cpu_fallback():
         featureDetectionFast(img, 20)
     with pytest.raises(SvoError):
         VisualOdometry(64, 64)
+
+
+def test_invalid_parameters_are_rejected_before_any_device_work():
+    """svo_create validates its parameters first: these fail with SVO_ERR_INVALID messages with or without a GPU."""
+    import ctypes as C
+    from stereo_visual_odometry_b200._lib import default_params, lib
+    L = lib()
+    for kw, needle in [(dict(width=8), "image size"), (dict(n_seq=0), "n_seq"), (dict(channels=2), "channels"),
+                       (dict(win_size=21), "winSize"), (dict(max_level=7), "max_level"), (dict(fast_threshold=0), "fast_threshold"),
+                       (dict(ransac_hypotheses=0), "ransac_hypotheses"), (dict(buckets_along_width=0), "bucket")]:
+        p = default_params(640, 480)
+        for k, v in kw.items():
+            setattr(p, k, v)
+        ctx = L.svo_create(C.byref(p))
+        assert not ctx, kw
+        assert needle in L.svo_last_error().decode(), (kw, L.svo_last_error())

@@ -273,3 +273,52 @@ def test_empty_frame_keeps_the_previous_pyramids():
             assert r.n_bucketed == 0
         if ok:
             assert np.abs(T - rT).max() < 5e-3
+
+
+def test_streaming_matches_synchronous_calls_at_kitti_size():
+    """The benchmarked configuration: 40 KITTI-shape frames through submit / collect with frames in flight (SM
+    partitions, both speculative kernels, candidate pruning, bucketed-list hand-over) against the plain serial
+    chain -- every transform bit for bit, every per-frame counter equal."""
+    import ctypes as C
+    from stereo_visual_odometry_b200._lib import FrameResult
+    seq = synth.make_sequence(n_frames=40, seed=7)
+    frames = list(seq.frames())
+    a = V.VisualOdometry(seq.width, seq.height)
+    a.initalize_projection_matricies(seq.Pl, seq.Pr)
+    sync = []
+    for (L, R) in frames:
+        ok, T = a.stereo_callback(L, R)
+        r = a.last_result()
+        sync.append((ok, T, (r.n_bucketed, r.n_matched, r.n_inliers, r.retry, r.lk_iters)))
+    b = V.VisualOdometry(seq.width, seq.height)
+    b.initalize_projection_matricies(seq.Pl, seq.Pr)
+    fr = FrameResult()
+    got = []
+    for i, (L, R) in enumerate(frames):
+        b.submit(L, R)
+        if i >= 3:
+            V.check(V.lib().svo_collect(b._ctx, C.byref(fr)))
+            got.append((bool(fr.success), np.array(fr.transform).reshape(4, 4), (fr.n_bucketed, fr.n_matched, fr.n_inliers, fr.retry, fr.lk_iters)))
+    while len(got) < len(frames):
+        V.check(V.lib().svo_collect(b._ctx, C.byref(fr)))
+        got.append((bool(fr.success), np.array(fr.transform).reshape(4, 4), (fr.n_bucketed, fr.n_matched, fr.n_inliers, fr.retry, fr.lk_iters)))
+    assert sum(ok for ok, _, _ in sync) >= len(frames) - 2
+    for k, ((ok0, T0, c0), (ok1, T1, c1)) in enumerate(zip(sync, got)):
+        assert ok0 == ok1 and np.array_equal(T0, T1) and c0 == c1, (k, c0, c1)
+
+
+def test_padded_row_strides_equal_contiguous_images():
+    """Images that are views into wider buffers (row stride > width, odd width): same results as contiguous copies."""
+    seq = synth.make_sequence(width=637, height=241, n_frames=5, seed=9)
+    frames = list(seq.frames())
+    a = V.VisualOdometry(637, 241)
+    a.initalize_projection_matricies(seq.Pl, seq.Pr)
+    b = V.VisualOdometry(637, 241)
+    b.initalize_projection_matricies(seq.Pl, seq.Pr)
+    rng = np.random.default_rng(0)
+    for (L, R) in frames:
+        big = rng.integers(0, 256, (2, 241, 701), dtype=np.uint8)   # garbage beyond the image columns
+        big[0, :, :637], big[1, :, :637] = L, R
+        ok0, T0 = a.stereo_callback(L, R)
+        ok1, T1 = b.stereo_callback(big[0, :, :637], big[1, :, :637])
+        assert ok0 == ok1 and np.array_equal(T0, T1)
