@@ -111,7 +111,7 @@ struct svo_ctx {
     const char* trace_path = nullptr;
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
-    int f_share = 50;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
+    int f_share = 56;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
     cudaEvent_t ev_td[4] = {nullptr, nullptr, nullptr, nullptr};    // every bucketed feature of f has its circular-matching result
     cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
@@ -666,7 +666,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         CU(cudaStreamWaitEvent(sP, c->ev_in[e], 0));
     }
     if (spec && !first) {
-        // the two candidate classes run side by side, each on half of the partition's block slots: F(f) as soon
+        // the two candidate classes run side by side, each on its share (f_share) of the partition's block slots: F(f) as soon
         // as image f is there (typically a frame ahead), T(f) the moment every bucketed feature of f - 1 has its keep bit
         const int half = c->klt_blocks_k > 1 ? (int)((long long)c->klt_blocks_k * c->f_share / 100) : 1;
         cudaStream_t sK2 = c->stream_k2;
