@@ -53,7 +53,7 @@ B_ALG_FRAME = 2 * W * H + 2 * pyramid_bytes(W, H)
 
 
 def render_frames(n_unique, seed):
-    from oracle import synth
+    import synthdata as synth
     seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=n_unique, seed=seed)
     L = np.empty((n_unique, H, W), np.uint8)
     R = np.empty((n_unique, H, W), np.uint8)

@@ -7,7 +7,7 @@ import numpy as np
 sys.path.insert(0, '.')
 import torch  # noqa: E402
 
-from oracle import synth  # noqa: E402
+import synthdata as synth  # noqa: E402
 from stereo_visual_odometry_b200._lib import FrameResult, check, default_params, lib, ptr  # noqa: E402
 
 W, H, N = 1241, 376, 40

@@ -10,7 +10,7 @@ sys.path.insert(0, '.')
 os.environ.setdefault("SVO_TRACE", "gpurun_out/trace.csv")
 import torch  # noqa: E402
 
-from oracle import synth  # noqa: E402
+import synthdata as synth  # noqa: E402
 from stereo_visual_odometry_b200._lib import FrameResult, check, default_params, lib, ptr  # noqa: E402
 
 W, H = 1241, 376
