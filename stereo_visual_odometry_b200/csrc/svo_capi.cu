@@ -111,7 +111,7 @@ struct svo_ctx {
     const char* trace_path = nullptr;
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
-    int f_share = 56;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
+    int f_share = 59;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
     cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
     cudaEvent_t ev_td[4] = {nullptr, nullptr, nullptr, nullptr};    // every bucketed feature of f has its circular-matching result
     cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
@@ -399,6 +399,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     const size_t S = (size_t)p->n_seq, C = S * (size_t)cap;
     CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 2 * SVO_PYR_SLOTS * S));
     CU(dev_alloc(c, &d.fastkeys, (size_t)2 * SVO_PYR_SLOTS * S * c->bg.nb));
+    CU(dev_alloc(c, &d.fast_nA, (size_t)SVO_PYR_SLOTS * S));
     CU(dev_alloc(c, &d.trackkeys, S * c->bg.nb));
     CU(dev_alloc(c, &d.state, S));
     CU(dev_alloc(c, &d.result, S));

@@ -74,6 +74,7 @@ struct FinalJob {
 struct DevArrays {
     uint8_t* pyr;                     // pyramids
     unsigned long long* fastkeys;     // [3][2][n_seq][nb]
+    int* fast_nA;                     // [3][n_seq] buckets with a thr_hi FAST winner (gates the thr_lo pass)
     unsigned long long* trackkeys;    // [n_seq][nb]
     SeqState* state;                  // [n_seq]
     svo_frame_result* result;         // [n_seq]

@@ -150,16 +150,20 @@ __global__ void __launch_bounds__(FT_THREADS)
 fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h, int pitch, int thr_lo,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
-            BucketGeom bg) {
+            BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min) {
+    // low-threshold pass of the pipeline: only needed when the retry of vo.cpp:327-332 can happen at all, i.e. when
+    // the thr_hi pass left fewer than gate_min buckets with a winner (every such bucket yields one bucketed feature)
+    if (gate && gate[blockIdx.z] >= gate_min) return;
     __shared__ __align__(16) uint8_t tile[FT_TH * FT_TW];
     __shared__ __align__(16) uint8_t score[FT_SH * FT_SW];
     __shared__ unsigned short list[FT_TASKS];
-    __shared__ int n_list;
+    __shared__ unsigned short hits[FT_OW * FT_OH];   // score-array positions of the nonzero scores among the outputs
+    __shared__ int n_list, n_hits;
     const int z = blockIdx.z;
     const uint8_t* src = img + (long long)z * img_stride;
     const int x0 = blockIdx.x * FT_OW, y0 = blockIdx.y * FT_OH;
     const int tid = threadIdx.x, lane = tid & 31;
-    if (tid == 0) n_list = 0;
+    if (tid == 0) n_list = n_hits = 0;
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
     // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
     const int tx0 = x0 - 8, ty0 = y0 - 4;
@@ -169,10 +173,19 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     const bool fastpath = (pitch & 3) == 0 && (((size_t)src) & 3) == 0 && ((w + 3) & ~3) <= pitch;
     if (fastpath) {
         const int wmax = ((w + 3) >> 2) - 1;
-        for (int i = tid; i < FT_TH * (FT_TW / 4); i += FT_THREADS) {
+        constexpr int NW = FT_TH * (FT_TW / 4), NIT = (NW + FT_THREADS - 1) / FT_THREADS;
+        unsigned v[NIT];
+#pragma unroll
+        for (int it = 0; it < NIT; ++it) {   // all loads of a thread in flight before the first store
+            const int i = min(tid + it * FT_THREADS, NW - 1);
             const int r = i / (FT_TW / 4), k = i - r * (FT_TW / 4);
             const int gy = min(max(ty0 + r, 0), h - 1), gk = min(max((tx0 >> 2) + k, 0), wmax);
-            reinterpret_cast<unsigned*>(tile)[i] = __ldg(reinterpret_cast<const unsigned*>(src + (long long)gy * pitch) + gk);
+            v[it] = __ldg(reinterpret_cast<const unsigned*>(src + (long long)gy * pitch) + gk);
+        }
+#pragma unroll
+        for (int it = 0; it < NIT; ++it) {
+            const int i = tid + it * FT_THREADS;
+            if (i < NW) reinterpret_cast<unsigned*>(tile)[i] = v[it];
         }
     } else {
         for (int i = tid; i < FT_TH * FT_TW; i += FT_THREADS) {
@@ -225,7 +238,12 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
         for (int e = 0; e < 4; ++e) {
             const int sc = (int)(((e < 2 ? sa : sb) >> (16 * (e & 1))) & 0xFFFFu) - 256;
             const int x = gx + e;
-            if (rowok && x >= 3 && x < w - 3 && sc > thr_lo) out |= (unsigned)(sc - 1) << (8 * e);
+            if (rowok && x >= 3 && x < w - 3 && sc > thr_lo) {
+                out |= (unsigned)(sc - 1) << (8 * e);
+                // an output pixel (not the 1-pixel score halo) with a score: a candidate for phase 3
+                if (!resp_map && r >= 1 && r <= FT_OH && 4 * q + e >= 4 && 4 * q + e < 4 + FT_OW)
+                    hits[atomicAdd(&n_hits, 1)] = (unsigned short)(r * FT_SW + 4 * q + e);
+            }
         }
         reinterpret_cast<unsigned*>(score)[t] = out;
     }
@@ -234,6 +252,30 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs, one output quad per task: most score
     // words are zero and are dismissed with one load
     const float inv_bh = 1.f / (float)bg.bh, inv_bw = 1.f / (float)bg.bw;
+    if (!resp_map) {   // pipeline mode (bucket keys only): one thread per nonzero score instead of the dense sweep
+        const int nh = n_hits;
+        for (int i = tid; i < nh; i += FT_THREADS) {
+            const int idx = hits[i];
+            const uint8_t* sp = score + idx;
+            const int v = *sp;
+            const bool keep = v > sp[-1] && v > sp[1] && v > sp[-FT_SW - 1] && v > sp[-FT_SW] && v > sp[-FT_SW + 1] &&
+                              v > sp[FT_SW - 1] && v > sp[FT_SW] && v > sp[FT_SW + 1];
+            if (!keep) continue;
+            const int gy = y0 + (idx / FT_SW) - 1, gx = x0 + (idx % FT_SW) - 4;
+            const int br = (int)(((float)gy + 0.5f) * inv_bh), bc = (int)(((float)gx + 0.5f) * inv_bw);
+            if (br >= bg.start_row && 0 < bg.age_threshold) {
+                const unsigned long long key = bucket_key(bucket_score(0, v, bg.fast_threshold),
+                                                          SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
+                const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
+                if (keysB) atomicMax(keysB + bidx, key);
+                if (keysA && v >= thr_hi) {
+                    const unsigned long long old = atomicMax(keysA + bidx, key);
+                    if (old == 0ull && countA) atomicAdd(countA + z, 1);   // buckets with a thr_hi winner
+                }
+            }
+        }
+        return;
+    }
     for (int i = tid; i < FT_OH * (FT_OW / 4); i += FT_THREADS) {
         const int oy = i / (FT_OW / 4), oq = i - oy * (FT_OW / 4);
         const int gx0 = x0 + 4 * oq, gy = y0 + oy;
@@ -252,15 +294,18 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
                 const int gx = gx0 + e;
                 if (!keep || gx >= w) continue;
                 outw |= (unsigned)v << (8 * e);
-                if (keysB) {
+                if (keysA || keysB) {
                     // exact for these small integers: the quotient is never within an ulp of an integer from below
                     const int br = (int)(((float)gy + 0.5f) * inv_bh), bc = (int)(((float)gx + 0.5f) * inv_bw);
                     if (br >= bg.start_row && 0 < bg.age_threshold) {
                         const unsigned long long key = bucket_key(bucket_score(0, v, bg.fast_threshold),
                                                                   SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
                         const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
-                        atomicMax(keysB + bidx, key);
-                        if (v >= thr_hi) atomicMax(keysA + bidx, key);
+                        if (keysB) atomicMax(keysB + bidx, key);
+                        if (keysA && v >= thr_hi) {
+                            const unsigned long long old = atomicMax(keysA + bidx, key);
+                            if (old == 0ull && countA) atomicAdd(countA + z, 1);   // buckets with a thr_hi winner
+                        }
                     }
                 }
             }
@@ -279,10 +324,11 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
 
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
-                 unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st) {
+                 unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st,
+                 int* countA, const int* gate, int gate_min) {
     dim3 grid((w + FT_OW - 1) / FT_OW, (h + FT_OH - 1) / FT_OH, n_img);
     fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map,
-                                             map_stride, map_pitch, keysA, keysB, bg);
+                                             map_stride, map_pitch, keysA, keysB, bg, countA, gate, gate_min);
 }
 
 // ---- ordered compaction of the response map (row-major == cv::FAST output order)
@@ -343,12 +389,18 @@ void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pit
 }
 
 // ============================================================================
-// pyrDown (5x5 binomial, (s + 128) >> 8, BORDER_REFLECT_101): shared-memory tiled, separable, word loads.
-// One block = 64 x 8 output pixels <- a 136 x 20 byte source tile (4 bytes of left margin keep the tile word
-// aligned): horizontal 5-tap pass into int16, vertical pass, packed 4-byte stores.  In copy mode the block also
-// writes the 128 x 16 source pixels it covers into the context's level-0 plane, so a new frame is read from HBM
-// exactly once for both the level-0 copy and level 1.
-constexpr int PD_OW = 64, PD_OH = 8, PD_TW = 2 * PD_OW + 8, PD_TH = 2 * PD_OH + 4, PD_THREADS = 256;
+// pyrDown (5x5 binomial, (s + 128) >> 8, BORDER_REFLECT_101): shared-memory tiled, separable, packed 16-bit lanes.
+// One block = 128 x 16 output pixels <- a 288 x 35 byte source tile (16 bytes of margin left and right keep the
+// tile rows 16-byte aligned with the image: 128-bit loads).  A thread owns one output word (4 pixels) of 4 output
+// rows: per source row it splits the 16-byte window around its 8 source columns into even / odd pixels as
+// int16x2 pairs (LOP / PRMT), forms the 1 4 6 4 1 row sums of two adjacent outputs per register (<= 4080 per
+// half), keeps the 11 row sums of its column strip in registers and runs the vertical 1 4 6 4 1 on the packed
+// pairs (<= 65408 per half: no carry between the halves), one PRMT packs the four (v >> 8) bytes.  In copy mode
+// the block also writes the 256 x 32 source pixels it covers into the context's level-0 plane, so a new frame is
+// read from HBM exactly once for both the level-0 copy and level 1.
+// RPT = output rows per thread (block = 128 x 4 * RPT outputs): 4 for batched launches (fewest row sums per output),
+// 2 or 1 when one frame's launch would otherwise be a handful of long blocks (latency instead of throughput).
+constexpr int PD_OW = 128, PD_TW = 2 * PD_OW + 32, PD_THREADS = 128;
 struct PyrDownJob {
     const uint8_t* src[2];    // per camera (n_cam == 1: only [0])
     long long src_seq_stride;
@@ -369,72 +421,120 @@ __device__ __forceinline__ unsigned ld_word_any(const uint8_t* p) {
     if (sh == 0) return w0;
     return __funnelshift_r(w0, __ldg(a + 1), 8 * sh);
 }
+// row sums 1 4 6 4 1 of the four outputs whose source columns are b0, b2, b4, b6 of the window
+// w0 = b[-4..-1], w1 = b[0..3], w2 = b[4..7], w3 = b[8..11]; returns (h0, h1) and (h2, h3) as int16x2
+__device__ __forceinline__ void pd_row_sums(unsigned w0, unsigned w1, unsigned w2, unsigned w3, unsigned& hA,
+                                            unsigned& hB) {
+    const unsigned e0 = w0 & 0x00FF00FFu, e1 = w1 & 0x00FF00FFu, e2 = w2 & 0x00FF00FFu, e3 = w3 & 0x00FF00FFu;
+    const unsigned o0 = __byte_perm(w0, 0u, 0x4341u), o1 = __byte_perm(w1, 0u, 0x4341u), o2 = __byte_perm(w2, 0u, 0x4341u);
+    const unsigned g0 = o0 * 4u + e0, g1 = o1 * 4u + e1, g2 = o2 * 4u + e2;     // even + 4 * odd-to-the-right
+    // outputs (0, 1): centres b0, b2: E[-1..1] + 4 * (O[-1] + O[0]) + 5 * E[0] more
+    hA = e1 * 5u + g1 + __byte_perm(g0, g1, 0x5432u) + __byte_perm(e1, e2, 0x5432u);
+    hB = e2 * 5u + g2 + __byte_perm(g1, g2, 0x5432u) + __byte_perm(e2, e3, 0x5432u);
+}
+template <int PD_ROWS_PER_THREAD>
 __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) {
+    constexpr int PD_OH = 4 * PD_ROWS_PER_THREAD, PD_TH = 2 * PD_OH + 3;
     __shared__ __align__(16) uint8_t tile[PD_TH * PD_TW];
-    __shared__ short hs[PD_TH * PD_OW];
     const int cam = j.n_cam == 2 ? (blockIdx.z & 1) : 0, seq = j.n_cam == 2 ? (blockIdx.z >> 1) : blockIdx.z;
     const uint8_t* src = j.src[cam] + (long long)seq * j.src_seq_stride;
     uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
     const int X0 = blockIdx.x * PD_OW, Y0 = blockIdx.y * PD_OH, tid = threadIdx.x;
-    const int sx0 = 2 * X0 - 4, sy0 = 2 * Y0 - 2;   // image position of tile[0][0]
-    // every byte the block uses lies inside the image: plain word loads (also past w up to the tile edge is fine
-    // as long as it stays inside the row's allocation: require it inside w to keep it simple)
-    const bool interior = sx0 >= 0 && sy0 >= 0 && sx0 + PD_TW + 4 <= j.sw && sy0 + PD_TH <= j.sh;
-    if (interior) {
-        for (int i = tid; i < PD_TH * (PD_TW / 4); i += PD_THREADS) {
-            const int r = i / (PD_TW / 4), k = i - r * (PD_TW / 4);
-            reinterpret_cast<unsigned*>(tile)[i] = ld_word_any(src + (long long)(sy0 + r) * j.spitch + sx0 + 4 * k);
-        }
-    } else {
-        for (int i = tid; i < PD_TH * PD_TW; i += PD_THREADS) {
-            const int r = i / PD_TW, c = i - r * PD_TW;
-            tile[i] = __ldg(src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + reflect101(sx0 + c, j.sw));
-        }
-    }
-    __syncthreads();
-    if (j.copy[cam]) {   // source rows 2*Y0 .. 2*Y0+15, columns 2*X0 .. 2*X0+127 = tile rows 2.., columns 4..
-        uint8_t* cp = j.copy[cam] + (long long)seq * j.copy_seq_stride;
-        for (int i = tid; i < 2 * PD_OH * (2 * PD_OW / 4); i += PD_THREADS) {
-            const int r = i >> 5, k = i & 31;
-            const int gy = 2 * Y0 + r, gx = 2 * X0 + 4 * k;
-            if (gy < j.sh && gx < j.sw)   // whole words: the copy plane's pitch is a multiple of 128
-                *reinterpret_cast<unsigned*>(cp + (long long)gy * j.cpitch + gx) =
-                    *reinterpret_cast<const unsigned*>(tile + (r + 2) * PD_TW + 4 + 4 * k);
-        }
-    }
-    // horizontal pass: hs[r][c] = 1 4 6 4 1 over image columns 2x-2 .. 2x+2 = tile columns 2c+2 .. 2c+6
-    for (int i = tid; i < PD_TH * PD_OW; i += PD_THREADS) {
-        const int r = i >> 6, c = i & 63;
-        const uint8_t* t = tile + r * PD_TW + 2 * c + 2;
-        hs[i] = (short)(t[0] + t[4] + 4 * (t[1] + t[3]) + 6 * t[2]);
-    }
-    __syncthreads();
-    // vertical pass: 4 adjacent outputs per thread, one word store
-    if (tid < PD_OH * PD_OW / 4) {
-        const int y = tid >> 4, c0 = (tid & 15) * 4;
-        const int oy = Y0 + y;
-        if (oy < j.dh) {
-            unsigned out = 0;
+    const int sx0 = 2 * X0 - 16, sy0 = 2 * Y0 - 2;   // image position of tile[0][0]
+    // ---- tile load, 16 bytes per task: one 128-bit load where the chunk lies inside the row and is aligned,
+    // else word by word (inside the row) or byte by byte with the reflected column (the image's edge chunks)
+    const bool al16 = (((size_t)src) & 15) == 0 && (j.spitch & 15) == 0;
+    for (int i = tid; i < PD_TH * (PD_TW / 16); i += PD_THREADS) {
+        const int r = i / (PD_TW / 16), k = i - r * (PD_TW / 16);
+        const int gx = sx0 + 16 * k;
+        const uint8_t* row = src + (long long)reflect101(sy0 + r, j.sh) * j.spitch;
+        uint4 v;
+        if (al16 && gx >= 0 && gx + 16 <= j.sw) {
+            v = __ldg(reinterpret_cast<const uint4*>(row + gx));
+        } else if (gx >= 4 && gx + 20 <= j.sw) {   // unaligned rows: the five aligned words around the chunk
+            const unsigned sh = (unsigned)((size_t)(row + gx) & 3);
+            const unsigned* a = reinterpret_cast<const unsigned*>(row + gx - sh);
+            const unsigned a0 = __ldg(a), a1 = __ldg(a + 1), a2 = __ldg(a + 2), a3 = __ldg(a + 3), a4 = __ldg(a + 4);
+            v = make_uint4(__funnelshift_r(a0, a1, 8 * sh), __funnelshift_r(a1, a2, 8 * sh),
+                           __funnelshift_r(a2, a3, 8 * sh), __funnelshift_r(a3, a4, 8 * sh));
+        } else {
+            unsigned wv[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const short* h = hs + (2 * y) * PD_OW + c0 + q;
-                const int v = (h[0] + h[4 * PD_OW] + 4 * (h[PD_OW] + h[3 * PD_OW]) + 6 * h[2 * PD_OW] + 128) >> 8;
-                out |= (unsigned)v << (8 * q);
+                const int wx = gx + 4 * q;
+                if (wx >= 4 && wx + 8 <= j.sw) {   // the unaligned word load touches the aligned words around it
+                    wv[q] = ld_word_any(row + wx);
+                } else {
+                    unsigned t = 0;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) t |= (unsigned)__ldg(row + reflect101(wx + e, j.sw)) << (8 * e);
+                    wv[q] = t;
+                }
             }
-            const int ox = X0 + c0;
-            uint8_t* o = dst + (long long)oy * j.dpitch + ox;
-            if (ox + 3 < j.dw && (j.dpitch & 3) == 0 && (((size_t)dst) & 3) == 0) {
-                *reinterpret_cast<unsigned*>(o) = out;
+            v = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        }
+        reinterpret_cast<uint4*>(tile)[i] = v;
+    }
+    __syncthreads();
+    if (j.copy[cam]) {   // source rows 2*Y0 .. 2*Y0+31, columns 2*X0 .. 2*X0+255 = tile rows 2.., columns 16..
+        uint8_t* cp = j.copy[cam] + (long long)seq * j.copy_seq_stride;
+        const bool cal16 = (((size_t)cp) & 15) == 0 && (j.cpitch & 15) == 0;
+        for (int i = tid; i < 2 * PD_OH * (2 * PD_OW / 16); i += PD_THREADS) {
+            const int r = i >> 4, k = i & 15;
+            const int gy = 2 * Y0 + r, gx = 2 * X0 + 16 * k;
+            if (gy >= j.sh || gx >= j.sw) continue;
+            const uint4 v = *reinterpret_cast<const uint4*>(tile + (r + 2) * PD_TW + 16 + 16 * k);
+            uint8_t* o = cp + (long long)gy * j.cpitch + gx;
+            if (cal16 && gx + 16 <= j.cpitch) {   // whole chunks: the copy plane's pitch is a multiple of 128
+                *reinterpret_cast<uint4*>(o) = v;
             } else {
-                for (int q = 0; q < 4; ++q)
-                    if (ox + q < j.dw) o[q] = (uint8_t)(out >> (8 * q));
+                const unsigned wv[4] = {v.x, v.y, v.z, v.w};
+                for (int e = 0; e < 16; ++e)
+                    if (gx + e < j.sw) o[e] = (uint8_t)(wv[e >> 2] >> (8 * (e & 3)));
             }
+        }
+    }
+    // ---- a thread: output columns X0 + 4c .. + 3, output rows Y0 + 4g .. + 3 <- tile rows 8g .. 8g + 10,
+    // window bytes b[-4 .. 11] around image column 2 * (X0 + 4c) = tile column 16 + 8c
+    const int c = tid & 31, g = tid >> 5;
+    unsigned hA[2 * PD_ROWS_PER_THREAD + 3], hB[2 * PD_ROWS_PER_THREAD + 3];
+#pragma unroll
+    for (int r = 0; r < 2 * PD_ROWS_PER_THREAD + 3; ++r) {
+        const uint8_t* t = tile + (2 * PD_ROWS_PER_THREAD * g + r) * PD_TW + 16 + 8 * c;
+        const unsigned w0 = *reinterpret_cast<const unsigned*>(t - 4);
+        const uint2 w12 = *reinterpret_cast<const uint2*>(t);
+        const unsigned w3 = *reinterpret_cast<const unsigned*>(t + 8);
+        pd_row_sums(w0, w12.x, w12.y, w3, hA[r], hB[r]);
+    }
+    const int ox = X0 + 4 * c;
+    const bool wordok = ox + 3 < j.dw && (j.dpitch & 3) == 0 && (((size_t)dst) & 3) == 0;
+#pragma unroll
+    for (int y = 0; y < PD_ROWS_PER_THREAD; ++y) {
+        const int oy = Y0 + PD_ROWS_PER_THREAD * g + y;
+        if (oy >= j.dh || ox >= j.dw) continue;
+        const unsigned vA = (hA[2 * y] + hA[2 * y + 4] + 0x00800080u) + (hA[2 * y + 1] + hA[2 * y + 3]) * 4u + hA[2 * y + 2] * 6u;
+        const unsigned vB = (hB[2 * y] + hB[2 * y + 4] + 0x00800080u) + (hB[2 * y + 1] + hB[2 * y + 3]) * 4u + hB[2 * y + 2] * 6u;
+        const unsigned out = __byte_perm(vA, vB, 0x7531u);   // (v >> 8) of the four halves
+        uint8_t* o = dst + (long long)oy * j.dpitch + ox;
+        if (wordok) {
+            *reinterpret_cast<unsigned*>(o) = out;
+        } else {
+            for (int q = 0; q < 4; ++q)
+                if (ox + q < j.dw) o[q] = (uint8_t)(out >> (8 * q));
         }
     }
 }
 static void launch_pyrdown_job(const PyrDownJob& j, int n_img, cudaStream_t st) {
-    dim3 grid((j.dw + PD_OW - 1) / PD_OW, (j.dh + PD_OH - 1) / PD_OH, n_img);
-    pyrdown_tile_kernel<<<grid, PD_THREADS, 0, st>>>(j);
+    const int gx = (j.dw + PD_OW - 1) / PD_OW;
+    const auto blocks = [&](int rpt) { return (long long)gx * ((j.dh + 4 * rpt - 1) / (4 * rpt)) * n_img; };
+    const long long enough = 4 * 148;   // a few blocks per SM
+    if (blocks(4) >= enough) {
+        pyrdown_tile_kernel<4><<<dim3(gx, (j.dh + 15) / 16, n_img), PD_THREADS, 0, st>>>(j);
+    } else if (blocks(2) >= enough) {
+        pyrdown_tile_kernel<2><<<dim3(gx, (j.dh + 7) / 8, n_img), PD_THREADS, 0, st>>>(j);
+    } else {
+        pyrdown_tile_kernel<1><<<dim3(gx, (j.dh + 3) / 4, n_img), PD_THREADS, 0, st>>>(j);
+    }
 }
 void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch, uint8_t* dst,
                     long long dst_stride, int dw, int dh, int dpitch, int n_img, cudaStream_t st) {
@@ -551,10 +651,16 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
     }
     unsigned long long* keysA = d.fastkeys + ((long long)(slot * 2 + 0) * d.n_seq) * bg.nb;
     unsigned long long* keysB = d.fastkeys + ((long long)(slot * 2 + 1) * d.n_seq) * bg.nb;
-    // FAST on the left level 0 of the slot (the pitch-aligned copy)
-    launch_fast(d.pyr + pg.base(0, slot, 0) + pg.off[0], ctx_seq_stride, pc.width, pc.height,
-                pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, keysA, keysB, bg, st);
-    return launches + 1;
+    // FAST on the left level 0 of the slot (the pitch-aligned copy): the thr_hi winners of every bucket, then the
+    // thr_lo winners -- a pass whose blocks return at once unless fewer than pre_matching_threshold buckets
+    // have a thr_hi winner (the only case in which bucket_merge_kernel can take the retry and read keysB)
+    int* nA = d.fast_nA + (long long)slot * d.n_seq;
+    const uint8_t* l0 = d.pyr + pg.base(0, slot, 0) + pg.off[0];
+    launch_fast(l0, ctx_seq_stride, pc.width, pc.height, pg.pitch[0], d.n_seq, pc.thr_hi, pc.thr_hi, nullptr, 0, 0,
+                keysA, nullptr, bg, st, nA, nullptr, 0);
+    launch_fast(l0, ctx_seq_stride, pc.width, pc.height, pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0,
+                nullptr, keysB, bg, st, nullptr, nA, pc.pre_matching_threshold);
+    return launches + 2;
 }
 
 // ============================================================================
@@ -1172,6 +1278,7 @@ __global__ void __launch_bounds__(SEL_T) select_kernel(DevArrays d, PyrGeom pg, 
             kA[i] = 0ull;
             kB[i] = 0ull;
         }
+        if (blockIdx.x == 0 && tid == 0) d.fast_nA[(long long)keybuf * d.n_seq + seq] = 0;
     }
     if (n == 0) {
         // circularMatching returns before lastLeft/RightPyramid are replaced (vo.cpp:179-181): keep the old
