@@ -441,23 +441,66 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
     uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
     const int X0 = blockIdx.x * PD_OW, Y0 = blockIdx.y * PD_OH, tid = threadIdx.x;
     const int sx0 = 2 * X0 - 16, sy0 = 2 * Y0 - 2;   // image position of tile[0][0]
-    // ---- tile load, 16 bytes per task: one 128-bit load where the chunk lies inside the row and is aligned,
-    // else word by word (inside the row) or byte by byte with the reflected column (the image's edge chunks)
+    // ---- tile load, 16 bytes per task.  Chunks that lie inside their image row ("inner") are fetched by every
+    // thread unconditionally (addresses of the other chunks are clamped, their data dropped), so all loads of a
+    // thread are in flight before the first shared-memory store: one 128-bit load per chunk where the rows are
+    // 16-byte aligned, else the five aligned words around the chunk + funnel shifts.  The at most two chunks per
+    // side that touch the image's left / right edge are then filled word by word / byte by byte with the reflected
+    // column by a second, dense sweep; chunks beyond column sw + 1 only feed outputs >= dw and are not loaded.
+    constexpr int NCH = PD_TW / 16, NT = PD_TH * NCH, NIT = (NT + PD_THREADS - 1) / PD_THREADS;
     const bool al16 = (((size_t)src) & 15) == 0 && (j.spitch & 15) == 0;
-    for (int i = tid; i < PD_TH * (PD_TW / 16); i += PD_THREADS) {
-        const int r = i / (PD_TW / 16), k = i - r * (PD_TW / 16);
-        const int gx = sx0 + 16 * k;
-        const uint8_t* row = src + (long long)reflect101(sy0 + r, j.sh) * j.spitch;
-        uint4 v;
-        if (al16 && gx >= 0 && gx + 16 <= j.sw) {
-            v = __ldg(reinterpret_cast<const uint4*>(row + gx));
-        } else if (gx >= 4 && gx + 20 <= j.sw) {   // unaligned rows: the five aligned words around the chunk
-            const unsigned sh = (unsigned)((size_t)(row + gx) & 3);
-            const unsigned* a = reinterpret_cast<const unsigned*>(row + gx - sh);
-            const unsigned a0 = __ldg(a), a1 = __ldg(a + 1), a2 = __ldg(a + 2), a3 = __ldg(a + 3), a4 = __ldg(a + 4);
-            v = make_uint4(__funnelshift_r(a0, a1, 8 * sh), __funnelshift_r(a1, a2, 8 * sh),
-                           __funnelshift_r(a2, a3, 8 * sh), __funnelshift_r(a3, a4, 8 * sh));
+    const int lo = al16 ? 0 : 4, lim = al16 ? 16 : 20;   // inner chunk: lo <= gx && gx + lim <= sw
+    if (j.sw >= lo + lim) {
+        const int gx_hi = al16 ? ((j.sw - 16) & ~15) : (j.sw - 20);
+        if (al16) {
+            uint4 v[NIT];
+#pragma unroll
+            for (int it = 0; it < NIT; ++it) {
+                const int i = min(tid + it * PD_THREADS, NT - 1);
+                const int r = i / NCH, k = i - r * NCH;
+                const int gx = min(max(sx0 + 16 * k, 0), gx_hi);
+                v[it] = __ldg(reinterpret_cast<const uint4*>(src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + gx));
+            }
+#pragma unroll
+            for (int it = 0; it < NIT; ++it) {
+                const int i = tid + it * PD_THREADS;
+                const int gx = sx0 + 16 * (i % NCH);
+                if (i < NT && gx >= 0 && gx + 16 <= j.sw) reinterpret_cast<uint4*>(tile)[i] = v[it];
+            }
         } else {
+            unsigned a[NIT][5];
+#pragma unroll
+            for (int it = 0; it < NIT; ++it) {
+                const int i = min(tid + it * PD_THREADS, NT - 1);
+                const int r = i / NCH, k = i - r * NCH;
+                const int gx = min(max(sx0 + 16 * k, 4), gx_hi);
+                const uint8_t* p = src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + gx;
+                const unsigned* w = reinterpret_cast<const unsigned*>(p - ((size_t)p & 3));
+#pragma unroll
+                for (int q = 0; q < 5; ++q) a[it][q] = __ldg(w + q);
+            }
+#pragma unroll
+            for (int it = 0; it < NIT; ++it) {
+                const int i = tid + it * PD_THREADS;
+                const int r = min(i, NT - 1) / NCH, gx = sx0 + 16 * (i % NCH);
+                // rows differ in alignment when the pitch is odd: the shift is the chunk's own
+                const unsigned sh = 8u * (unsigned)((size_t)(src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + gx) & 3);
+                if (i < NT && gx >= 4 && gx + 20 <= j.sw)
+                    reinterpret_cast<uint4*>(tile)[i] =
+                        make_uint4(__funnelshift_r(a[it][0], a[it][1], sh), __funnelshift_r(a[it][1], a[it][2], sh),
+                                   __funnelshift_r(a[it][2], a[it][3], sh), __funnelshift_r(a[it][3], a[it][4], sh));
+            }
+        }
+    }
+    {
+        const int rem = j.sw - lim - sx0;
+        const int kr = (j.sw >= lo + lim && rem >= 0) ? (rem >> 4) + 1 : 0;   // first chunk right of the inner ones
+        for (int i = tid; i < PD_TH * 4; i += PD_THREADS) {
+            const int r = i >> 2, e = i & 3;
+            const int k = e < 2 ? e : kr + (e - 2);
+            const int gx = sx0 + 16 * k;
+            if (k >= NCH || gx > j.sw + 1 || (j.sw >= lo + lim && gx >= lo && gx + lim <= j.sw)) continue;   // none / unused / inner
+            const uint8_t* row = src + (long long)reflect101(sy0 + r, j.sh) * j.spitch;
             unsigned wv[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -467,13 +510,12 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
                 } else {
                     unsigned t = 0;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) t |= (unsigned)__ldg(row + reflect101(wx + e, j.sw)) << (8 * e);
+                    for (int b = 0; b < 4; ++b) t |= (unsigned)__ldg(row + reflect101(wx + b, j.sw)) << (8 * b);
                     wv[q] = t;
                 }
             }
-            v = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+            reinterpret_cast<uint4*>(tile)[r * NCH + k] = make_uint4(wv[0], wv[1], wv[2], wv[3]);
         }
-        reinterpret_cast<uint4*>(tile)[i] = v;
     }
     __syncthreads();
     if (j.copy[cam]) {   // source rows 2*Y0 .. 2*Y0+31, columns 2*X0 .. 2*X0+255 = tile rows 2.., columns 16..
