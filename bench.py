@@ -35,7 +35,7 @@ FRAMES_PER_STEP = 400
 E2E_DEPTH = 3
 # dram__bytes_read.sum + dram__bytes_write.sum of the ingest kernels per stereo frame in the 64-frame launch
 # (ncu --set full, profiles/r01_ncu_summary.md): mostly reads, the written planes stay in the 126 MB L2
-NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 168.3e6 / 64
+NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 158.97e6 / 64   # profiles/r01_ncu_summary.md (v12 capture)
 REF_FRAMES_PER_STEP = 8
 METRIC = "stereo frames/s at KITTI 1241x376"
 
@@ -395,20 +395,20 @@ def run_gpu(args, rank, world, local_rank):
         # (profiles/r01_ncu_summary.md), per launch set like `achieved`; the kernels are issue bound, not HBM bound.
         ing = stages["ingest_fast_pyramid"]
         ach1 = B_ALG_FRAME / (ing["us_per_frame"] * 1e-6) / 1e9
-        roofline_single = {"bound": "hbm", "kernel": "ingest, 1 frame per launch (4 launches)", "achieved": ach1,
+        roofline_single = {"bound": "hbm", "kernel": "ingest, 1 frame per launch (5 launches)", "achieved": ach1,
                            "peak": peak, "unit": "GB/s", "frac": ach1 / peak, "us_per_launch_set": ing["us_per_frame"],
                            "algorithmic_bytes_per_launch_set": B_ALG_FRAME}
         if batch and "ingest_GBps" in batch:
             nfl = batch["sequences_per_launch"]
             roofline = {"bound": "hbm",
-                        "kernel": "ingest: pyrdown_tile_kernel x3 (level-0 copy fused) + fast_kernel, %d frames per launch" % nfl,
+                        "kernel": "ingest: pyrdown_tile_kernel x3 (level-0 copy fused) + fast_kernel x2 (thr-20 pass, gated low-threshold pass), %d frames per launch" % nfl,
                         "achieved": batch["ingest_GBps"], "peak": peak, "unit": "GB/s",
                         "frac": batch["ingest_GBps"] / peak, "traffic": (NCU_INGEST_TRAFFIC_BYTES_PER_FRAME * nfl) if NCU_INGEST_TRAFFIC_BYTES_PER_FRAME else None,
                         "traffic_source": "ncu --set full capture of the same launches (profiles/r01_ncu_summary.md)",
                         "peak_source": peak_src, "frames_per_launch": nfl,
                         "algorithmic_bytes_per_launch_set": B_ALG_FRAME * nfl,
                         "us_per_launch_set": batch["ingest_us_per_launch"],
-                        "limiter": "SM issue (FAST arc scoring ~60% issue-slot utilisation), not HBM: see profiles/"}
+                        "limiter": "SM issue (FAST 55 %, pyrDown 59-69 % issue-slot utilisation), not HBM: see profiles/"}
         else:
             roofline = dict(roofline_single, traffic=None, peak_source=peak_src)
         roofline_batch = roofline_single   # kept under the old key for continuity: the 1-frame figure
