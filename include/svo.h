@@ -61,7 +61,7 @@ typedef struct svo_params {
     float ransac_confidence;      /* .98  vo.cpp:295 (kept for the record)       */
     double max_translation_norm;  /* .1   vo.h MAX_TRANSLATION_NORM              */
     double max_rotation_norm;     /* .5   vo.h MAX_ROTATION_NORM                 */
-    uint64_t ransac_seed;         /* seed of the hypothesis sample stream        */
+    uint64_t ransac_seed;         /* reserved (ABI layout): the sample stream is OpenCV's fixed RNG((uint64)-1) replayed */
     int device;                   /* CUDA device ordinal                         */
     int channels;                 /* 1 = 8UC1 (default); 3 = interleaved 8UC3 exactly as the reference CLI feeds
                                      cv::imread's BGR images (src/main.cpp:37-46): FAST scans the first `width`
@@ -151,6 +151,11 @@ int svo_get_result(svo_ctx* ctx, int seq, svo_frame_result* out);
  *   which = 3: feature set after the frame (x,y / age / strength)              */
 int svo_get_tap(svo_ctx* ctx, int seq, int which, int cap, float* f_out, int* i_out,
                 uint8_t* u8_out);
+/* The images the NEXT frame will be matched against (level 0 of the cached t0 pyramids of sequence `seq`,
+ * lastLeftPyramid / lastRightPyramid of vo.h:257-258, including the "kept after an empty frame" case of
+ * vo.cpp:179-181), copied to host buffers of `stride` bytes per row (>= width * channels).  Synchronises.
+ * Lets a wrapper serve VisualOdometry::circularMatching (vo.h:374-379) without keeping host copies per frame. */
+int svo_get_frame_images(svo_ctx* ctx, int seq, uint8_t* left_out, uint8_t* right_out, int stride);
 /* The CUDA stream the context launches on (cudaStream_t as void*). */
 void* svo_stream(svo_ctx* ctx);
 /* Number of kernel launches issued by the context so far. */

@@ -279,12 +279,21 @@ class VisualOdometry {
     int frame_id = 0;
     cv::Mat pendingLeft_, pendingRight_;     /* last submitted frame (streaming calls) */
     svo_ctx* ctx_ = nullptr;                 /* device-resident state (pyramids, currentVOFeatures, R|t, last_transform) */
-    cv::Mat imageRightT0_, imageLeftT0_;     /* host copies kept only for the stateless public circularMatching() */
+    cv::Mat imageRightT0_, imageLeftT0_;     /* t0 images for the public circularMatching(): fetched from the device on demand */
+    bool t0_fetched_ = false;
+    int cols_ = 0, rows_ = 0, type_ = 0;     /* geometry the context was created for */
     cv::Mat_<float64> last_transform = cv::Mat_<float64>::eye(4, 4);
     std::ofstream vo_log;
 
     void ensure_ctx(const cv::Mat& img) {
-        if (ctx_) return;
+        if (ctx_) {   /* the reference would hit an OpenCV size / type assertion; never read past a smaller buffer */
+            if (img.cols != cols_ || img.rows != rows_ || img.type() != type_)
+                throw std::runtime_error("svo: image size or type differs from the first frame of this VisualOdometry");
+            return;
+        }
+        cols_ = img.cols;
+        rows_ = img.rows;
+        type_ = img.type();
         svo_params p = detail::params_for(img);
         ctx_ = svo_create(&p);
         if (!ctx_) throw std::runtime_error(std::string("svo_create: ") + svo_last_error());
@@ -346,8 +355,7 @@ class VisualOdometry {
         }
         cv::Mat_<float64> T(4, 4);
         const int ok = detail::check(svo_process_frame(ctx_, L, R, sl, T.ptr<double>(0)));
-        image_left.copyTo(imageLeftT0_);     /* vo.cpp:74-75 */
-        image_right.copyTo(imageRightT0_);
+        t0_fetched_ = false;   /* vo.cpp:74-75: the t0 images live in the context's pyramid ring; no host copies per frame */
         ++frame_id;
         if (ok) last_transform = T;
         return std::make_pair(ok != 0, T);
@@ -380,9 +388,10 @@ class VisualOdometry {
         std::memcpy(T.ptr<double>(0), r.transform, sizeof(double) * 16);
         ++frame_id;
         if (r.success) last_transform = T;
-        if (svo_pending(ctx_) == 0) {
-            pendingLeft_.copyTo(imageLeftT0_);
-            pendingRight_.copyTo(imageRightT0_);
+        t0_fetched_ = false;
+        if (svo_pending(ctx_) == 0) {   /* nothing in flight any more: drop the references to the caller's buffers */
+            pendingLeft_ = cv::Mat();
+            pendingRight_ = cv::Mat();
         }
         return std::make_pair(r.success != 0, T);
     }
@@ -428,7 +437,14 @@ class VisualOdometry {
                           std::vector<cv::Point2f>& pointsRightT0, std::vector<cv::Point2f>& pointsLeftT1,
                           std::vector<cv::Point2f>& pointsRightT1, FeatureSet& current_features) {
         if (pointsLeftT0.size() == 0) return;   /* vo.cpp:179-181 */
-        if (imageLeftT0_.empty()) throw std::runtime_error("svo: circularMatching needs a prior stereo_callback");
+        if (!ctx_ || frame_id == 0) throw std::runtime_error("svo: circularMatching needs a prior stereo_callback");
+        if (svo_pending(ctx_) != 0) throw std::runtime_error("svo: collect the submitted frames before circularMatching");
+        if (!t0_fetched_) {   /* the images of the cached t0 pyramids (vo.h:257-258), once per frame at most */
+            imageLeftT0_ = cv::Mat(rows_, cols_, type_);
+            imageRightT0_ = cv::Mat(rows_, cols_, type_);
+            detail::check(svo_get_frame_images(ctx_, 0, imageLeftT0_.data, imageRightT0_.data, (int)imageLeftT0_.step));
+            t0_fetched_ = true;
+        }
         int s0, s1, s2, s3;
         const uint8_t *a = detail::gray(imageLeftT0_, s0), *b = detail::gray(imageRightT0_, s1),
                       *c = detail::gray(imgLeftT1, s2), *d = detail::gray(imgRightT1, s3);

@@ -53,7 +53,7 @@ SYMBOLS = [
     "svo_version", "svo_last_error", "svo_device_count", "svo_default_params", "svo_create",
     "svo_destroy", "svo_set_projection", "svo_process_frame", "svo_process_frame_batch",
     "svo_process_frame_batch_dev", "svo_submit_frame", "svo_submit_frame_batch", "svo_collect", "svo_pending", "svo_stream_join", "svo_pipeline_info",
-    "svo_synchronize", "svo_get_result", "svo_get_tap", "svo_stream",
+    "svo_synchronize", "svo_get_result", "svo_get_tap", "svo_get_frame_images", "svo_stream",
     "svo_launch_count", "svo_enable_timers", "svo_get_stage_time", "svo_reset_timers",
     "svo_fast_detect", "svo_bucket_filter", "svo_build_pyramid", "svo_lk_track",
     "svo_circular_match", "svo_matching_features", "svo_find_close_points", "svo_compact",
@@ -103,6 +103,7 @@ def lib():
     L.svo_synchronize.argtypes = [vp]
     L.svo_get_result.argtypes = [vp, C.c_int, C.POINTER(FrameResult)]
     L.svo_get_tap.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, ip, u8p]
+    L.svo_get_frame_images.argtypes = [vp, C.c_int, u8p, u8p, C.c_int]
     L.svo_stream.argtypes = [vp]
     L.svo_stream.restype = vp
     L.svo_launch_count.argtypes = [vp]

@@ -167,13 +167,14 @@ inline cv::Mat read_image(const std::string& path, std::string* why = nullptr) {
     return out;
 }
 
-// cv::cvtColor(BGR2GRAY) for 8-bit: fixed point, 14 fractional bits, coefficients 1868 / 9617 / 4899 (B, G, R)
+// cv::cvtColor(BGR2GRAY) for 8-bit as OpenCV 4.x computes it: fixed point with 15 fractional bits, coefficients
+// 3735 / 19235 / 9798 (B, G, R), round to nearest (tests/test_cli.py compares with cv2.cvtColor)
 inline cv::Mat bgr_to_gray(const cv::Mat& bgr) {
     cv::Mat g(bgr.rows, bgr.cols, CV_8UC1);
     for (int y = 0; y < bgr.rows; ++y) {
         const uint8_t* p = bgr.ptr<uint8_t>(y);
         uint8_t* d = g.ptr<uint8_t>(y);
-        for (int x = 0; x < bgr.cols; ++x) d[x] = (uint8_t)((p[3 * x] * 1868 + p[3 * x + 1] * 9617 + p[3 * x + 2] * 4899 + (1 << 13)) >> 14);
+        for (int x = 0; x < bgr.cols; ++x) d[x] = (uint8_t)((p[3 * x] * 3735 + p[3 * x + 1] * 19235 + p[3 * x + 2] * 9798 + (1 << 14)) >> 15);
     }
     return g;
 }

@@ -134,6 +134,15 @@ int main(int argc, char** argv) {
                     o.write(rgb, 3);
                 }
             return 0;
+        } else if (a == "--dump-gray" && i + 2 < argc) {   // --gray conversion check: image file -> binary PGM
+            std::string why;
+            const cv::Mat m = svo_cli::read_image(argv[i + 1], &why);
+            if (m.empty()) { std::cerr << why << std::endl; return 2; }
+            const cv::Mat g = svo_cli::bgr_to_gray(m);
+            std::ofstream o(argv[i + 2], std::ios::binary);
+            o << "P5\n" << g.cols << " " << g.rows << "\n255\n";
+            for (int y = 0; y < g.rows; ++y) o.write((const char*)g.ptr<uint8_t>(y), g.cols);
+            return 0;
         } else if (a == "-h" || a == "--help") {
             std::cout << "usage: vo N folder [--gray] [--calib file.yaml] [--pose0 pitch26|identity] [--out file.csv] [--stream]\n";
             return 0;

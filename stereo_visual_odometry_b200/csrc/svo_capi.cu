@@ -80,7 +80,7 @@ extern "C" void svo_default_params(svo_params* p, int width, int height) {
     p->ransac_confidence = 0.98f;
     p->max_translation_norm = 0.1;
     p->max_rotation_norm = 0.5;
-    p->ransac_seed = 0x5eed5eedULL;
+    p->ransac_seed = 0;   /* unused: the sample stream is OpenCV's fixed RNG((uint64)-1) */
     p->device = 0;
     p->channels = 1;
 }
@@ -381,7 +381,6 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     pc.reproj_thr_sq = (float)((double)p->ransac_reproj_error * (double)p->ransac_reproj_error);
     pc.max_t_norm = p->max_translation_norm;
     pc.max_r_norm = p->max_rotation_norm;
-    pc.seed = p->ransac_seed;
     pc.ransac_iterations = p->ransac_iterations;
     pc.ransac_confidence = (double)p->ransac_confidence;
     pc.lk = make_lk_config(*p, c->pg.nlevels);
@@ -671,6 +670,10 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         // as image f is there (typically a frame ahead), T(f) the moment every bucketed feature of f - 1 has its keep bit
         const int half = c->klt_blocks_k > 1 ? (int)((long long)c->klt_blocks_k * c->f_share / 100) : 1;
         cudaStream_t sK2 = c->stream_k2;
+        // both passes read pyramid slot / FAST keys of frame f - 1 too: ingest(f - 1) normally precedes ingest(f) on
+        // the ingest stream, but not when frame f - 1 was a serial frame on stream_full (first submit after a drain)
+        CU(cudaStreamWaitEvent(sK, c->ev_in[e1], 0));
+        CU(cudaStreamWaitEvent(sK2, c->ev_in[e1], 0));
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
         {
             TraceScope ts(c, "spec_fast", 1, sK);
@@ -733,7 +736,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
             TraceScope ts(c, "final_a", 3, sP);
             launch_pnp_final_a(c->d, c->pc, sP);
         }
-        c->launches += 6;
+        c->launches += 7;
     }
     if (!tm) {
         CU(cudaEventRecord(c->ev_fa[e], sP));
@@ -764,7 +767,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (c->timers) {
         CU(cudaStreamSynchronize(sP));
         const int nst = first ? 1 : 6;
-        const int nl[6] = {n_ingest, 1, 1, 1, 1, 2};
+        const int nl[6] = {n_ingest, 1, 1, 1, 2, 2};
         for (int i = 0; i < nst; ++i) {
             float ms = 0.f;
             cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]);
@@ -875,6 +878,23 @@ extern "C" int svo_synchronize(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     CU(cudaSetDevice(c->p.device));
     for (cudaStream_t st : {c->stream_in, c->stream_k, c->stream_k2, c->stream, c->stream_fb, c->stream_full}) CU(cudaStreamSynchronize(st));
+    return SVO_OK;
+}
+
+extern "C" int svo_get_frame_images(svo_ctx* c, int seq, uint8_t* left_out, uint8_t* right_out, int stride) {
+    if (!c || !left_out || !right_out) return fail(SVO_ERR_INVALID, "NULL argument");
+    if (seq < 0 || seq >= c->d.n_seq) return fail(SVO_ERR_INVALID, "bad sequence index");
+    const int row_bytes = c->p.width * c->pg.cn;
+    if (stride < row_bytes) return fail(SVO_ERR_INVALID, "stride < width * channels");
+    if (c->frames == 0) return fail(SVO_ERR_STATE, "no frame has been processed yet");
+    CU(cudaSetDevice(c->p.device));
+    int rc = svo_synchronize(c);
+    if (rc != SVO_OK) return rc;
+    const int slot = (int)((c->frames - 1) % SVO_PYR_SLOTS);
+    CU(cudaMemcpy2D(left_out, stride, c->d.pyr + c->pg.base(seq, slot, 0) + c->pg.off[0], c->pg.pitch[0], row_bytes,
+                    c->p.height, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy2D(right_out, stride, c->d.pyr + c->pg.base(seq, slot, 1) + c->pg.off[0], c->pg.pitch[0], row_bytes,
+                    c->p.height, cudaMemcpyDeviceToHost));
     return SVO_OK;
 }
 
@@ -1175,6 +1195,10 @@ static int run_matching(const svo_params* p, const uint8_t* L0, const uint8_t* R
     svo_params q = *p;
     q.n_seq = 1;
     q.features_per_bucket = 1;
+    // select_kernel / bucket_merge_kernel pack counts into 16-bit halves: the same bounds svo_create enforces
+    if (n_in > 32767 || fs_cap > 32767) return fail(SVO_ERR_INVALID, "at most 32767 features per call");
+    if ((long long)q.buckets_along_height * q.buckets_along_width > 16384)
+        return fail(SVO_ERR_INVALID, "at most 16384 buckets (reference: 92 x 160 = 14720)");
     svo_ctx* c = ctx_create(&q, n_in > fs_cap ? n_in : fs_cap, false);
     if (!c) return SVO_ERR_CUDA;
     struct Guard {

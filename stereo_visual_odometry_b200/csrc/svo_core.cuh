@@ -1071,6 +1071,22 @@ SVO_HD int ransac_update_num_iters(double p, double ep, int model_points, int ma
     return (int)lrint(num / denom);
 #endif
 }
+// The iteration budget of the sequential loop after it has looked at the first n_have counts (it stops earlier
+// when the budget drops below n_have): > n_have means the loop goes on to hypothesis n_have.
+SVO_HD int ransac_replay_budget(const int* counts, int n_have, int n_points, int max_iters, double confidence,
+                                int& best_count) {
+    int niters = max_iters < 1 ? 1 : max_iters;
+    int max_good = 0;
+    for (int k = 0; k < niters && k < n_have; ++k) {
+        const int c = counts[k];
+        if (c > (max_good > 4 ? max_good : 4)) {
+            max_good = c;
+            niters = ransac_update_num_iters(confidence, (double)(n_points - c) / n_points, 5, niters);
+        }
+    }
+    best_count = max_good;
+    return niters;
+}
 // Replays the sequential loop over per-hypothesis inlier counts: a model replaces the best
 // iff count > max(best, 4); the iteration budget shrinks adaptively.  Returns the index of
 // the winning hypothesis or -1.
@@ -1088,25 +1104,6 @@ SVO_HD int ransac_replay(const int* counts, int n_hyp, int n_points, int max_ite
     }
     best_count = max_good;
     return best;
-}
-
-// Counter-based RNG for hypothesis sampling (splitmix64).
-SVO_HD uint64_t splitmix64(uint64_t x) {
-    x += 0x9E3779B97F4A7C15ull;
-    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
-    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-    return x ^ (x >> 31);
-}
-// 5 distinct indices in [0, n), n >= 5
-SVO_HD void sample5(uint64_t seed, uint64_t stream, int n, int* idx) {
-    uint64_t ctr = 0;
-    for (int i = 0; i < 5;) {
-        const uint64_t r = splitmix64(seed ^ splitmix64(stream * 0x100000001B3ull + (ctr++)));
-        const int v = (int)((r >> 11) % (uint64_t)n);
-        bool dup = false;
-        for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
-        if (!dup) idx[i++] = v;
-    }
 }
 
 }  // namespace svo

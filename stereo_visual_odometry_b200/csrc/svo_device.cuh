@@ -123,7 +123,6 @@ struct PipeConfig {
     float circular_threshold;
     float reproj_thr_sq;         // (float)(8*8)
     double max_t_norm, max_r_norm;
-    uint64_t seed;
     int ransac_iterations;       // RANSAC_ITERATIONS (vo.h) = OpenCV's iteration cap
     double ransac_confidence;    // (double)(float)0.98 (vo.cpp:295)
     int check_bounds;            // in-bounds test of matchingFeatures (vo.cpp:341-359)

@@ -2,429 +2,436 @@
 //
 // cv::solvePnPRansac (called by the reference at src/vo.cpp:301-304) estimates every RANSAC
 // hypothesis with SOLVEPNP_EPNP on 5 points whatever `flags` says (flags = SOLVEPNP_ITERATIVE is
-// only used for the final refit on the inliers).  This restates OpenCV's calib3d epnp.cpp
-// (Lepetit/Moreno-Noguer/Fua): PCA control points, barycentric coordinates, the 12x12 M^T M
-// null space, the three beta approximations, 5 Gauss-Newton steps each, absolute orientation by
-// SVD, best reprojection error wins.  All FP64.
+// only used for the final refit on the inliers).  Five points leave M^T M (12 x 12) with a
+// two-dimensional exact null space, and EPnP's result depends on WHICH basis of it the SVD returns
+// and on the sign / order conventions of the PCA that places the control points.  OpenCV runs all
+// of its small SVDs (n < 25) through its own one-sided Jacobi (modules/core/src/lapack.cpp,
+// JacobiSVDImpl_), a deterministic sequential algorithm -- so this file restates that algorithm and
+// OpenCV's calib3d epnp.cpp OPERATION FOR OPERATION, in the same order and in plain IEEE double
+// arithmetic (the library is built with --fmad=false; the host test build has no FMA contraction
+// either).  The result is the same pose cv::solvePnP(SOLVEPNP_EPNP) returns, bit for bit in
+// tests/test_host_cores.py, including the samples whose null-space basis is decided by rounding.
+//
+// Lane cooperation (device: LANES = 32, one warp per hypothesis; host tests: LANES = 1): every lane
+// computes the sequential scalar chains redundantly (identical values in every lane), element-wise
+// updates are split over the lanes.  The arithmetic does not depend on LANES.
 #pragma once
 #include "svo_core.cuh"
 
+// phase timestamps for tools/epnp_bench.cu (compiled out everywhere else)
+#ifndef SVO_EPNP_TICK
+#define SVO_EPNP_TICK(k)
+#endif
+
 namespace svo {
 
-// Cyclic Jacobi eigen-decomposition of a symmetric N x N matrix (row-major, destroyed).
-// On return d[i] are the eigenvalues sorted in DESCENDING order and Vt row i is the matching
-// unit eigenvector (i.e. the layout of cvSVD(..., CV_SVD_U_T) on a symmetric PSD matrix).
-template <int N>
-SVO_HD void jacobi_eigen_sym(double* A, double* Vt, double* d) {
-    for (int i = 0; i < N; ++i)
-        for (int j = 0; j < N; ++j) Vt[i * N + j] = (i == j) ? 1.0 : 0.0;
-    for (int sweep = 0; sweep < 60; ++sweep) {
-        double off = 0.0, diag = 0.0;
-        for (int i = 0; i < N; ++i) {
-            diag += A[i * N + i] * A[i * N + i];
-            for (int j = i + 1; j < N; ++j) off += A[i * N + j] * A[i * N + j];
-        }
-        if (off <= 1e-30 * diag || off == 0.0) break;
-        for (int p = 0; p < N - 1; ++p)
-            for (int q = p + 1; q < N; ++q) {
-                const double apq = A[p * N + q];
-                if (apq == 0.0) continue;
-                const double app = A[p * N + p], aqq = A[q * N + q];
-                const double theta = (aqq - app) / (2.0 * apq);
-                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
-                for (int k = 0; k < N; ++k) {   // A <- A J
-                    const double akp = A[k * N + p], akq = A[k * N + q];
-                    A[k * N + p] = c * akp - s * akq;
-                    A[k * N + q] = s * akp + c * akq;
-                }
-                for (int k = 0; k < N; ++k) {   // A <- J^T A
-                    const double apk = A[p * N + k], aqk = A[q * N + k];
-                    A[p * N + k] = c * apk - s * aqk;
-                    A[q * N + k] = s * apk + c * aqk;
-                }
-                for (int k = 0; k < N; ++k) {   // rows of Vt are eigenvectors
-                    const double vp = Vt[p * N + k], vq = Vt[q * N + k];
-                    Vt[p * N + k] = c * vp - s * vq;
-                    Vt[q * N + k] = s * vp + c * vq;
-                }
-            }
-    }
-    for (int i = 0; i < N; ++i) d[i] = A[i * N + i];
-    for (int i = 0; i < N - 1; ++i) {   // selection sort, descending
-        int m = i;
-        for (int j = i + 1; j < N; ++j)
-            if (d[j] > d[m]) m = j;
-        if (m != i) {
-            const double td = d[i];
-            d[i] = d[m];
-            d[m] = td;
-            for (int k = 0; k < N; ++k) {
-                const double tv = Vt[i * N + k];
-                Vt[i * N + k] = Vt[m * N + k];
-                Vt[m * N + k] = tv;
-            }
-        }
-    }
-}
-
-// Least squares min ||A x - b|| for a ROWS x COLS system (row-major A, destroyed) by Householder QR.
-// Returns false if A is (numerically) rank deficient.
-template <int ROWS, int COLS>
-SVO_HD bool householder_ls(double* A, double* b, double* x) {
-#pragma unroll
-    for (int k = 0; k < COLS; ++k) {
-        double norm = 0.0;
-        for (int i = k; i < ROWS; ++i) norm += A[i * COLS + k] * A[i * COLS + k];
-        norm = sqrt(norm);
-        if (norm == 0.0) return false;
-        const double alpha = A[k * COLS + k] > 0 ? -norm : norm;
-        // v = a_k - alpha e_k
-        double v[ROWS];
-        for (int i = 0; i < ROWS; ++i) v[i] = (i >= k) ? A[i * COLS + k] : 0.0;
-        v[k] -= alpha;
-        double vtv = 0.0;
-        for (int i = k; i < ROWS; ++i) vtv += v[i] * v[i];
-        if (vtv == 0.0) return false;
-        for (int j = k; j < COLS; ++j) {
-            double dot = 0.0;
-            for (int i = k; i < ROWS; ++i) dot += v[i] * A[i * COLS + j];
-            const double f = 2.0 * dot / vtv;
-            for (int i = k; i < ROWS; ++i) A[i * COLS + j] -= f * v[i];
-        }
-        double dot = 0.0;
-        for (int i = k; i < ROWS; ++i) dot += v[i] * b[i];
-        const double f = 2.0 * dot / vtv;
-        for (int i = k; i < ROWS; ++i) b[i] -= f * v[i];
-    }
-    for (int k = COLS - 1; k >= 0; --k) {
-        double s = b[k];
-        for (int j = k + 1; j < COLS; ++j) s -= A[k * COLS + j] * x[j];
-        const double r = A[k * COLS + k];
-        if (fabs(r) < 1e-300) return false;
-        x[k] = s / r;
-    }
-    return true;
-}
-
-// SVD of a 3x3 matrix A = U diag(S) V^T by one-sided Jacobi.  U, V row-major.
-SVO_HD void svd3x3(const double* Ain, double* U, double* S, double* V) {
-    double A[9];
-    for (int i = 0; i < 9; ++i) {
-        A[i] = Ain[i];
-        V[i] = (i % 4 == 0) ? 1.0 : 0.0;
-    }
-    for (int sweep = 0; sweep < 60; ++sweep) {
-        bool changed = false;
-        for (int p = 0; p < 2; ++p)
-            for (int q = p + 1; q < 3; ++q) {
-                double a = 0, b = 0, c = 0;
-                for (int r = 0; r < 3; ++r) {
-                    a += A[r * 3 + p] * A[r * 3 + p];
-                    b += A[r * 3 + q] * A[r * 3 + q];
-                    c += A[r * 3 + p] * A[r * 3 + q];
-                }
-                if (fabs(c) <= DBL_EPSILON * sqrt(a * b)) continue;
-                changed = true;
-                const double zeta = (b - a) / (2.0 * c);
-                const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                const double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
-                for (int r = 0; r < 3; ++r) {
-                    const double ap = A[r * 3 + p], aq = A[r * 3 + q];
-                    A[r * 3 + p] = cs * ap - sn * aq;
-                    A[r * 3 + q] = sn * ap + cs * aq;
-                    const double vp = V[r * 3 + p], vq = V[r * 3 + q];
-                    V[r * 3 + p] = cs * vp - sn * vq;
-                    V[r * 3 + q] = sn * vp + cs * vq;
-                }
-            }
-        if (!changed) break;
-    }
-    for (int k = 0; k < 3; ++k) S[k] = sqrt(A[k] * A[k] + A[3 + k] * A[3 + k] + A[6 + k] * A[6 + k]);
-    // order columns by descending singular value
-    for (int i = 0; i < 2; ++i) {
-        int m = i;
-        for (int j = i + 1; j < 3; ++j)
-            if (S[j] > S[m]) m = j;
-        if (m != i) {
-            double ts = S[i]; S[i] = S[m]; S[m] = ts;
-            for (int r = 0; r < 3; ++r) {
-                double ta = A[r * 3 + i]; A[r * 3 + i] = A[r * 3 + m]; A[r * 3 + m] = ta;
-                double tv = V[r * 3 + i]; V[r * 3 + i] = V[r * 3 + m]; V[r * 3 + m] = tv;
-            }
-        }
-    }
-    for (int k = 0; k < 3; ++k) {
-        if (S[k] > 1e-12 * (S[0] > 0 ? S[0] : 1.0)) {
-            for (int r = 0; r < 3; ++r) U[r * 3 + k] = A[r * 3 + k] / S[k];
-        } else {   // complete the basis
-            const int a = (k + 1) % 3, b = (k + 2) % 3;
-            U[0 * 3 + k] = U[1 * 3 + a] * U[2 * 3 + b] - U[2 * 3 + a] * U[1 * 3 + b];
-            U[1 * 3 + k] = U[2 * 3 + a] * U[0 * 3 + b] - U[0 * 3 + a] * U[2 * 3 + b];
-            U[2 * 3 + k] = U[0 * 3 + a] * U[1 * 3 + b] - U[1 * 3 + a] * U[0 * 3 + b];
-        }
-    }
-}
-
-SVO_HD bool inv3x3(const double* m, double* o) {
-    const double c0 = m[4] * m[8] - m[5] * m[7], c1 = m[5] * m[6] - m[3] * m[8], c2 = m[3] * m[7] - m[4] * m[6];
-    const double det = m[0] * c0 + m[1] * c1 + m[2] * c2;
-    if (det == 0.0 || !(fabs(det) > 0.0)) return false;
-    const double id = 1.0 / det;
-    o[0] = c0 * id; o[1] = (m[2] * m[7] - m[1] * m[8]) * id; o[2] = (m[1] * m[5] - m[2] * m[4]) * id;
-    o[3] = c1 * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[2] * m[3] - m[0] * m[5]) * id;
-    o[6] = c2 * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
-    return true;
-}
-
 // ---------------------------------------------------------------------------
-// Cooperative EPnP for one 5-point sample: executed by LANES lanes (32 on the device: one warp per
-// RANSAC hypothesis; 1 in the host unit tests -- identical arithmetic, the lane loops are just serial).
-// `Red` provides sync() and sumd() (sum of a double across the lanes).
-struct EpnpWork {              // per-hypothesis scratch (shared memory on the device)
-    double A[144];             // M^T M, diagonalised in place
-    double Vt[144];            // rows = eigenvectors
-    double M[120];             // 10 x 12
-    double cs[12];             // (c, s) of the 6 concurrent rotations
-    unsigned char pq[136];     // round-robin pair table [11][6][2]
-    double dv[72];             // [4][6][3]
-    double L[60], rho[6];
-    double pws[15], us[10], alphas[20], cws[12];
-    double Rs[3][9], ts[3][3], errs[3];
-    int order[4];              // indices of the 4 smallest eigenvalues, ascending
-    int ok;
-};
+// OpenCV core restatements
+
+// cv::hypot<double> of lapack.cpp (NOT libm's hypot: different rounding)
+SVO_HD double cv_hypot(double a, double b) {
+    a = fabs(a);
+    b = fabs(b);
+    if (a > b) {
+        b /= a;
+        return a * sqrt(1 + b * b);
+    }
+    if (b > 0) {
+        a /= b;
+        return b * sqrt(1 + a * a);
+    }
+    return 0;
+}
 
 struct SerialRedD {
     static SVO_HD void sync() {}
+    static SVO_HD void sync_all() {}
     static SVO_HD double sumd(double v) { return v; }
 };
 
-// round-robin pairing of 12 indices: round r in [0, 11), slot k in [0, 6)
-SVO_HD void rr_pair(int r, int k, int& p, int& q) {
-    int a, b;
-    if (k == 0) { a = 11; b = r; }
-    else { a = (r + k) % 11; b = (r - k + 11) % 11; }
-    p = a < b ? a : b;
-    q = a < b ? b : a;
-}
-
-// Jacobi rotation zeroing a_pq of a symmetric matrix: one sqrt, one division, one rsqrt.
-SVO_HD void jacobi_cs(double app, double aqq, double apq, double& c, double& s) {
-    c = 1.0;
-    s = 0.0;
-    if (apq != 0.0) {
-        const double h = aqq - app;
-        const double r = sqrt(h * h + 4.0 * apq * apq);
-        const double t = (h >= 0 ? 2.0 : -2.0) * apq / (fabs(h) + r);
-#if defined(__CUDA_ARCH__)
-        c = rsqrt(t * t + 1.0);
-#else
-        c = 1.0 / sqrt(t * t + 1.0);
-#endif
-        s = t * c;
-    }
-}
-
-// Parallel-order (round-robin) Jacobi on the 12x12 symmetric matrix w.A: 11 rounds of 6 disjoint
-// rotations per sweep.  Per round: 6 lanes compute (c, s); then the 21 upper 2x2 blocks
-// A_blk <- J_i^T A_blk J_j are updated in place (each block is owned by one lane, the mirror
-// block is written too so the matrix stays exactly symmetric) together with the 6 x 12 row pairs of Vt.
-template <int LANES, class Red>
-SVO_HD void jacobi12_parallel(EpnpWork& w, int lane) {
-    for (int i = lane; i < 144; i += LANES) w.Vt[i] = (i / 12 == i % 12) ? 1.0 : 0.0;
-    for (int i = lane; i < 66; i += LANES) {
-        int p, q;
-        rr_pair(i / 6, i % 6, p, q);
-        w.pq[2 * i] = (unsigned char)p;
-        w.pq[2 * i + 1] = (unsigned char)q;
+// JacobiSVDImpl_<double> as cv::SVD::compute runs it for an m x n matrix (m = M >= n = N).
+//   At   N rows of length M: row i = column i of the input (OpenCV works on the transpose).  On return row i
+//        is the i-th LEFT singular vector (column i of U), singular values descending.
+//   Vt   N x N, row stride ldv, or nullptr (the V rotations never influence At / W): rows = right singular vectors
+//   W    N singular values (during the sweeps: the cached squared row norms, exactly OpenCV's W[])
+//   perm N ints of scratch
+// Every lane executes the sequential scalar work redundantly on identical data (a warp is then ONE sequential
+// machine without divergence; what bounds the time is the dependent FP64 chain, not the issue rate), keeps the two
+// active rows in registers and stores identical values, so a lane only ever reads what it has written itself;
+// the one hazard left -- a lane rewriting row j while another has not loaded it yet -- is closed by one warp
+// barrier per pair.  The V rotations and the final row operations are split over the lanes by column.
+// The skip test |p| <= eps sqrt(a b) is decided from p^2 against eps^2 a b and falls back to the literal
+// expression only within 1e-6 relative of the threshold, so the decisions are OpenCV's, without a square root
+// on the dependent path of every pair.
+template <int M, int N, int LANES, class Red>
+SVO_HD void cv_jacobi_svd(double* At, double* Vt, int ldv, double* W, int* perm, int lane) {
+    constexpr int n = N;
+    constexpr int UNROLL = N <= 3 ? N : 1;   // tiny systems: fully unrolled, everything in registers
+    (void)UNROLL;
+    const double eps = DBL_EPSILON * 10, minval = DBL_MIN, eps2 = eps * eps;
+    if (Vt)
+        for (int e = lane; e < n * n; e += LANES) Vt[(e / n) * ldv + (e % n)] = (e / n == e % n) ? 1.0 : 0.0;
+#pragma unroll UNROLL
+    for (int i = 0; i < n; ++i) {
+        double sd = 0;
+#pragma unroll
+        for (int k = 0; k < M; ++k) {
+            const double t = At[i * M + k];
+            sd += t * t;
+        }
+        W[i] = sd;
     }
     Red::sync();
-    constexpr int NB = (21 + LANES - 1) / LANES;   // blocks per lane
-    constexpr int NV = (72 + LANES - 1) / LANES;   // Vt items per lane
-    // block l -> (ki <= kj) in row-major upper-triangular order, decoded once (packed ki | kj << 4)
-    unsigned char blk[NB];
+    const int max_iter = M > 30 ? M : 30;
+    for (int iter = 0; iter < max_iter; ++iter) {
+        bool changed = false;
+#pragma unroll UNROLL
+        for (int i = 0; i < n - 1; ++i) {
+            double ai[M];
 #pragma unroll
-    for (int bi = 0; bi < NB; ++bi) {
-        int ki = 0, rem = lane + bi * LANES;
-        while (ki < 5 && rem >= 6 - ki) { rem -= 6 - ki; ++ki; }
-        blk[bi] = (unsigned char)(ki | ((ki + rem) << 4));
-    }
-    for (int sweep = 0; sweep < 30; ++sweep) {
-        double off = 0.0, diag = 0.0;
-        for (int i = lane; i < 144; i += LANES) {
-            const double v = w.A[i] * w.A[i];
-            if (i / 12 == i % 12) diag += v; else off += v;
+            for (int k = 0; k < M; ++k) ai[k] = At[i * M + k];
+            double wi = W[i];
+            bool dirty = false;
+#pragma unroll UNROLL
+            for (int j = i + 1; j < n; ++j) {
+                double aj[M];
+#pragma unroll
+                for (int k = 0; k < M; ++k) aj[k] = At[j * M + k];
+                const double wj = W[j];
+                Red::sync();   // every lane holds row j before any lane rewrites it
+                double p = 0;
+#pragma unroll
+                for (int k = 0; k < M; ++k) p += ai[k] * aj[k];
+                const double lhs = p * p, rhs = eps2 * (wi * wj);
+                bool skip;
+                if (lhs > rhs * 1.000001 && rhs > 1e-280) skip = false;
+                else if (lhs < rhs * 0.999999 && lhs > 1e-280) skip = true;
+                else skip = fabs(p) <= eps * sqrt(wi * wj);
+                if (skip) continue;
+                p *= 2;
+                const double beta = wi - wj, gamma = cv_hypot(p, beta);
+                double c, s;
+                if (beta < 0) {
+                    const double delta = (gamma - beta) * 0.5;
+                    s = sqrt(delta / gamma);
+                    c = p / (gamma * s * 2);
+                } else {
+                    c = sqrt((gamma + beta) / (gamma * 2));
+                    s = p / (gamma * c * 2);
+                }
+                double a = 0, b = 0;
+#pragma unroll
+                for (int k = 0; k < M; ++k) {
+                    const double t0 = c * ai[k] + s * aj[k];
+                    const double t1 = -s * ai[k] + c * aj[k];
+                    ai[k] = t0;
+                    At[j * M + k] = t1;
+                    a += t0 * t0;
+                    b += t1 * t1;
+                }
+                wi = a;
+                W[j] = b;
+                if (Vt) {
+                    double* Vi = Vt + i * ldv;
+                    double* Vj = Vt + j * ldv;
+                    for (int k = lane; k < n; k += LANES) {
+                        const double x = Vi[k], y = Vj[k];
+                        Vi[k] = c * x + s * y;
+                        Vj[k] = -s * x + c * y;
+                    }
+                }
+                dirty = changed = true;
+            }
+            if (dirty) {
+#pragma unroll
+                for (int k = 0; k < M; ++k) At[i * M + k] = ai[k];
+                W[i] = wi;
+            }
         }
-        off = Red::sumd(off);
-        diag = Red::sumd(diag);
-#ifdef SVO_DEBUG_SWEEPS
-        printf("sweep %d off %.3g diag %.3g\n", sweep, off, diag);
-#endif
-        if (off <= 1e-22 * diag || off == 0.0) break;
-        for (int r = 0; r < 11; ++r) {
-            const unsigned char* pq = w.pq + 12 * r;
-            for (int k = lane; k < 6; k += LANES) {
-                const int p = pq[2 * k], q = pq[2 * k + 1];
-                jacobi_cs(w.A[p * 13], w.A[q * 13], w.A[p * 12 + q], w.cs[2 * k], w.cs[2 * k + 1]);
+        if (!changed) break;
+    }
+    Red::sync();
+    // singular values (the cached squared norms ARE the sequential sums OpenCV recomputes here), selection sort
+    // (descending) by lane 0, row swaps split over the lanes
+    if (lane == 0) {
+#pragma unroll UNROLL
+        for (int i = 0; i < n; ++i) W[i] = sqrt(W[i]);
+#pragma unroll UNROLL
+        for (int i = 0; i < n - 1; ++i) {
+            int j = i;
+#pragma unroll UNROLL
+            for (int k = i + 1; k < n; ++k)
+                if (W[j] < W[k]) j = k;
+            perm[i] = j;
+            if (i != j) {
+                const double tw = W[i];
+                W[i] = W[j];
+                W[j] = tw;
             }
-            Red::sync();
-#pragma unroll
-            for (int bi = 0; bi < NB; ++bi) {
-                const int l = lane + bi * LANES;
-                if (l < 21) {
-                    const int ki = blk[bi] & 15, kj = blk[bi] >> 4;
-                    const int pi = pq[2 * ki], qi = pq[2 * ki + 1], pj = pq[2 * kj], qj = pq[2 * kj + 1];
-                    const double ci = w.cs[2 * ki], si = w.cs[2 * ki + 1], cj = w.cs[2 * kj], sj = w.cs[2 * kj + 1];
-                    const double a = w.A[pi * 12 + pj], b = w.A[pi * 12 + qj], c = w.A[qi * 12 + pj], d = w.A[qi * 12 + qj];
-                    const double a1 = ci * a - si * c, b1 = ci * b - si * d, c1 = si * a + ci * c, d1 = si * b + ci * d;
-                    double a2 = cj * a1 - sj * b1, b2 = sj * a1 + cj * b1, c2 = cj * c1 - sj * d1, d2 = sj * c1 + cj * d1;
-                    if (ki == kj) { b2 = 0.0; c2 = 0.0; }
-                    w.A[pi * 12 + pj] = a2; w.A[pi * 12 + qj] = b2; w.A[qi * 12 + pj] = c2; w.A[qi * 12 + qj] = d2;
-                    w.A[pj * 12 + pi] = a2; w.A[qj * 12 + pi] = b2; w.A[pj * 12 + qi] = c2; w.A[qj * 12 + qi] = d2;
+        }
+    }
+    Red::sync();
+#pragma unroll UNROLL
+    for (int i = 0; i < n - 1; ++i) {
+        const int j = perm[i];
+        if (i != j) {
+            for (int k = lane; k < M; k += LANES) {
+                const double t = At[i * M + k];
+                At[i * M + k] = At[j * M + k];
+                At[j * M + k] = t;
+            }
+            if (Vt)
+                for (int k = lane; k < n; k += LANES) {
+                    const double t = Vt[i * ldv + k];
+                    Vt[i * ldv + k] = Vt[j * ldv + k];
+                    Vt[j * ldv + k] = t;
                 }
-            }
-#pragma unroll
-            for (int vi = 0; vi < NV; ++vi) {
-                const int it = lane + vi * LANES;
-                if (it < 72) {
-                    const int k = it / 12, col = it - k * 12;
-                    const int p = pq[2 * k], q = pq[2 * k + 1];
-                    const double c = w.cs[2 * k], s = w.cs[2 * k + 1];
-                    const double vp = w.Vt[p * 12 + col], vq = w.Vt[q * 12 + col];
-                    w.Vt[p * 12 + col] = c * vp - s * vq;
-                    w.Vt[q * 12 + col] = s * vp + c * vq;
+        }
+    }
+    Red::sync();
+    // left singular vectors: rows scaled by 1 / w; a (numerically exact) zero singular value gets OpenCV's
+    // pseudo-random completion (RNG 0x12345678, two Gram-Schmidt passes) -- lane 0, it practically never runs
+    uint64_t rng = 0x12345678ull;
+#pragma unroll UNROLL
+    for (int i = 0; i < n; ++i) {
+        double sd = W[i];
+        if (sd <= minval) {
+            Red::sync();   // rows j < i are complete
+            if (lane == 0) {
+                for (int ii = 0; ii < 100 && sd <= minval; ++ii) {
+                    const double val0 = 1. / M;
+                    for (int k = 0; k < M; ++k) At[i * M + k] = (cv_rng_next(rng) & 256) != 0 ? val0 : -val0;
+                    for (int it = 0; it < 2; ++it)
+                        for (int j = 0; j < i; ++j) {
+                            sd = 0;
+                            for (int k = 0; k < M; ++k) sd += At[i * M + k] * At[j * M + k];
+                            double asum = 0;
+                            for (int k = 0; k < M; ++k) {
+                                const double t = At[i * M + k] - sd * At[j * M + k];
+                                At[i * M + k] = t;
+                                asum += fabs(t);
+                            }
+                            asum = asum > eps * 100 ? 1 / asum : 0;
+                            for (int k = 0; k < M; ++k) At[i * M + k] *= asum;
+                        }
+                    sd = 0;
+                    for (int k = 0; k < M; ++k) {
+                        const double t = At[i * M + k];
+                        sd += t * t;
+                    }
+                    sd = sqrt(sd);
                 }
-            }
+                const double s = sd > minval ? 1 / sd : 0.;
+                for (int k = 0; k < M; ++k) At[i * M + k] *= s;
+            }   // (the generator state only matters in lane 0)
             Red::sync();
+            continue;
+        }
+        const double s = 1 / sd;
+        for (int k = lane; k < M; k += LANES) At[i * M + k] *= s;
+    }
+    Red::sync();
+}
+
+// SVBkSbImpl_<double> (cv::SVD::backSubst): x = V diag(1/w) U^T b, singular values <= 2 eps sum(w) dropped.
+// U is given as Ut (row i = left singular vector i, length M), Vt N x N.  Serial.
+//   vector right-hand side (cv::solve(..., DECOMP_SVD), nb == 1)
+template <int M, int N>
+SVO_HD void cv_svbksb_vec(const double* w, const double* Ut, const double* Vt, int ldv, const double* b, double* x) {
+    constexpr int nm = M < N ? M : N;
+    double threshold = 0;
+#pragma unroll
+    for (int i = 0; i < nm; ++i) threshold += w[i];
+    threshold *= DBL_EPSILON * 2;
+#pragma unroll
+    for (int j = 0; j < N; ++j) x[j] = 0;
+#pragma unroll
+    for (int i = 0; i < nm; ++i) {
+        double wi = w[i];
+        if (fabs(wi) <= threshold) continue;
+        wi = 1 / wi;
+        double s = 0;
+#pragma unroll
+        for (int j = 0; j < M; ++j) s += Ut[i * M + j] * b[j];
+        s *= wi;
+#pragma unroll
+        for (int j = 0; j < N; ++j) x[j] = x[j] + s * Vt[i * ldv + j];
+    }
+}
+//   no right-hand side (cv::invert(..., DECOMP_SVD)): x (N x M, row-major) = pseudo-inverse
+template <int M, int N>
+SVO_HD void cv_svbksb_inv(const double* w, const double* Ut, const double* Vt, int ldv, double* x) {
+    constexpr int nm = M < N ? M : N;
+    double threshold = 0;
+#pragma unroll
+    for (int i = 0; i < nm; ++i) threshold += w[i];
+    threshold *= DBL_EPSILON * 2;
+#pragma unroll
+    for (int j = 0; j < N * M; ++j) x[j] = 0;
+#pragma unroll
+    for (int i = 0; i < nm; ++i) {
+        double wi = w[i];
+        if (fabs(wi) <= threshold) continue;
+        wi = 1 / wi;
+        double buffer[M];
+#pragma unroll
+        for (int j = 0; j < M; ++j) buffer[j] = Ut[i * M + j] * wi;
+#pragma unroll
+        for (int r = 0; r < N; ++r) {
+            const double s = Vt[i * ldv + r];
+#pragma unroll
+            for (int j = 0; j < M; ++j) x[r * M + j] = x[r * M + j] + s * buffer[j];
         }
     }
 }
 
-// least squares with a run-time column count (<= 5), 6 rows; same instruction stream for the three
-// beta approximations so that lanes 0..2 do not diverge
-SVO_HD bool householder_ls6(double* A /*6 x 5 storage, row stride 5*/, double* b, double* x, int cols) {
-    for (int k = 0; k < cols; ++k) {
-        double norm = 0.0;
-        for (int i = k; i < 6; ++i) norm += A[i * 5 + k] * A[i * 5 + k];
-        norm = sqrt(norm);
-        if (norm == 0.0) return false;
-        const double alpha = A[k * 5 + k] > 0 ? -norm : norm;
-        double v[6];
-        for (int i = 0; i < 6; ++i) v[i] = (i >= k) ? A[i * 5 + k] : 0.0;
-        v[k] -= alpha;
-        double vtv = 0.0;
-        for (int i = k; i < 6; ++i) vtv += v[i] * v[i];
-        if (vtv == 0.0) return false;
-        for (int j = k; j < cols; ++j) {
-            double dot = 0.0;
-            for (int i = k; i < 6; ++i) dot += v[i] * A[i * 5 + j];
-            const double f = 2.0 * dot / vtv;
-            for (int i = k; i < 6; ++i) A[i * 5 + j] -= f * v[i];
+// epnp::qr_solve (Householder; including its column scan that never looks at the last row).  A: 6 x 4
+// row-major, destroyed.  Leaves x untouched when a column is exactly zero, like the original.
+SVO_HD void epnp_qr_solve(double* A, double* b, double* x) {
+    constexpr int nr = 6, nc = 4;
+    double A1[nc], A2[nc];
+#pragma unroll
+    for (int k = 0; k < nc; ++k) {
+        double eta = fabs(A[k * nc + k]);
+#pragma unroll
+        for (int i = k + 1; i < nr; ++i) {
+            const double elt = fabs(A[(i - 1) * nc + k]);
+            if (eta < elt) eta = elt;
         }
-        double dot = 0.0;
-        for (int i = k; i < 6; ++i) dot += v[i] * b[i];
-        const double f = 2.0 * dot / vtv;
-        for (int i = k; i < 6; ++i) b[i] -= f * v[i];
+        if (eta == 0) return;
+        double sum2 = 0.0;
+        const double inv_eta = 1. / eta;
+#pragma unroll
+        for (int i = k; i < nr; ++i) {
+            A[i * nc + k] *= inv_eta;
+            sum2 += A[i * nc + k] * A[i * nc + k];
+        }
+        double sigma = sqrt(sum2);
+        if (A[k * nc + k] < 0) sigma = -sigma;
+        A[k * nc + k] += sigma;
+        A1[k] = sigma * A[k * nc + k];
+        A2[k] = -eta * sigma;
+#pragma unroll
+        for (int j = k + 1; j < nc; ++j) {
+            double sum = 0;
+#pragma unroll
+            for (int i = k; i < nr; ++i) sum += A[i * nc + k] * A[i * nc + j];
+            const double tau = sum / A1[k];
+#pragma unroll
+            for (int i = k; i < nr; ++i) A[i * nc + j] -= tau * A[i * nc + k];
+        }
     }
-    for (int k = cols - 1; k >= 0; --k) {
-        double s = b[k];
-        for (int j = k + 1; j < cols; ++j) s -= A[k * 5 + j] * x[j];
-        const double r = A[k * 5 + k];
-        if (fabs(r) < 1e-300) return false;
-        x[k] = s / r;
+#pragma unroll
+    for (int j = 0; j < nc; ++j) {
+        double tau = 0;
+#pragma unroll
+        for (int i = j; i < nr; ++i) tau += A[i * nc + j] * b[i];
+        tau /= A1[j];
+#pragma unroll
+        for (int i = j; i < nr; ++i) b[i] -= tau * A[i * nc + j];
     }
-    return true;
+    x[nc - 1] = b[nc - 1] / A2[nc - 1];
+#pragma unroll
+    for (int i = nc - 2; i >= 0; --i) {
+        double sum = 0;
+#pragma unroll
+        for (int j = i + 1; j < nc; ++j) sum += A[i * nc + j] * x[j];
+        x[i] = (b[i] - sum) / A2[i];
+    }
 }
 
+// ---------------------------------------------------------------------------
+struct EpnpWork {              // per-hypothesis scratch (shared memory on the device)
+    double A[144];             // M^T M -> rows = left singular vectors (ut of epnp::compute_pose)
+    double M[120];             // 10 x 12
+    double W[12];
+    double dv[72];             // [4][6][3]
+    double L[60], rho[6];
+    double pws[15], us[10], alphas[20], cws[12];
+    double vAt[3][30], vVt[3][25], vW[3][5];   // the three beta approximations: SVD of the 6 x {4, 3, 5} systems
+    double Rs[3][9], ts[3][3], errs[3];
+    int perm[12], vperm[3][5];
+    int ok;
+};
+
+SVO_HD double epnp_dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+// epnp::gauss_newton: 5 iterations of compute_A_and_b_gauss_newton + qr_solve
 SVO_HD void epnp_gauss_newton(const double* L, const double* rho, double* betas) {
+    double x[4] = {0, 0, 0, 0};
     for (int it = 0; it < 5; ++it) {
-        double A[24], b[6], x[4];
-        const double b0 = betas[0], b1 = betas[1], b2 = betas[2], b3 = betas[3];
+        double A[24], b[6];
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             const double* r = L + i * 10;
             double* a = A + i * 4;
-            a[0] = 2 * r[0] * b0 + r[1] * b1 + r[3] * b2 + r[6] * b3;
-            a[1] = r[1] * b0 + 2 * r[2] * b1 + r[4] * b2 + r[7] * b3;
-            a[2] = r[3] * b0 + r[4] * b1 + 2 * r[5] * b2 + r[8] * b3;
-            a[3] = r[6] * b0 + r[7] * b1 + r[8] * b2 + 2 * r[9] * b3;
-            b[i] = rho[i] - (r[0] * b0 * b0 + r[1] * b0 * b1 + r[2] * b1 * b1 + r[3] * b0 * b2 + r[4] * b1 * b2 +
-                             r[5] * b2 * b2 + r[6] * b0 * b3 + r[7] * b1 * b3 + r[8] * b2 * b3 + r[9] * b3 * b3);
+            a[0] = 2 * r[0] * betas[0] + r[1] * betas[1] + r[3] * betas[2] + r[6] * betas[3];
+            a[1] = r[1] * betas[0] + 2 * r[2] * betas[1] + r[4] * betas[2] + r[7] * betas[3];
+            a[2] = r[3] * betas[0] + r[4] * betas[1] + 2 * r[5] * betas[2] + r[8] * betas[3];
+            a[3] = r[6] * betas[0] + r[7] * betas[1] + r[8] * betas[2] + 2 * r[9] * betas[3];
+            b[i] = rho[i] - (r[0] * betas[0] * betas[0] + r[1] * betas[0] * betas[1] + r[2] * betas[1] * betas[1] +
+                             r[3] * betas[0] * betas[2] + r[4] * betas[1] * betas[2] + r[5] * betas[2] * betas[2] +
+                             r[6] * betas[0] * betas[3] + r[7] * betas[1] * betas[3] + r[8] * betas[2] * betas[3] +
+                             r[9] * betas[3] * betas[3]);
         }
-        if (!householder_ls<6, 4>(A, b, x)) return;   // OpenCV's qr_solve gives up on a singular A
+        epnp_qr_solve(A, b, x);
 #pragma unroll
         for (int i = 0; i < 4; ++i) betas[i] += x[i];
     }
 }
 
-// Orthogonal polar factor of a 3x3 matrix by scaled Newton iteration.  false if (near-)singular.
-SVO_HD bool polar_orthogonal3(const double* M, double* Q) {
-    double X[9], n2 = 0.0;
-    for (int i = 0; i < 9; ++i) n2 += M[i] * M[i];
-    if (!(n2 > 0.0)) return false;
-    const double sc = sqrt(3.0 / n2);
-    for (int i = 0; i < 9; ++i) X[i] = M[i] * sc;
-    for (int it = 0; it < 40; ++it) {
-        // cofactors: inv(X)^T = cof(X) / det(X)
-        double C[9];
-        C[0] = X[4] * X[8] - X[5] * X[7]; C[1] = X[5] * X[6] - X[3] * X[8]; C[2] = X[3] * X[7] - X[4] * X[6];
-        C[3] = X[2] * X[7] - X[1] * X[8]; C[4] = X[0] * X[8] - X[2] * X[6]; C[5] = X[1] * X[6] - X[0] * X[7];
-        C[6] = X[1] * X[5] - X[2] * X[4]; C[7] = X[2] * X[3] - X[0] * X[5]; C[8] = X[0] * X[4] - X[1] * X[3];
-        const double det = X[0] * C[0] + X[1] * C[1] + X[2] * C[2];
-        if (!(fabs(det) > 1e-9)) return false;   // X has unit-scale entries: rank deficient input
-        const double id = 1.0 / det;
-        double diff = 0.0;
-        for (int i = 0; i < 9; ++i) {
-            const double nx = 0.5 * (X[i] + C[i] * id);
-            diff += fabs(nx - X[i]);
-            X[i] = nx;
-        }
-        if (diff < 1e-15) break;
-    }
-    for (int i = 0; i < 9; ++i) Q[i] = X[i];
-    return true;
-}
-
 // compute_ccs / compute_pcs / solve_for_sign / estimate_R_and_t / reprojection_error of epnp.cpp
 SVO_HD double epnp_R_and_t(const EpnpWork& w, const Intrinsics& K, const double* betas, double* R9, double* t3) {
     double ccs[4][3], pcs[15];
+#pragma unroll
     for (int i = 0; i < 4; ++i) ccs[i][0] = ccs[i][1] = ccs[i][2] = 0.0;
+#pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const double* v = w.Vt + 12 * w.order[i];
+        const double* v = w.A + 12 * (11 - i);
+#pragma unroll
         for (int j = 0; j < 4; ++j)
+#pragma unroll
             for (int k = 0; k < 3; ++k) ccs[j][k] += betas[i] * v[3 * j + k];
     }
+#pragma unroll
     for (int i = 0; i < 5; ++i) {
         const double* a = w.alphas + 4 * i;
+#pragma unroll
         for (int j = 0; j < 3; ++j)
             pcs[3 * i + j] = a[0] * ccs[0][j] + a[1] * ccs[1][j] + a[2] * ccs[2][j] + a[3] * ccs[3][j];
     }
-    if (pcs[2] < 0.0)
+    if (pcs[2] < 0.0) {
+#pragma unroll
         for (int i = 0; i < 15; ++i) pcs[i] = -pcs[i];
+    }
     double pc0[3] = {0, 0, 0}, pw0[3] = {0, 0, 0};
+#pragma unroll
     for (int i = 0; i < 5; ++i)
+#pragma unroll
         for (int j = 0; j < 3; ++j) {
             pc0[j] += pcs[3 * i + j];
             pw0[j] += w.pws[3 * i + j];
         }
+#pragma unroll
     for (int j = 0; j < 3; ++j) {
         pc0[j] /= 5;
         pw0[j] /= 5;
     }
-    double abt[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    // cvSVD(ABt, D, U, V): R = U V^T, third row negated when det < 0.  At = ABt^T, accumulated in place.
+    double At[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Vt[9], D[3];
+    int perm[3];
+#pragma unroll
     for (int i = 0; i < 5; ++i)
+#pragma unroll
         for (int j = 0; j < 3; ++j)
-            for (int k = 0; k < 3; ++k) abt[3 * j + k] += (pcs[3 * i + j] - pc0[j]) * (w.pws[3 * i + k] - pw0[k]);
-    // R = U V^T of the SVD of ABt == the orthogonal polar factor of ABt (det = sign(det ABt)):
-    // Newton iteration X <- (X + X^-T) / 2, quadratically convergent; SVD only for a (near-)singular ABt.
-    if (!polar_orthogonal3(abt, R9)) {
-        double U[9], S[3], V[9];
-        svd3x3(abt, U, S, V);
-        for (int i = 0; i < 3; ++i)
-            for (int j = 0; j < 3; ++j)
-                R9[i * 3 + j] = U[i * 3] * V[j * 3] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
-    }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) At[3 * k + j] += (pcs[3 * i + j] - pc0[j]) * (w.pws[3 * i + k] - pw0[k]);
+    cv_jacobi_svd<3, 3, 1, SerialRedD>(At, Vt, 3, D, perm, 0);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)   // U[i][k] = At[k][i], V[j][k] = Vt[k][j]
+            R9[i * 3 + j] = At[0 + i] * Vt[0 + j] + At[3 + i] * Vt[3 + j] + At[6 + i] * Vt[6 + j];
     const double det = R9[0] * R9[4] * R9[8] + R9[1] * R9[5] * R9[6] + R9[2] * R9[3] * R9[7] - R9[2] * R9[4] * R9[6] -
                        R9[1] * R9[3] * R9[8] - R9[0] * R9[5] * R9[7];
     if (det < 0) {
@@ -432,28 +439,73 @@ SVO_HD double epnp_R_and_t(const EpnpWork& w, const Intrinsics& K, const double*
         R9[7] = -R9[7];
         R9[8] = -R9[8];
     }
-    for (int i = 0; i < 3; ++i) t3[i] = pc0[i] - (R9[i * 3] * pw0[0] + R9[i * 3 + 1] * pw0[1] + R9[i * 3 + 2] * pw0[2]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) t3[i] = pc0[i] - epnp_dot3(R9 + 3 * i, pw0);
     double sum2 = 0.0;
+#pragma unroll
     for (int i = 0; i < 5; ++i) {
         const double* pw = w.pws + 3 * i;
-        const double Xc = R9[0] * pw[0] + R9[1] * pw[1] + R9[2] * pw[2] + t3[0];
-        const double Yc = R9[3] * pw[0] + R9[4] * pw[1] + R9[5] * pw[2] + t3[1];
-        const double inv_Zc = 1.0 / (R9[6] * pw[0] + R9[7] * pw[1] + R9[8] * pw[2] + t3[2]);
+        const double Xc = epnp_dot3(R9, pw) + t3[0];
+        const double Yc = epnp_dot3(R9 + 3, pw) + t3[1];
+        const double inv_Zc = 1.0 / (epnp_dot3(R9 + 6, pw) + t3[2]);
         const double ue = K.cx + K.fx * Xc * inv_Zc, ve = K.cy + K.fy * Yc * inv_Zc;
-        const double du = w.us[2 * i] - ue, dv = w.us[2 * i + 1] - ve;
-        sum2 += sqrt(du * du + dv * dv);
+        const double u = w.us[2 * i], v = w.us[2 * i + 1];
+        sum2 += sqrt((u - ue) * (u - ue) + (v - ve) * (v - ve));
     }
     return sum2 / 5;
 }
 
-// X: 5 x 3 object points (float32), uv: 5 x 2 pixel coordinates (float32).  Every lane returns the
-// same pose; false when the sample is degenerate.
-template <int LANES, class Red>
-SVO_HD bool epnp5_solve(EpnpWork& w, const Intrinsics& K, const float* X, const float* uv, int lane, Pose& out) {
+// find_betas_approx_{1,2,3} + gauss_newton + compute_R_and_t for ONE of the three approximations, executed by the
+// LANES lanes of one warp: columns [B11 B12 B13 B14] / [B11 B12 B22] / [B11 B12 B22 B13 B23] of L_6x10,
+// cv::solve(..., DECOMP_SVD).  The scalar tail (back substitution, Gauss-Newton, R and t) runs redundantly in every lane.
+template <int VAR, int LANES, class Red>
+SVO_HD void epnp_variant(EpnpWork& w, const Intrinsics& K, int lane) {
+    constexpr int ncol = VAR == 0 ? 4 : (VAR == 1 ? 3 : 5);
+    const int colmap[3][5] = {{0, 1, 3, 6, 0}, {0, 1, 2, 0, 0}, {0, 1, 2, 3, 4}};
+    double* At = w.vAt[VAR];
+    double* Vt = w.vVt[VAR];
+    for (int e = lane; e < ncol * 6; e += LANES) At[e] = w.L[(e % 6) * 10 + colmap[VAR][e / 6]];
+    Red::sync();
+    cv_jacobi_svd<6, ncol, LANES, Red>(At, Vt, 5, w.vW[VAR], w.vperm[VAR], lane);
+    double x[5] = {0, 0, 0, 0, 0}, be[4];
+    cv_svbksb_vec<6, ncol>(w.vW[VAR], At, Vt, 5, w.rho, x);
+    SVO_EPNP_TICK(5)
+    if (VAR == 0) {
+        if (x[0] < 0) { be[0] = sqrt(-x[0]); be[1] = -x[1] / be[0]; be[2] = -x[2] / be[0]; be[3] = -x[3] / be[0]; }
+        else          { be[0] = sqrt(x[0]);  be[1] = x[1] / be[0];  be[2] = x[2] / be[0];  be[3] = x[3] / be[0]; }
+    } else {
+        if (x[0] < 0) { be[0] = sqrt(-x[0]); be[1] = (x[2] < 0) ? sqrt(-x[2]) : 0.0; }
+        else          { be[0] = sqrt(x[0]);  be[1] = (x[2] > 0) ? sqrt(x[2]) : 0.0; }
+        if (x[1] < 0) be[0] = -be[0];
+        be[2] = VAR == 2 ? x[3] / be[0] : 0.0;
+        be[3] = 0.0;
+    }
+    epnp_gauss_newton(w.L, w.rho, be);
+    SVO_EPNP_TICK(6)
+    double R9[9], t3[3];
+    const double err = epnp_R_and_t(w, K, be, R9, t3);
     if (lane == 0) {
+        w.errs[VAR] = err;
+        for (int i = 0; i < 9; ++i) w.Rs[VAR][i] = R9[i];
+        for (int i = 0; i < 3; ++i) w.ts[VAR][i] = t3[i];
+    }
+}
+
+// X: 5 x 3 object points (float32), uv: 5 x 2 pixel coordinates (float32).  Executed by GROUPS warps of LANES lanes
+// (device: 3 x 32, one block per hypothesis -- the three beta approximations run side by side; host tests: 1 x 1).
+// `Red` provides sync() (the lanes of one group) and sync_all() (all groups).  Every lane returns the same pose;
+// false when the result is not finite.
+template <int LANES, int GROUPS, class Red>
+SVO_HD bool epnp5_solve(EpnpWork& w, const Intrinsics& K, const float* X, const float* uv, int lane, int group,
+                        Pose& out) {
+    constexpr int n = 5;
+    const int tid = group * LANES + lane;
+    constexpr int NT = LANES * GROUPS;
+    SVO_EPNP_TICK(0)
+    if (tid == 0) {
         w.ok = 1;
         const double ifx = 1.0 / K.fx, ify = 1.0 / K.fy;
-        for (int i = 0; i < 5; ++i) {
+        for (int i = 0; i < n; ++i) {
             for (int j = 0; j < 3; ++j) w.pws[3 * i + j] = (double)X[3 * i + j];
             // cv::undistortPoints (zero distortion) stores normalised coordinates as float32;
             // epnp::init_points maps them back to pixels in double
@@ -462,49 +514,61 @@ SVO_HD bool epnp5_solve(EpnpWork& w, const Intrinsics& K, const float* X, const 
             w.us[2 * i] = (double)xn * K.fx + K.cx;
             w.us[2 * i + 1] = (double)yn * K.fy + K.cy;
         }
-        // choose_control_points
-        for (int j = 0; j < 3; ++j) {
-            double s = 0.0;
-            for (int i = 0; i < 5; ++i) s += w.pws[3 * i + j];
-            w.cws[j] = s / 5;
-        }
-        double c[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, vt[9], dc[3];
-        for (int i = 0; i < 5; ++i)
-            for (int a = 0; a < 3; ++a)
-                for (int b = 0; b < 3; ++b)
-                    c[3 * a + b] += (w.pws[3 * i + a] - w.cws[a]) * (w.pws[3 * i + b] - w.cws[b]);
-        jacobi_eigen_sym<3>(c, vt, dc);
-        for (int i = 1; i < 4; ++i) {
-            const double k = sqrt((dc[i - 1] > 0 ? dc[i - 1] : 0.0) / 5);
-            for (int j = 0; j < 3; ++j) w.cws[3 * i + j] = w.cws[j] + k * vt[3 * (i - 1) + j];
-        }
-        // compute_barycentric_coordinates
-        double cc[9], ci[9];
-        for (int i = 0; i < 3; ++i)
-            for (int j = 1; j < 4; ++j) cc[3 * i + j - 1] = w.cws[3 * j + i] - w.cws[i];
-        if (!inv3x3(cc, ci)) w.ok = 0;
-        else
-            for (int i = 0; i < 5; ++i) {
-                const double* pi = w.pws + 3 * i;
-                double* a = w.alphas + 4 * i;
-                for (int j = 0; j < 3; ++j)
-                    a[1 + j] = ci[3 * j] * (pi[0] - w.cws[0]) + ci[3 * j + 1] * (pi[1] - w.cws[1]) +
-                               ci[3 * j + 2] * (pi[2] - w.cws[2]);
-                a[0] = 1.0 - a[1] - a[2] - a[3];
+        // choose_control_points: centroid + PCA axes (SVD of PW0^T PW0, rows of U^T)
+        double cws[12];
+        for (int j = 0; j < 3; ++j) cws[j] = 0;
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < 3; ++j) cws[j] += w.pws[3 * i + j];
+        for (int j = 0; j < 3; ++j) cws[j] /= n;
+        double c[9], dc[3];
+        int perm[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int b = a; b < 3; ++b) {   // cv::mulTransposed: upper triangle, sequential over the rows, mirrored
+                double s = 0;
+                for (int k = 0; k < n; ++k) s += (w.pws[3 * k + a] - cws[a]) * (w.pws[3 * k + b] - cws[b]);
+                c[3 * a + b] = s;
+                c[3 * b + a] = s;
             }
-        // rho
-        for (int r = 0, a = 0, b = 1; r < 6; ++r) {
-            double s = 0.0;
-            for (int k = 0; k < 3; ++k) s += (w.cws[3 * a + k] - w.cws[3 * b + k]) * (w.cws[3 * a + k] - w.cws[3 * b + k]);
-            w.rho[r] = s;
-            ++b;
-            if (b > 3) { ++a; b = a + 1; }
+        cv_jacobi_svd<3, 3, 1, SerialRedD>(c, nullptr, 0, dc, perm, 0);   // symmetric: the transpose is the matrix itself
+#pragma unroll
+        for (int i = 1; i < 4; ++i) {
+            const double k = sqrt(dc[i - 1] / n);
+#pragma unroll
+            for (int j = 0; j < 3; ++j) cws[3 * i + j] = cws[j] + k * c[3 * (i - 1) + j];
         }
+        // compute_barycentric_coordinates: cvInvert(CC, CC_inv, CV_SVD)
+        double cct[9], vt[9], wd[3], ci[9];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 1; j < 4; ++j) cct[(j - 1) * 3 + i] = cws[3 * j + i] - cws[i];   // transposed: row = column of CC
+        cv_jacobi_svd<3, 3, 1, SerialRedD>(cct, vt, 3, wd, perm, 0);
+        cv_svbksb_inv<3, 3>(wd, cct, vt, 3, ci);
+        for (int i = 0; i < n; ++i) {
+            const double* pi = w.pws + 3 * i;
+            double* a = w.alphas + 4 * i;
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                a[1 + j] = ci[3 * j] * (pi[0] - cws[0]) + ci[3 * j + 1] * (pi[1] - cws[1]) + ci[3 * j + 2] * (pi[2] - cws[2]);
+            a[0] = 1.0 - a[1] - a[2] - a[3];
+        }
+        // compute_rho
+        const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            const double* p1 = cws + 3 * pa[r];
+            const double* p2 = cws + 3 * pb[r];
+            w.rho[r] = (p1[0] - p2[0]) * (p1[0] - p2[0]) + (p1[1] - p2[1]) * (p1[1] - p2[1]) +
+                       (p1[2] - p2[2]) * (p1[2] - p2[2]);
+        }
+        for (int i = 0; i < 12; ++i) w.cws[i] = cws[i];
     }
-    Red::sync();
-    if (!w.ok) return false;
+    Red::sync_all();
+    SVO_EPNP_TICK(1)
     // fill_M
-    for (int e = lane; e < 120; e += LANES) {
+    for (int e = tid; e < 120; e += NT) {
         const int row = e / 12, col = e - row * 12;
         const int i = row >> 1, k = col / 3, c3 = col - 3 * k;
         const double as = w.alphas[4 * i + k];
@@ -513,67 +577,42 @@ SVO_HD bool epnp5_solve(EpnpWork& w, const Intrinsics& K, const float* X, const 
         else v = c3 == 0 ? 0.0 : (c3 == 1 ? as * K.fy : as * (K.cy - w.us[2 * i + 1]));
         w.M[e] = v;
     }
-    Red::sync();
-    for (int e = lane; e < 144; e += LANES) {
+    Red::sync_all();
+    for (int e = tid; e < 144; e += NT) {   // M^T M, sequential over the 10 rows
         const int a = e / 12, b = e - a * 12;
         double s = 0.0;
+#pragma unroll
         for (int r = 0; r < 10; ++r) s += w.M[r * 12 + a] * w.M[r * 12 + b];
         w.A[e] = s;
     }
-    Red::sync();
-    jacobi12_parallel<LANES, Red>(w, lane);
-    if (lane == 0) {   // the 4 smallest eigenvalues, ascending (ut rows 11, 10, 9, 8 of cvSVD)
-        bool used[12];
-        for (int i = 0; i < 12; ++i) used[i] = false;
-        for (int k = 0; k < 4; ++k) {
-            int m = -1;
-            for (int i = 0; i < 12; ++i)
-                if (!used[i] && (m < 0 || w.A[i * 13] < w.A[m * 13])) m = i;
-            used[m] = true;
-            w.order[k] = m;
-        }
-    }
-    Red::sync();
-    for (int e = lane; e < 72; e += LANES) {   // dv[i][j][k]
+    Red::sync_all();
+    SVO_EPNP_TICK(2)
+    if (group == 0) cv_jacobi_svd<12, 12, LANES, Red>(w.A, nullptr, 0, w.W, w.perm, lane);
+    Red::sync_all();
+    SVO_EPNP_TICK(3)
+    // compute_L_6x10: v[i] = ut row 11 - i
+    for (int e = tid; e < 72; e += NT) {   // dv[i][j][k]
         const int i = e / 18, j = (e - i * 18) / 3, k = e - i * 18 - j * 3;
         const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
-        const double* v = w.Vt + 12 * w.order[i];
+        const double* v = w.A + 12 * (11 - i);
         w.dv[e] = v[3 * pa[j] + k] - v[3 * pb[j] + k];
     }
-    Red::sync();
-    for (int e = lane; e < 60; e += LANES) {   // L_6x10
+    Red::sync_all();
+    for (int e = tid; e < 60; e += NT) {   // L_6x10
         const int r = e / 10, c = e - r * 10;
         const int ia[10] = {0, 0, 1, 0, 1, 2, 0, 1, 2, 3}, ib[10] = {0, 1, 1, 2, 2, 2, 3, 3, 3, 3};
-        const double* a = w.dv + ia[c] * 18 + r * 3;
-        const double* b = w.dv + ib[c] * 18 + r * 3;
-        const double d = a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
+        const double d = epnp_dot3(w.dv + ia[c] * 18 + r * 3, w.dv + ib[c] * 18 + r * 3);
         w.L[e] = (ia[c] == ib[c]) ? d : 2.0 * d;
     }
-    Red::sync();
-    for (int var = lane; var < 3; var += LANES) {
-        // find_betas_approx_{1,2,3}: columns [B11 B12 B13 B14] / [B11 B12 B22] / [B11 B12 B22 B13 B23]
-        const int ncol = var == 0 ? 4 : (var == 1 ? 3 : 5);
-        const int colmap[3][5] = {{0, 1, 3, 6, 0}, {0, 1, 2, 0, 0}, {0, 1, 2, 3, 4}};
-        double A[30], b[6], x[5] = {0, 0, 0, 0, 0}, be[4];
-        for (int i = 0; i < 6; ++i) {
-            for (int k = 0; k < 5; ++k) A[i * 5 + k] = k < ncol ? w.L[i * 10 + colmap[var][k]] : 0.0;
-            b[i] = w.rho[i];
-        }
-        householder_ls6(A, b, x, ncol);
-        if (var == 0) {
-            if (x[0] < 0) { be[0] = sqrt(-x[0]); be[1] = -x[1] / be[0]; be[2] = -x[2] / be[0]; be[3] = -x[3] / be[0]; }
-            else          { be[0] = sqrt(x[0]);  be[1] = x[1] / be[0];  be[2] = x[2] / be[0];  be[3] = x[3] / be[0]; }
-        } else {
-            if (x[0] < 0) { be[0] = sqrt(-x[0]); be[1] = (x[2] < 0) ? sqrt(-x[2]) : 0.0; }
-            else          { be[0] = sqrt(x[0]);  be[1] = (x[2] > 0) ? sqrt(x[2]) : 0.0; }
-            if (x[1] < 0) be[0] = -be[0];
-            be[2] = var == 2 ? x[3] / be[0] : 0.0;
-            be[3] = 0.0;
-        }
-        epnp_gauss_newton(w.L, w.rho, be);
-        w.errs[var] = epnp_R_and_t(w, K, be, w.Rs[var], w.ts[var]);
+    Red::sync_all();
+    SVO_EPNP_TICK(4)
+    for (int var = group; var < 3; var += GROUPS) {
+        if (var == 0) epnp_variant<0, LANES, Red>(w, K, lane);
+        else if (var == 1) epnp_variant<1, LANES, Red>(w, K, lane);
+        else epnp_variant<2, LANES, Red>(w, K, lane);
     }
-    Red::sync();
+    Red::sync_all();
+    SVO_EPNP_TICK(7)
     int best = 0;
     if (w.errs[1] < w.errs[0]) best = 1;
     if (w.errs[2] < w.errs[best]) best = 2;

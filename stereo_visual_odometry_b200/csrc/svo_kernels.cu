@@ -685,11 +685,19 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
         launch_pyrdown_job(j, d.n_seq * 2, st);
         ++launches;
     }
-    if (pg.nlevels == 1 && left && pg.cn == 1) {   // no pyramid level to fuse the copy with
-        cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 0) + pg.off[0], pg.pitch[0], left, stride, pg.w[0], pg.h[0],
-                          cudaMemcpyDeviceToDevice, st);
-        cudaMemcpy2DAsync(d.pyr + pg.base(0, slot, 1) + pg.off[0], pg.pitch[0], right, stride, pg.w[0], pg.h[0],
-                          cudaMemcpyDeviceToDevice, st);
+    if (pg.nlevels == 1 && left && pg.cn == 1) {   // no pyramid level to fuse the copy with: every sequence's planes
+        PyrDownJob j;
+        memset(&j, 0, sizeof(j));
+        for (int cam = 0; cam < 2; ++cam) {
+            j.src[cam] = cam ? right : left;
+            j.copy[cam] = d.pyr + pg.base(0, slot, cam) + pg.off[0];
+        }
+        j.src_seq_stride = seq_stride;
+        j.spitch = stride;
+        j.copy_seq_stride = ctx_seq_stride;
+        j.cpitch = pg.pitch[0];
+        copy_rows_kernel<<<dim3((pg.w[0] + 255) / 256, pg.h[0], d.n_seq * 2), 256, 0, st>>>(j, pg.w[0]);
+        ++launches;
     }
     unsigned long long* keysA = d.fastkeys + ((long long)(slot * 2 + 0) * d.n_seq) * bg.nb;
     unsigned long long* keysB = d.fastkeys + ((long long)(slot * 2 + 1) * d.n_seq) * bg.nb;
@@ -1392,10 +1400,17 @@ void launch_select(const DevArrays& d, const PyrGeom& pg, const PipeConfig& pc, 
 // PnP-RANSAC: parallel 5-point hypotheses (LM from the extrinsic guess, like
 // solvePnP(ITERATIVE, useExtrinsicGuess) inside OpenCV's RANSAC loop), inlier counting
 // by warp reduction, then an FP64 LM refit on the inliers of the best hypothesis.
-constexpr int HYP_WARPS = 4;
+// One block of three warps per RANSAC hypothesis: EPnP on the 5-point sample (what cv::solvePnPRansac runs per
+// iteration; svo_epnp.cuh restates it operation for operation, so its time is one long dependent FP64 chain --
+// the three beta approximations run side by side in the three warps), then the inlier count over all matched
+// points by the whole block.  OpenCV's loop is adaptive: with >= 75 % inliers it never looks beyond the first 16
+// hypotheses, so the launch is split -- hypotheses [0, HYP_FIRST) always, the rest only when the replay of the
+// first counts says the loop goes on (checked on the device by every block of the second launch).
+constexpr int HYP_THREADS = 96, HYP_FIRST = 16;
 
 struct WarpRedD {
     static __device__ __forceinline__ void sync() { __syncwarp(); }
+    static __device__ __forceinline__ void sync_all() { __syncthreads(); }
     static __device__ __forceinline__ double sumd(double v) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -1403,17 +1418,24 @@ struct WarpRedD {
     }
 };
 
-// One warp per RANSAC hypothesis: EPnP on the 5-point sample (what cv::solvePnPRansac runs per
-// iteration), then the inlier count over all matched points by warp reduction.
-__global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, PipeConfig pc) {
-    __shared__ EpnpWork work[HYP_WARPS];
+__global__ void __launch_bounds__(HYP_THREADS) pnp_hyp_kernel(DevArrays d, PipeConfig pc, int hyp0) {
+    __shared__ EpnpWork work;
+    __shared__ int sm_cnt[HYP_THREADS / 32];
     const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int hyp = blockIdx.x * HYP_WARPS + wid;
+    const int hyp = hyp0 + blockIdx.x;
     SeqState* s = d.state + seq;
     const int n = s->n_matched;
     const int min_n = max(4, pc.features_threshold);
     if (hyp >= d.n_hyp || n <= min_n) return;   // vo.cpp:82-84
+    if (hyp0 > 0) {
+        // the sequential loop only reaches this hypothesis if its iteration budget, after the first hyp0 counts,
+        // is still larger than hyp0
+        int bc;
+        if (ransac_replay_budget(d.hyp_count + (long long)seq * d.n_hyp, hyp0, n, pc.ransac_iterations,
+                                 pc.ransac_confidence, bc) <= hyp0)
+            return;
+    }
     const long long fo = (long long)seq * d.cap;
     const float* X3 = d.X3 + fo * 3;
     const float2* uv = d.m_L1 + fo;
@@ -1434,10 +1456,10 @@ __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, Pi
         U[2 * i + 1] = q.y;
     }
     Pose P;
-    const bool solved = epnp5_solve<32, WarpRedD>(work[wid], pc.K, X, U, lane, P);
+    const bool solved = epnp5_solve<32, 3, WarpRedD>(work, pc.K, X, U, lane, wid, P);
     int cnt = 0;
     if (solved && valid) {
-        for (int i = lane; i < n; i += 32) {
+        for (int i = threadIdx.x; i < n; i += HYP_THREADS) {
             const float2 q = uv[i];
             const float uvf[2] = {q.x, q.y};
             const float e = reproj_err_sq(P, pc.K, X3 + 3 * i, uvf);
@@ -1445,11 +1467,13 @@ __global__ void __launch_bounds__(HYP_WARPS * 32) pnp_hyp_kernel(DevArrays d, Pi
         }
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if (lane == 0) {
+    if (lane == 0) sm_cnt[wid] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
         double* hp = d.hyp_pose + ((long long)seq * d.n_hyp + hyp) * 12;
         for (int i = 0; i < 9; ++i) hp[i] = P.R[i];
         for (int i = 0; i < 3; ++i) hp[9 + i] = P.t[i];
-        d.hyp_count[(long long)seq * d.n_hyp + hyp] = (solved && valid) ? cnt : 0;
+        d.hyp_count[(long long)seq * d.n_hyp + hyp] = (solved && valid) ? sm_cnt[0] + sm_cnt[1] + sm_cnt[2] : 0;
     }
 }
 
@@ -1666,8 +1690,9 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_b_kernel(DevArrays d, P
     write_result(d, seq, job, 1, SVO_REASON_OK, 1, n_in, T);
 }
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
-    dim3 grid((d.n_hyp + HYP_WARPS - 1) / HYP_WARPS, d.n_seq);
-    pnp_hyp_kernel<<<grid, HYP_WARPS * 32, 0, st>>>(d, pc);
+    const int first = d.n_hyp < HYP_FIRST ? d.n_hyp : HYP_FIRST;
+    pnp_hyp_kernel<<<dim3(first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, 0);
+    if (d.n_hyp > first) pnp_hyp_kernel<<<dim3(d.n_hyp - first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, first);
 }
 void launch_pnp_final_a(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     pnp_final_a_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);

@@ -311,9 +311,13 @@ class VisualOdometry:
     def circularMatching(self, imgLeftT1, imgRightT1, pointsLeftT0, current_features: FeatureSet | None = None):
         """vo.h:374-379 / vo.cpp:169-240 against the images of the previous stereo_callback.
         Returns (pL0, pR0, pL1, pR1) compacted; `current_features` is compacted in place."""
-        if self._last_images is None:
+        if self._ctx is None or self._last_images is None:
             raise SvoError("circularMatching needs a prior stereo_callback (t0 pyramids)")
-        L0, R0 = self._last_images
+        # the images of the cached t0 pyramids (vo.h:257-258) come from the context: after an empty frame they are
+        # still the OLD ones (vo.cpp:179-181), exactly as in the reference
+        L0 = np.empty_like(np.ascontiguousarray(self._last_images[0]))
+        R0 = np.empty_like(L0)
+        check(lib().svo_get_frame_images(self._ctx, 0, ptr(L0), ptr(R0), L0.strides[0]))
         return circularMatching(L0, R0, imgLeftT1, imgRightT1, pointsLeftT0, current_features, self.params)
 
     def matchingFeatures(self, imageLeftT0, imageRightT0, imageLeftT1, imageRightT1, currentVOFeatures: FeatureSet):

@@ -47,7 +47,8 @@ def hostcores():
 
 @pytest.fixture(scope="session")
 def run1():
-    """First 8 stereo pairs of the reference's run1 sequence: dict(bgr=[(L,R)], gray=[(L,R)], xyz=golden rows)."""
+    """The reference's run1 sequence as committed fixtures (tests/golden/make_golden.py): dict(bgr=[(L,R)] and
+    xyz=golden rows for frames 0..7 as the CLI reads them, gray=[(L,R)] for frames 0..47 as 8UC1)."""
     import cv2
     z = np.load(os.path.join(ROOT, "tests", "golden", "run1_first8.npz"))
     bgr, gray = [], []
@@ -56,6 +57,9 @@ def run1():
         R = cv2.imdecode(z[f"right_{i}"], cv2.IMREAD_COLOR)
         bgr.append((L, R))
         gray.append((cv2.cvtColor(L, cv2.COLOR_BGR2GRAY), cv2.cvtColor(R, cv2.COLOR_BGR2GRAY)))
+    z2 = np.load(os.path.join(ROOT, "tests", "golden", "run1_gray_8_47.npz"))
+    for i in range(8, 48):
+        gray.append((cv2.imdecode(z2[f"left_{i}"], cv2.IMREAD_GRAYSCALE), cv2.imdecode(z2[f"right_{i}"], cv2.IMREAD_GRAYSCALE)))
     return dict(bgr=bgr, gray=gray, xyz=z["result_xyz"])
 
 

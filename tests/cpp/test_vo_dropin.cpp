@@ -118,6 +118,58 @@ static void circular_matching() {
     REQUIRE(n == 121);
 }
 
+// VisualOdometry::matchingFeatures (include/vo.h:354-362, src/vo.cpp:315-366 of the reference) through the header:
+// FAST on the t0 left image (+ the threshold / 4 retry below 100 features), bucketing, circular matching, bounds,
+// compaction -- all five containers index-aligned.  The scene is the reference's own test_circularMatching grid
+// (main.cpp:174-209): 121 triangles, t1 shifted by +1 px in x, the right images by +1 px in y.
+static void matching_features() {
+    cv::Mat iL0 = blank(600, 600), iR0 = blank(600, 600), iL1 = blank(600, 600), iR1 = blank(600, 600);
+    for (int i = 0; i <= 10; ++i)
+        for (int j = 0; j <= 10; ++j) {
+            stamp(iL0, (j + 1) * 40, (i + 1) * 40, 8);
+            stamp(iL1, (j + 1) * 40 + 1, (i + 1) * 40, 8);
+            stamp(iR0, (j + 1) * 40, (i + 1) * 40 + 1, 8);
+            stamp(iR1, (j + 1) * 40 + 1, (i + 1) * 40 + 1, 8);
+        }
+    VisualOdometry vo;
+    FeatureSet fs;   // empty: everything comes from FAST on iL0
+    std::vector<cv::Point2f> pl0, pr0, pl1, pr1;
+    vo.matchingFeatures(iL0, iR0, iL1, iR1, fs, pl0, pr0, pl1, pr1);
+    const size_t n = fs.points.size();
+    REQUIRE(n == 121);
+    REQUIRE(pl0.size() == n && pr0.size() == n && pl1.size() == n && pr1.size() == n);
+    REQUIRE(fs.ages.size() == n && fs.strengths.size() == n);
+    FeatureSet expect;   // what FAST + bucketing alone yield, in the same (bucket row-major) order
+    expect.appendFeaturesFromImage(iL0, FAST_THRESHOLD);
+    REQUIRE(expect.size() == (int)n);
+    for (size_t k = 0; k < n; ++k) {
+        REQUIRE(fs.points[k].x == expect.points[k].x && fs.points[k].y == expect.points[k].y);   // t0 coordinates (vo.cpp:360)
+        REQUIRE(fs.ages[k] == 0 && fs.strengths[k] == expect.strengths[k]);                       // ages++ is stereo_callback's job
+        REQUIRE(pl0[k].x == fs.points[k].x && pl0[k].y == fs.points[k].y);
+        REQUIRE(std::fabs(pl1[k].x - pl0[k].x - 1) < 0.05f && std::fabs(pl1[k].y - pl0[k].y) < 0.05f);
+        REQUIRE(std::fabs(pr0[k].x - pl0[k].x) < 0.05f && std::fabs(pr0[k].y - pl0[k].y - 1) < 0.05f);
+        REQUIRE(std::fabs(pr1[k].x - pl0[k].x - 1) < 0.05f && std::fabs(pr1[k].y - pl0[k].y - 1) < 0.05f);
+    }
+    // second call with the tracked set (t1 positions, one frame older) as stereo_callback would hand it over:
+    // the old features win their buckets (age 1 beats age 0 at equal strength), nothing new is appended beside them
+    FeatureSet tracked;
+    for (size_t k = 0; k < n; ++k)   // exact pixel positions, so that every tracked feature shares the bucket of its corner
+        tracked.points.push_back(cv::Point2f(std::round(pl1[k].x), std::round(pl1[k].y)));
+    tracked.ages.assign(n, 1);
+    tracked.strengths = fs.strengths;
+    vo.matchingFeatures(iL1, iR1, iL0, iR0, tracked, pl0, pr0, pl1, pr1);   // back to the first pair: shift -1 px
+    REQUIRE(tracked.points.size() == n && pl0.size() == n);
+    for (size_t k = 0; k < n; ++k) {
+        REQUIRE(tracked.ages[k] == 1);
+        REQUIRE(std::fabs(pl1[k].x - pl0[k].x + 1) < 0.05f && std::fabs(pl1[k].y - pl0[k].y) < 0.05f);
+    }
+    // no texture at all: the retry fires, nothing is found, every container comes back empty (vo.cpp:179-181)
+    cv::Mat z = blank(200, 320);
+    FeatureSet none;
+    vo.matchingFeatures(z, z, z, z, none, pl0, pr0, pl1, pr1);
+    REQUIRE(none.size() == 0 && pl0.empty() && pr0.empty() && pl1.empty() && pr1.empty());
+}
+
 static void camera_to_world() {
     cv::Mat_<float> K = cv::Mat_<float>::eye(3, 3);
     const int n = 27;
@@ -191,6 +243,7 @@ int main() {
     std::printf("TEST FEATURE SET EDGE\n");     featureset_edges();
     std::printf("TEST FIND UNMOVED POINTS\n");  unmoved_points();
     std::printf("TEST CIRCULAR MATCHING\n");    circular_matching();
+    std::printf("TEST MATCHING FEATURES\n");    matching_features();
     std::printf("TEST CAMERA TO WORLD\n");      camera_to_world();
     std::printf("TEST FIRST FRAME\n");          first_frame_contract();
     std::printf("TEST STREAMING\n");            streaming_matches_sync();

@@ -227,7 +227,7 @@ int hc_pnp_ransac(const float* K9, const float* uv, const float* X3, int n, doub
                 Us[2 * i + 1] = uv[2 * idx[i] + 1];
             }
             static EpnpWork w;
-            if (!epnp5_solve<1, SerialRedD>(w, K, Xs, Us, 0, P)) P.t[0] = NAN;
+            if (!epnp5_solve<1, 1, SerialRedD>(w, K, Xs, Us, 0, 0, P)) P.t[0] = NAN;
         } else {
             SetEval ev{X3, uv, idx, 5, K};
             pnp_refine_lm(P, ev, 20);
@@ -272,7 +272,7 @@ int hc_epnp5(const float* K9, const float* uv, const float* X3, double* R, doubl
     Intrinsics K{K9[0], K9[4], K9[2], K9[5]};
     static EpnpWork w;
     Pose P;
-    const bool ok = epnp5_solve<1, SerialRedD>(w, K, X3, uv, 0, P);
+    const bool ok = epnp5_solve<1, 1, SerialRedD>(w, K, X3, uv, 0, 0, P);
     memcpy(R, P.R, sizeof(double) * 9);
     memcpy(t, P.t, sizeof(double) * 3);
     return ok ? 1 : 0;

@@ -57,6 +57,12 @@ def test_cli_builds_and_decodes_like_imread(tmp_path):
         assert np.array_equal(read_ppm(tmp_path / "o.ppm"), cv2.imread(str(tmp_path / name), cv2.IMREAD_COLOR)), name
     r = subprocess.run([EXE, "--dump-image", str(tmp_path / "missing.png"), str(tmp_path / "o.ppm")], capture_output=True)
     assert r.returncode != 0
+    # --gray: cv::cvtColor(BGR2GRAY) bit for bit (15-bit fixed point), on a real frame and on random colours
+    cv2.imwrite(str(tmp_path / "rand.png"), rng.integers(0, 256, (64, 96, 3), dtype=np.uint8))
+    for path in (src, tmp_path / "rand.png"):
+        subprocess.run([EXE, "--dump-gray", str(path), str(tmp_path / "g_out.pgm")], check=True)
+        got = cv2.imread(str(tmp_path / "g_out.pgm"), cv2.IMREAD_UNCHANGED)
+        assert np.array_equal(got, cv2.cvtColor(cv2.imread(str(path)), cv2.COLOR_BGR2GRAY)), path
 
 
 @pytest.mark.skipif(has_gpu(), reason="only meaningful without a GPU")

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 from oracle import ref_cv2 as O
-from oracle import synth
+import synthdata as synth
 
 u8p, fp, dp, ip = C.POINTER(C.c_uint8), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_int)
 
@@ -149,17 +149,42 @@ def test_pnp_reference_known_answer(hostcores):   # main.cpp:211-264
     assert np.abs(R - np.array([[0, 1, 0], [-1, 0, 0], [0, 0, 1]], float)).max() < 1e-8
 
 
+def test_epnp_hypothesis_is_bit_identical_to_opencv(hostcores):
+    """One RANSAC hypothesis = cv::solvePnP(SOLVEPNP_EPNP) on 5 points.  svo_epnp.cuh restates OpenCV's one-sided
+    Jacobi SVD and epnp.cpp operation for operation, so even the samples whose 2-D null-space basis is decided by
+    rounding noise must give the same pose: translation within 1e-12 (measured: identical doubles)."""
+    import cv2
+    hostcores.hc_epnp5.argtypes = [fp, fp, fp, dp, dp]
+    rng = np.random.default_rng(11)
+    Pl, _ = synth.projection_matrices("cli")
+    K = np.ascontiguousarray(Pl[:, :3], np.float32)
+    worst = 0.0
+    for trial in range(300):
+        X = np.stack([rng.uniform(-3, 3, 5), rng.uniform(-1, 1, 5), rng.uniform(1.5, 20, 5)], 1).astype(np.float32)
+        Rm, _ = cv2.Rodrigues(rng.normal(0, 0.02, 3))
+        Xc = (Rm @ X.astype(np.float64).T).T + rng.normal(0, 0.05, 3)
+        uv = (Xc[:, :2] / Xc[:, 2:]) * np.array([K[0, 0], K[1, 1]]) + np.array([K[0, 2], K[1, 2]])
+        uv = (uv + rng.normal(0, [0.0, 0.3, 3.0][trial % 3], uv.shape)).astype(np.float32)   # exact / noisy / gross
+        ok, rv, tv = cv2.solvePnP(X.reshape(-1, 1, 3), uv.reshape(-1, 1, 2), K, np.zeros((4, 1), np.float32),
+                                  flags=cv2.SOLVEPNP_EPNP)
+        R, t = np.zeros(9), np.zeros(3)
+        assert hostcores.hc_epnp5(P(K, fp), P(uv, fp), P(X, fp), P(R, dp), P(t, dp))
+        Rc, _ = cv2.Rodrigues(rv)
+        worst = max(worst, np.abs(t - tv.ravel()).max(), np.abs(R.reshape(3, 3) - Rc).max())
+    assert worst < 1e-12, worst
+
+
 def test_pnp_ransac_matches_opencv(hostcores):
-    """Replaying OpenCV's sample stream gives (near-)identical inlier sets; pose within the stated
-    1e-3 rad / 1e-3 relative translation whenever the inlier sets agree."""
+    """cameraToWorld (vo.cpp:282-313): OpenCV's sample stream, EPnP hypotheses, adaptive stop and LM refit are all
+    replayed, so on the same inputs the inlier set is IDENTICAL and the pose agrees far inside north_star's
+    1e-3 rad / 1e-3 relative translation -- with 12 % gross outliers and 0.2 px noise in the data."""
     import cv2
     rng = np.random.default_rng(4)
     Pl, _ = synth.projection_matrices("cli")
     K = Pl[:, :3]
     n = 1500
     X3 = np.stack([rng.uniform(-3, 3, n), rng.uniform(-1, 1, n), rng.uniform(1.5, 20, n)], 1).astype(np.float32)
-    same = 0
-    for trial in range(8):
+    for trial in range(12):
         rv, tt = rng.normal(0, 0.01, 3), rng.normal(0, 0.03, 3)
         Rm, _ = cv2.Rodrigues(rv)
         Xc = (Rm @ X3.astype(np.float64).T).T + tt
@@ -171,14 +196,10 @@ def test_pnp_ransac_matches_opencv(hostcores):
         inl, ok, R, t = host_pnp(hostcores, K, uv, X3, np.eye(3), np.zeros(3))
         ri, rok, rR, rt = O.camera_to_world(K, uv, X3, np.eye(3), np.zeros((3, 1)))
         assert ok and rok
-        assert len(set(inl) ^ set(ri)) <= 0.01 * n
+        assert np.array_equal(inl, ri), (trial, len(set(inl) ^ set(ri)))
         dR = np.linalg.norm(cv2.Rodrigues(R @ rR.T)[0])
         dt = np.linalg.norm(t - rt.ravel()) / np.linalg.norm(rt)
-        assert dR < 1e-3 and dt < 2e-2
-        if len(set(inl) ^ set(ri)) == 0:
-            same += 1
-            assert dR < 1e-6 and dt < 1e-6
-    assert same >= 4
+        assert dR < 1e-6 and dt < 1e-6, (trial, dR, dt)
 
 
 def test_bucket_key_order(hostcores):

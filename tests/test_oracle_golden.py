@@ -126,3 +126,38 @@ def test_camera_to_world():   # main.cpp:211-264
     assert ok and len(inl) == 27
     assert abs(t[0, 0]) < 1e-6 and abs(t[1, 0]) < 1e-6 and abs(t[2, 0] - 1) < 1e-6
     assert np.abs(R - np.array([[0, 1, 0], [-1, 0, 0], [0, 0, 1]], float)).max() < 1e-8
+
+
+def test_oracle_pose_moves_when_one_feature_is_dropped():
+    """Why the pipeline pose bar is stated per matched set (tests/test_gpu_pipeline.py::check): cv2.solvePnPRansac
+    itself, as the reference calls it (vo.cpp:301-304), is not stable to 1e-3 when ONE of ~2000 matched features is
+    removed -- the fixed-seed sample stream indexes the array, so every later 5-point sample changes.  Measured on
+    the oracle alone: a large share of the single-feature drops moves the translation by more than 1e-3 relative
+    (up to ~2e-2), while 1e-4 px noise on the SAME set moves it by < 1e-4."""
+    import cv2
+    import synthdata as synth
+    from oracle import ref_cv2 as O
+    cv2.setNumThreads(0)
+    seq = synth.make_sequence(n_frames=5, seed=0)
+    vo = O.RefVO(seq.Pl, seq.Pr)
+    rng = np.random.default_rng(0)
+    drop, jitter = [], []
+    for L, R in seq.frames():
+        Rg, tg = vo.R.copy(), vo.t.copy()
+        vo.stereo_callback(L, R)
+        tp = vo.taps
+        if tp.X3 is None:
+            continue
+        for _ in range(8):
+            m = np.ones(len(tp.pL1), bool)
+            m[rng.integers(len(m))] = False
+            _, ok, _, t1 = O.camera_to_world(vo.K, tp.pL1[m], tp.X3[m], Rg, tg)
+            drop.append(np.linalg.norm(t1 - tp.t) / np.linalg.norm(tp.t))
+            noisy = (tp.pL1 + rng.normal(0, 1e-4, tp.pL1.shape)).astype(np.float32)
+            _, ok, _, t2 = O.camera_to_world(vo.K, noisy, tp.X3, Rg, tg)
+            jitter.append(np.linalg.norm(t2 - tp.t) / np.linalg.norm(tp.t))
+    drop, jitter = np.array(drop), np.array(jitter)
+    print(f"oracle: one feature dropped -> dt > 1e-3 in {(drop > 1e-3).mean():.0%} of the trials, max {drop.max():.1e}; "
+          f"same set + 1e-4 px noise -> max {jitter.max():.1e}")
+    assert jitter.max() < 1e-3
+    assert (drop > 1e-3).mean() > 0.05 and drop.max() < 5e-2
