@@ -148,6 +148,16 @@ struct SerialRed {
     // exact integer sums of the two mismatch accumulators, converted to float32 (round to nearest)
     static SVO_HD void sum2f(long long a, long long b, bool, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
     static SVO_HD void sync() {}
+    // float32 window sums in OpenCV's order (cv_lk_sum_prod / cv_lk_sum_b below); one lane holds all 100 pixels
+    static inline float cv_sum_prod(const int* a, const int* b, int);
+    static inline void cv_sum_b(const int* p1, const int* p2, int, float& b1, float& b2);
+    // totals of the products and of their absolute values: below 2^24 the float32 sums are exact in any order
+    static SVO_HD bool sum_b_exact(long long s1, long long s2, long long a1, long long a2, float& b1, float& b2) {
+        if (a1 > (1 << 24) || a2 > (1 << 24)) return false;
+        b1 = (float)s1;
+        b2 = (float)s2;
+        return true;
+    }
 };
 
 // cvRound(float): round half to even.
@@ -333,6 +343,55 @@ SVO_HD int lk_stage_i(const LkLevel& I, int x0, int y0, int lane, uint8_t* ip) {
     return 0;
 }
 
+// ---- float32 sums in the order cv::calcOpticalFlowPyrLK's SIMD128 code forms them (lkpyramid.cpp, winSize 10, cn 1):
+// per window row the first 8 pixels go through 4-lane float accumulators, pixels 8 and 9 through a scalar float
+// accumulator; the lanes are folded at the end.  Inputs: row-major 10 x 10 integer arrays.
+SVO_HD float cv_lk_reduce4(const float* q) { return fadd(fadd(q[0], q[2]), fadd(q[1], q[3])); }
+// sum a[s] * b[s]: lane l accumulates pixels l and l + 4 of every row (float products), scalar tail pixels 8, 9
+SVO_HD float cv_lk_sum_prod(const int* a, const int* b) {
+    float q[4] = {0.f, 0.f, 0.f, 0.f}, tail = 0.f;
+    for (int y = 0; y < SVO_LK_WIN; ++y) {
+        for (int h = 0; h < 2; ++h)
+            for (int l = 0; l < 4; ++l) {
+                const int sidx = y * SVO_LK_WIN + 4 * h + l;
+                q[l] = fadd(q[l], fmul((float)a[sidx], (float)b[sidx]));
+            }
+        for (int x = 8; x < SVO_LK_WIN; ++x) {
+            const int sidx = y * SVO_LK_WIN + x;
+            tail = fadd(tail, (float)(a[sidx] * b[sidx]));
+        }
+    }
+    return fadd(tail, cv_lk_reduce4(q));
+}
+// mismatch vector: b1 = sum diff * Ix, b2 = sum diff * Iy with OpenCV's pairing (the products of pixels x and
+// x + 4 of a row are added as int32 before the conversion to float).  p1 / p2: the integer products per pixel.
+SVO_HD void cv_lk_sum_b(const int* p1, const int* p2, float& b1, float& b2) {
+    float qb0[4] = {0.f, 0.f, 0.f, 0.f}, qb1[4] = {0.f, 0.f, 0.f, 0.f}, t1 = 0.f, t2 = 0.f;
+    for (int y = 0; y < SVO_LK_WIN; ++y) {
+        const int* gx = p1 + y * SVO_LK_WIN;
+        const int* gy = p2 + y * SVO_LK_WIN;
+        qb0[0] = fadd(qb0[0], (float)(gx[0] + gx[4]));
+        qb0[1] = fadd(qb0[1], (float)(gy[0] + gy[4]));
+        qb0[2] = fadd(qb0[2], (float)(gx[1] + gx[5]));
+        qb0[3] = fadd(qb0[3], (float)(gy[1] + gy[5]));
+        qb1[0] = fadd(qb1[0], (float)(gx[2] + gx[6]));
+        qb1[1] = fadd(qb1[1], (float)(gy[2] + gy[6]));
+        qb1[2] = fadd(qb1[2], (float)(gx[3] + gx[7]));
+        qb1[3] = fadd(qb1[3], (float)(gy[3] + gy[7]));
+        for (int x = 8; x < SVO_LK_WIN; ++x) {
+            t1 = fadd(t1, (float)gx[x]);
+            t2 = fadd(t2, (float)gy[x]);
+        }
+    }
+    float sv[4];
+    for (int l = 0; l < 4; ++l) sv[l] = fadd(qb0[l], qb1[l]);
+    b1 = fadd(t1, fadd(sv[0], sv[2]));
+    b2 = fadd(t2, fadd(sv[1], sv[3]));
+}
+
+inline float SerialRed::cv_sum_prod(const int* a, const int* b, int) { return cv_lk_sum_prod(a, b); }
+inline void SerialRed::cv_sum_b(const int* p1, const int* p2, int, float& b1, float& b2) { cv_lk_sum_b(p1, p2, b1, b2); }
+
 // Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
 // the same scalar control flow; window pixels are distributed by LkMap; Red sums across lanes).
 // Returns status (1 = tracked) and writes the output position.
@@ -421,7 +480,6 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
 
         // ---- template window: Ival (x32), Ix, Iy (bilinear), structure tensor
         int Iv[SLOTS], Ixv[SLOTS], Iyv[SLOTS];
-        int sA11 = 0, sA12 = 0, sA22 = 0;
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) {
             const uint8_t* p = sc.ipatch + offI[s] + xo;
@@ -433,12 +491,11 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             Iv[s] = val[s] ? (int)(short)iv : 0;
             Ixv[s] = val[s] ? (int)(short)ix : 0;
             Iyv[s] = val[s] ? (int)(short)iy : 0;
-            sA11 += Ixv[s] * Ixv[s]; sA12 += Ixv[s] * Iyv[s]; sA22 += Iyv[s] * Iyv[s];
         }
-        sA11 = Red::sum(sA11); sA12 = Red::sum(sA12); sA22 = Red::sum(sA22);
-        const float A11 = fmul((float)sA11, FLT_SCALE);
-        const float A12 = fmul((float)sA12, FLT_SCALE);
-        const float A22 = fmul((float)sA22, FLT_SCALE);
+        // OpenCV accumulates the structure tensor in float32 (4 SIMD lanes + a scalar tail): same order, same roundings
+        const float A11 = fmul(Red::cv_sum_prod(Ixv, Ixv, lane), FLT_SCALE);
+        const float A12 = fmul(Red::cv_sum_prod(Ixv, Iyv, lane), FLT_SCALE);
+        const float A22 = fmul(Red::cv_sum_prod(Iyv, Iyv, lane), FLT_SCALE);
         float D = fsub(fmul(A11, A22), fmul(A12, A12));
         const float dA = fsub(A11, A22);
         const float disc = fadd(fmul(dA, dA), fmul(fmul(4.f, A12), A12));
@@ -448,9 +505,6 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             continue;
         }
         D = 1.f / D;
-        // |sum diff * Ix| <= 8160 * sum |Ix| <= 8160 * 10 * sqrt(sum Ix^2): below 2^31 the plain 32-bit warp sum
-        // of the mismatch vector cannot overflow and needs no per-iteration check
-        const bool small_grad = sA11 < 690000000 && sA22 < 690000000;
         // iteration-invariant part of the window test: (inx, iny) inside the staged patch AND not fully outside
         // the level  <=>  0 <= inx - lox <= rx, 0 <= iny - loy <= ry   (rx / ry < 0: never)
         int lox = imax(jx0, -SVO_LK_WIN), loy = imax(jy0, -SVO_LK_WIN);
@@ -483,17 +537,25 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             lk_weights(fsub(cx, (float)inx), fsub(cy, (float)iny), iw00, iw01, iw10, iw11);
             const unsigned jt = pack_weights(iw00, iw01), jb = pack_weights(iw10, iw11);
             const unsigned short* jbase = sc.jp + (iny - jy0) * SVO_LK_JC + (inx - jx0);
-            typename LkAcc<LANES>::type sb1 = 0, sb2 = 0;   // <= 4 pixels per lane fit 32 bits
+            // mismatch vector.  OpenCV sums it in float32 in a fixed order; while the sum of the absolute products stays
+            // below 2^24 every partial sum is an exactly representable integer, so the order is irrelevant and the plain
+            // integer total is the same number.  Otherwise the sums are formed in OpenCV's order (Red::cv_sum_b).
+            int p1[SLOTS], p2[SLOTS];
+            typename LkAcc<LANES>::type sb1 = 0, sb2 = 0, sa1 = 0, sa2 = 0;   // <= 4 pixels per lane fit 32 bits
 #pragma unroll
             for (int s = 0; s < SLOTS; ++s) {
                 const unsigned short* q = jbase + offJ[s];
                 const int v = dp2a_lo_su(jb, q[SVO_LK_JC], dp2a_lo_su(jt, q[0], 1 << 8));
                 const int diff = (v >> 9) - Iv[s];
-                sb1 += diff * Ixv[s];
-                sb2 += diff * Iyv[s];
+                p1[s] = diff * Ixv[s];
+                p2[s] = diff * Iyv[s];
+                sb1 += p1[s];
+                sb2 += p2[s];
+                sa1 += p1[s] < 0 ? -p1[s] : p1[s];
+                sa2 += p2[s] < 0 ? -p2[s] : p2[s];
             }
             float b1, b2;
-            Red::sum2f(sb1, sb2, small_grad, b1, b2);
+            if (!Red::sum_b_exact(sb1, sb2, sa1, sa2, b1, b2)) Red::cv_sum_b(p1, p2, lane, b1, b2);
             b1 = fmul(b1, FLT_SCALE);
             b2 = fmul(b2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);

@@ -29,18 +29,58 @@ struct WarpRed {
         const unsigned hi = __reduce_add_sync(0xffffffffu, u >> 16);
         return ((long long)hi << 16) + (long long)lo - (32ll << 27);
     }
-    // exact sums of the two per-lane mismatch accumulators as float32.  A lane holds <= 4 pixels (|v| < 2^27);
-    // when every lane is below 2^26 the warp total fits 32 bits and one REDUX each is exact, otherwise the
-    // split 64-bit path runs (warp-uniform branch).
-    // `small`: the caller proved that the totals fit 32 bits (warp-uniform)
-    static __device__ __forceinline__ void sum2f(int a, int b, bool small, float& fa, float& fb) {
-        if (!small && __any_sync(0xffffffffu, max(abs(a), abs(b)) >= (1 << 26))) {
-            fa = (float)sum64(a);
-            fb = (float)sum64(b);
-        } else {
-            fa = (float)__reduce_add_sync(0xffffffffu, a);
-            fb = (float)__reduce_add_sync(0xffffffffu, b);
+    // ---- float32 window sums in the order cv::calcOpticalFlowPyrLK forms them (svo_core.cuh cv_lk_sum_prod /
+    // cv_lk_sum_b are the serial statements).  Window pixel (row y, column x) lives in lane (y % 3) * 10 + x, slot
+    // y / 3 (LkMap<32>).  OpenCV's five accumulators -- SIMD lanes 0..3 (pixels l and l + 4 of every row) and the
+    // scalar tail (pixels 8, 9) -- are run as sequential float32 chains in lanes 0..4, fed by shuffles that do not
+    // depend on the chain; the fold at the end is OpenCV's.
+    static __device__ __forceinline__ float fold5(float acc) {
+        const float q0 = __shfl_sync(0xffffffffu, acc, 0), q1 = __shfl_sync(0xffffffffu, acc, 1),
+                    q2 = __shfl_sync(0xffffffffu, acc, 2), q3 = __shfl_sync(0xffffffffu, acc, 3),
+                    tail = __shfl_sync(0xffffffffu, acc, 4);
+        return __fadd_rn(tail, __fadd_rn(__fadd_rn(q0, q2), __fadd_rn(q1, q3)));
+    }
+    static __device__ __forceinline__ float cv_sum_prod(const int* a, const int* b, int lane) {
+        float f[4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) f[s] = __fmul_rn((float)a[s], (float)b[s]);   // slots without a pixel hold zeros
+        const int c0 = lane < 4 ? lane : 8, step = lane < 4 ? 4 : 1;
+        float acc = 0.f;
+#pragma unroll
+        for (int y = 0; y < 10; ++y) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, f[y / 3], (y % 3) * 10 + c0 + h * step));
         }
+        return fold5(acc);
+    }
+    // p1 / p2: the integer products diff * Ix, diff * Iy of the lane's (up to) four pixels.  Chains 0..3 add the
+    // products of pixels l and l + 4 as int32 before the conversion (v_dotprod), the tail converts each product.
+    static __device__ __forceinline__ void cv_sum_b(const int* p1, const int* p2, int lane, float& b1, float& b2) {
+        const bool main_chain = lane < 4;
+        const int c0 = main_chain ? lane : 8, step = main_chain ? 4 : 1;
+        float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+        for (int y = 0; y < 10; ++y) {
+            const int s0 = (y % 3) * 10 + c0, s1 = s0 + step;
+            const int a0 = __shfl_sync(0xffffffffu, p1[y / 3], s0), a1 = __shfl_sync(0xffffffffu, p1[y / 3], s1);
+            const int e0 = __shfl_sync(0xffffffffu, p2[y / 3], s0), e1 = __shfl_sync(0xffffffffu, p2[y / 3], s1);
+            // main chains: one float per pair sum; tail: the two products one after the other (x + 0.f == x)
+            m1 = __fadd_rn(__fadd_rn(m1, main_chain ? (float)(a0 + a1) : (float)a0), main_chain ? 0.f : (float)a1);
+            m2 = __fadd_rn(__fadd_rn(m2, main_chain ? (float)(e0 + e1) : (float)e0), main_chain ? 0.f : (float)e1);
+        }
+        // chains 0..3 = qb0[0], qb0[2], qb1[0], qb1[2] (pixels 0|4, 1|5, 2|6, 3|7): b = tail + ((c0 + c2) + (c1 + c3))
+        b1 = fold5(m1);
+        b2 = fold5(m2);
+    }
+    // totals of the products and of their absolute values: while the absolute total stays below 2^24 every float32
+    // partial sum OpenCV forms is an exactly representable integer, i.e. the plain integer total
+    static __device__ __forceinline__ bool sum_b_exact(int s1, int s2, int a1, int a2, float& b1, float& b2) {
+        const unsigned t1 = __reduce_add_sync(0xffffffffu, (unsigned)a1), t2 = __reduce_add_sync(0xffffffffu, (unsigned)a2);
+        if (t1 > (1u << 24) || t2 > (1u << 24)) return false;
+        b1 = (float)__reduce_add_sync(0xffffffffu, s1);
+        b2 = (float)__reduce_add_sync(0xffffffffu, s2);
+        return true;
     }
     // any 64-bit per-lane value (multi-channel windows)
     static __device__ __forceinline__ long long sum64g(long long v) {

@@ -70,9 +70,9 @@ def test_lk_matches_opencv(hostcores, run1):
         pts = np.concatenate([pts + rng.uniform(-0.5, 0.5, pts.shape).astype(np.float32), border])
         o, s = host_lk(hostcores, I, J, pts)
         ro, rs = O.lk_leg(I, J, pts)
-        assert (s == rs).mean() >= 0.99
-        d = np.abs(o - ro).max(1)
-        assert (d <= 0.05).mean() >= 0.99
+        # north_star's bar is 0.05 px on >= 99 %; the window sums follow OpenCV's float32 order, so: identical bits
+        assert np.array_equal(s, rs)
+        assert np.array_equal(o, ro), (np.abs(o - ro).max(), (o != ro).any(1).mean())
 
 
 def host_lk_cn(hc, I, J, pts):
