@@ -140,6 +140,9 @@ SVO_HD void lk_config_finish(LkConfig& c) {
     c.eps_hi = (float)(c.eps_sq * (1.0 + 1e-6));
 }
 
+#ifdef SVO_LK_COUNT
+static long long g_lk_count[3];
+#endif
 // Reduction policy for LANES == 1 (host unit tests).
 struct SerialRed {
     static SVO_HD int sum(int v) { return v; }
@@ -149,11 +152,16 @@ struct SerialRed {
     static SVO_HD void sum2f(long long a, long long b, bool, float& fa, float& fb) { fa = (float)a; fb = (float)b; }
     static SVO_HD void sync() {}
     // float32 window sums in OpenCV's order (cv_lk_sum_prod / cv_lk_sum_b below); one lane holds all 100 pixels
-    static inline float cv_sum_prod(const int* a, const int* b, int);
-    static inline void cv_sum_b(const int* p1, const int* p2, int, float& b1, float& b2);
-    // totals of the products and of their absolute values: below 2^24 the float32 sums are exact in any order
-    static SVO_HD bool sum_b_exact(long long s1, long long s2, long long a1, long long a2, float& b1, float& b2) {
-        if (a1 > (1 << 24) || a2 > (1 << 24)) return false;
+    static inline void cv_sum_prod3(const int* ix, const int* iy, int, unsigned*, float& a11, float& a12, float& a22);
+    static inline void cv_sum_b(const int* p1, const int* p2, int, unsigned*, float& b1, float& b2);
+    // totals of the products and of their absolute values (both components together): below 2^24 the float32 sums
+    // are exact in any order
+    static SVO_HD bool sum_b_exact(long long s1, long long s2, long long a12, float& b1, float& b2) {
+#ifdef SVO_LK_COUNT
+        ++g_lk_count[a12 > (1 << 24) ? 1 : 0];
+        if (a12 > (1 << 24) && a12 <= (1 << 26)) ++g_lk_count[2];
+#endif
+        if (a12 > (1 << 24)) return false;
         b1 = (float)s1;
         b2 = (float)s2;
         return true;
@@ -218,6 +226,7 @@ struct LkScratch {
     short dxp[SVO_LK_DW * SVO_LK_DP];                      // Scharr dx of the 11x11 window positions
     short dyp[SVO_LK_DW * SVO_LK_DP];                      // Scharr dy
     unsigned short jp[SVO_LK_JR * SVO_LK_JC];              // J patch as horizontal pixel pairs p(x) | p(x+1) << 8
+    unsigned stage[3 * SVO_LK_NPIX];                       // window products regrouped into OpenCV's accumulation chains
 };
 
 SVO_HD void lk_weights(float a, float b, int& iw00, int& iw01, int& iw10, int& iw11) {
@@ -389,8 +398,12 @@ SVO_HD void cv_lk_sum_b(const int* p1, const int* p2, float& b1, float& b2) {
     b2 = fadd(t2, fadd(sv[1], sv[3]));
 }
 
-inline float SerialRed::cv_sum_prod(const int* a, const int* b, int) { return cv_lk_sum_prod(a, b); }
-inline void SerialRed::cv_sum_b(const int* p1, const int* p2, int, float& b1, float& b2) { cv_lk_sum_b(p1, p2, b1, b2); }
+inline void SerialRed::cv_sum_prod3(const int* ix, const int* iy, int, unsigned*, float& a11, float& a12, float& a22) {
+    a11 = cv_lk_sum_prod(ix, ix);
+    a12 = cv_lk_sum_prod(ix, iy);
+    a22 = cv_lk_sum_prod(iy, iy);
+}
+inline void SerialRed::cv_sum_b(const int* p1, const int* p2, int, unsigned*, float& b1, float& b2) { cv_lk_sum_b(p1, p2, b1, b2); }
 
 // Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
 // the same scalar control flow; window pixels are distributed by LkMap; Red sums across lanes).
@@ -493,9 +506,11 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             Iyv[s] = val[s] ? (int)(short)iy : 0;
         }
         // OpenCV accumulates the structure tensor in float32 (4 SIMD lanes + a scalar tail): same order, same roundings
-        const float A11 = fmul(Red::cv_sum_prod(Ixv, Ixv, lane), FLT_SCALE);
-        const float A12 = fmul(Red::cv_sum_prod(Ixv, Iyv, lane), FLT_SCALE);
-        const float A22 = fmul(Red::cv_sum_prod(Iyv, Iyv, lane), FLT_SCALE);
+        float A11, A12, A22;
+        Red::cv_sum_prod3(Ixv, Iyv, lane, sc.stage, A11, A12, A22);
+        A11 = fmul(A11, FLT_SCALE);
+        A12 = fmul(A12, FLT_SCALE);
+        A22 = fmul(A22, FLT_SCALE);
         float D = fsub(fmul(A11, A22), fmul(A12, A12));
         const float dA = fsub(A11, A22);
         const float disc = fadd(fmul(dA, dA), fmul(fmul(4.f, A12), A12));
@@ -555,7 +570,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
                 sa2 += p2[s] < 0 ? -p2[s] : p2[s];
             }
             float b1, b2;
-            if (!Red::sum_b_exact(sb1, sb2, sa1, sa2, b1, b2)) Red::cv_sum_b(p1, p2, lane, b1, b2);
+            if (!Red::sum_b_exact(sb1, sb2, sa1 + sa2, b1, b2)) Red::cv_sum_b(p1, p2, lane, sc.stage, b1, b2);
             b1 = fmul(b1, FLT_SCALE);
             b2 = fmul(b2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);

@@ -46,6 +46,7 @@ SVO_HD double cv_hypot(double a, double b) {
 struct SerialRedD {
     static SVO_HD void sync() {}
     static SVO_HD void sync_all() {}
+    static SVO_HD bool any(bool v) { return v; }
     static SVO_HD double sumd(double v) { return v; }
 };
 
@@ -233,6 +234,192 @@ SVO_HD void cv_jacobi_svd(double* At, double* Vt, int ldv, double* W, int* perm,
     Red::sync();
 }
 
+// ---- the same algorithm for the larger systems (12 x 12, 6 x {3, 4, 5}), as a wavefront --------------------------
+// OpenCV visits the pairs (0,1), (0,2), ..., (n-2,n-1) one after the other, but pair (i, j) only reads and writes rows
+// i and j: it depends on (i, j-1) [row i] and (i-1, j) [row j] and on nothing else.  Executing every pair as soon as
+// its two predecessors are done -- step i + j - 1 of its sweep, sweeps n steps apart -- gives each pair exactly the
+// operands of the sequential order, hence bit-identical results, in ~n steps per sweep instead of n (n - 1) / 2.
+// One lane runs one pair of the current step (<= 8 pairs are ever concurrent), serially and branch-free through the
+// c / s computation so that the lanes stay converged.  A sweep is only known to be the last one (no rotation) when
+// it ends; the pairs of the following sweep that have run by then all skipped (their rows had not changed since
+// they were skipped the sweep before), so running them is harmless.
+// Row stride LD (13 for the 12 x 12: the concurrent lanes then read distinct shared-memory banks).
+template <int M, int LD>
+SVO_HD bool cv_jacobi_pair(double* At, double* Vt, int ldv, double* W, int i, int j, int n) {
+    const double eps = DBL_EPSILON * 10, eps2 = eps * eps;
+    double ai[M], aj[M];
+#pragma unroll
+    for (int k = 0; k < M; ++k) {
+        ai[k] = At[i * LD + k];
+        aj[k] = At[j * LD + k];
+    }
+    const double wi = W[i], wj = W[j];
+    double p = 0;
+#pragma unroll
+    for (int k = 0; k < M; ++k) p += ai[k] * aj[k];
+    // |p| <= eps * sqrt(wi * wj), decided from the squares unless it is a close call
+    const double lhs = p * p, rhs = eps2 * (wi * wj);
+    bool skip;
+    if (lhs > rhs * 1.000001 && rhs > 1e-280) skip = false;
+    else if (lhs < rhs * 0.999999 && lhs > 1e-280) skip = true;
+    else skip = fabs(p) <= eps * sqrt(wi * wj);
+    if (skip) return false;
+    p *= 2;
+    const double beta = wi - wj;
+    // gamma = cv_hypot(p, beta): |p| != 0 here, so the larger magnitude is positive
+    const double pa = fabs(p), pb = fabs(beta);
+    const double big = pa > pb ? pa : pb, small = pa > pb ? pb : pa;
+    const double q = small / big;
+    const double gamma = big * sqrt(1 + q * q);
+    const bool neg = beta < 0;
+    const double num = neg ? (gamma - beta) * 0.5 : (gamma + beta), den = neg ? gamma : gamma * 2;
+    const double r = sqrt(num / den);
+    const double o = p / (gamma * r * 2);
+    const double c = neg ? o : r, s = neg ? r : o;
+    double a = 0, b = 0;
+#pragma unroll
+    for (int k = 0; k < M; ++k) {
+        const double t0 = c * ai[k] + s * aj[k];
+        const double t1 = -s * ai[k] + c * aj[k];
+        At[i * LD + k] = t0;
+        At[j * LD + k] = t1;
+        a += t0 * t0;
+        b += t1 * t1;
+    }
+    W[i] = a;
+    W[j] = b;
+    if (Vt) {
+        double* Vi = Vt + i * ldv;
+        double* Vj = Vt + j * ldv;
+        for (int k = 0; k < n; ++k) {
+            const double x = Vi[k], y = Vj[k];
+            Vi[k] = c * x + s * y;
+            Vj[k] = -s * x + c * y;
+        }
+    }
+    return true;
+}
+
+template <int M, int N, int LD, int LANES, class Red>
+SVO_HD void cv_jacobi_svd_wave(double* At, double* Vt, int ldv, double* W, int* perm, int lane) {
+    constexpr int n = N, LAST = 2 * N - 4;   // step of the last pair (n-2, n-1) within its sweep; sweeps start n steps apart
+    const double eps = DBL_EPSILON * 10, minval = DBL_MIN;
+    const int max_iter = M > 30 ? M : 30;
+    if (Vt)
+        for (int e = lane; e < n * n; e += LANES) Vt[(e / n) * ldv + (e % n)] = (e / n == e % n) ? 1.0 : 0.0;
+    for (int i = lane; i < n; i += LANES) {
+        double sd = 0;
+#pragma unroll
+        for (int k = 0; k < M; ++k) {
+            const double t = At[i * LD + k];
+            sd += t * t;
+        }
+        W[i] = sd;
+    }
+    Red::sync();
+    int cur = 0;
+    bool chg_cur = false, chg_next = false;
+    for (int t = 0;; ++t) {
+        const int r0 = t - n * cur, r1 = r0 - n;
+        const int lo0 = r0 + 2 - n > 0 ? r0 + 2 - n : 0, c0 = (r0 >> 1) - lo0 + 1;
+        const bool next_ok = r1 >= 0 && cur + 1 < max_iter;
+        const int lo1 = r1 + 2 - n > 0 ? r1 + 2 - n : 0, c1 = next_ok ? (r1 >> 1) - lo1 + 1 : 0;
+        bool rot_cur = false, rot_next = false;
+        for (int q = lane; q < c0 + c1; q += LANES) {
+            const bool in_cur = q < c0;
+            const int i = in_cur ? lo0 + q : lo1 + (q - c0);
+            const int j = (in_cur ? r0 : r1) + 1 - i;
+            const bool rot = cv_jacobi_pair<M, LD>(At, Vt, ldv, W, i, j, n);
+            rot_cur = rot_cur || (rot && in_cur);
+            rot_next = rot_next || (rot && !in_cur);
+        }
+        Red::sync();
+        chg_cur = Red::any(rot_cur) || chg_cur;
+        chg_next = Red::any(rot_next) || chg_next;
+        if (r0 == LAST) {
+            if (!chg_cur || cur + 1 >= max_iter) break;
+            ++cur;
+            chg_cur = chg_next;
+            chg_next = false;
+        }
+    }
+    // singular values (the cached squared norms ARE the sequential sums OpenCV recomputes here), selection sort
+    // (descending) by lane 0, row swaps split over the lanes
+    if (lane == 0) {
+        for (int i = 0; i < n; ++i) W[i] = sqrt(W[i]);
+        for (int i = 0; i < n - 1; ++i) {
+            int j = i;
+            for (int k = i + 1; k < n; ++k)
+                if (W[j] < W[k]) j = k;
+            perm[i] = j;
+            if (i != j) {
+                const double tw = W[i];
+                W[i] = W[j];
+                W[j] = tw;
+            }
+        }
+    }
+    Red::sync();
+    for (int i = 0; i < n - 1; ++i) {
+        const int j = perm[i];
+        if (i != j) {
+            for (int k = lane; k < M; k += LANES) {
+                const double t = At[i * LD + k];
+                At[i * LD + k] = At[j * LD + k];
+                At[j * LD + k] = t;
+            }
+            if (Vt)
+                for (int k = lane; k < n; k += LANES) {
+                    const double t = Vt[i * ldv + k];
+                    Vt[i * ldv + k] = Vt[j * ldv + k];
+                    Vt[j * ldv + k] = t;
+                }
+        }
+    }
+    Red::sync();
+    // left singular vectors: rows scaled by 1 / w; a (numerically exact) zero singular value gets OpenCV's
+    // pseudo-random completion (RNG 0x12345678, two Gram-Schmidt passes) -- lane 0, it practically never runs
+    uint64_t rng = 0x12345678ull;
+    for (int i = 0; i < n; ++i) {
+        double sd = W[i];
+        if (sd <= minval) {
+            Red::sync();   // rows j < i are complete
+            if (lane == 0) {
+                for (int ii = 0; ii < 100 && sd <= minval; ++ii) {
+                    const double val0 = 1. / M;
+                    for (int k = 0; k < M; ++k) At[i * LD + k] = (cv_rng_next(rng) & 256) != 0 ? val0 : -val0;
+                    for (int it = 0; it < 2; ++it)
+                        for (int j = 0; j < i; ++j) {
+                            sd = 0;
+                            for (int k = 0; k < M; ++k) sd += At[i * LD + k] * At[j * LD + k];
+                            double asum = 0;
+                            for (int k = 0; k < M; ++k) {
+                                const double t = At[i * LD + k] - sd * At[j * LD + k];
+                                At[i * LD + k] = t;
+                                asum += fabs(t);
+                            }
+                            asum = asum > eps * 100 ? 1 / asum : 0;
+                            for (int k = 0; k < M; ++k) At[i * LD + k] *= asum;
+                        }
+                    sd = 0;
+                    for (int k = 0; k < M; ++k) {
+                        const double t = At[i * LD + k];
+                        sd += t * t;
+                    }
+                    sd = sqrt(sd);
+                }
+                const double s = sd > minval ? 1 / sd : 0.;
+                for (int k = 0; k < M; ++k) At[i * LD + k] *= s;
+            }   // (the generator state only matters in lane 0)
+            Red::sync();
+            continue;
+        }
+        const double s = 1 / sd;
+        for (int k = lane; k < M; k += LANES) At[i * LD + k] *= s;
+    }
+    Red::sync();
+}
+
 // SVBkSbImpl_<double> (cv::SVD::backSubst): x = V diag(1/w) U^T b, singular values <= 2 eps sum(w) dropped.
 // U is given as Ut (row i = left singular vector i, length M), Vt N x N.  Serial.
 //   vector right-hand side (cv::solve(..., DECOMP_SVD), nb == 1)
@@ -341,8 +528,9 @@ SVO_HD void epnp_qr_solve(double* A, double* b, double* x) {
 }
 
 // ---------------------------------------------------------------------------
+#define SVO_EPNP_LDA 13
 struct EpnpWork {              // per-hypothesis scratch (shared memory on the device)
-    double A[144];             // M^T M -> rows = left singular vectors (ut of epnp::compute_pose)
+    double A[12 * SVO_EPNP_LDA];   // M^T M (row stride 13) -> rows = left singular vectors (ut of epnp::compute_pose)
     double M[120];             // 10 x 12
     double W[12];
     double dv[72];             // [4][6][3]
@@ -387,7 +575,7 @@ SVO_HD double epnp_R_and_t(const EpnpWork& w, const Intrinsics& K, const double*
     for (int i = 0; i < 4; ++i) ccs[i][0] = ccs[i][1] = ccs[i][2] = 0.0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const double* v = w.A + 12 * (11 - i);
+        const double* v = w.A + SVO_EPNP_LDA * (11 - i);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
 #pragma unroll
@@ -466,7 +654,7 @@ SVO_HD void epnp_variant(EpnpWork& w, const Intrinsics& K, int lane) {
     double* Vt = w.vVt[VAR];
     for (int e = lane; e < ncol * 6; e += LANES) At[e] = w.L[(e % 6) * 10 + colmap[VAR][e / 6]];
     Red::sync();
-    cv_jacobi_svd<6, ncol, LANES, Red>(At, Vt, 5, w.vW[VAR], w.vperm[VAR], lane);
+    cv_jacobi_svd_wave<6, ncol, 6, LANES, Red>(At, Vt, 5, w.vW[VAR], w.vperm[VAR], lane);
     double x[5] = {0, 0, 0, 0, 0}, be[4];
     cv_svbksb_vec<6, ncol>(w.vW[VAR], At, Vt, 5, w.rho, x);
     SVO_EPNP_TICK(5)
@@ -583,18 +771,18 @@ SVO_HD bool epnp5_solve(EpnpWork& w, const Intrinsics& K, const float* X, const 
         double s = 0.0;
 #pragma unroll
         for (int r = 0; r < 10; ++r) s += w.M[r * 12 + a] * w.M[r * 12 + b];
-        w.A[e] = s;
+        w.A[a * SVO_EPNP_LDA + b] = s;
     }
     Red::sync_all();
     SVO_EPNP_TICK(2)
-    if (group == 0) cv_jacobi_svd<12, 12, LANES, Red>(w.A, nullptr, 0, w.W, w.perm, lane);
+    if (group == 0) cv_jacobi_svd_wave<12, 12, SVO_EPNP_LDA, LANES, Red>(w.A, nullptr, 0, w.W, w.perm, lane);
     Red::sync_all();
     SVO_EPNP_TICK(3)
     // compute_L_6x10: v[i] = ut row 11 - i
     for (int e = tid; e < 72; e += NT) {   // dv[i][j][k]
         const int i = e / 18, j = (e - i * 18) / 3, k = e - i * 18 - j * 3;
         const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
-        const double* v = w.A + 12 * (11 - i);
+        const double* v = w.A + SVO_EPNP_LDA * (11 - i);
         w.dv[e] = v[3 * pa[j] + k] - v[3 * pb[j] + k];
     }
     Red::sync_all();

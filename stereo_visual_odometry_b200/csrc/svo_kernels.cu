@@ -31,53 +31,83 @@ struct WarpRed {
     }
     // ---- float32 window sums in the order cv::calcOpticalFlowPyrLK forms them (svo_core.cuh cv_lk_sum_prod /
     // cv_lk_sum_b are the serial statements).  Window pixel (row y, column x) lives in lane (y % 3) * 10 + x, slot
-    // y / 3 (LkMap<32>).  OpenCV's five accumulators -- SIMD lanes 0..3 (pixels l and l + 4 of every row) and the
-    // scalar tail (pixels 8, 9) -- are run as sequential float32 chains in lanes 0..4, fed by shuffles that do not
-    // depend on the chain; the fold at the end is OpenCV's.
-    static __device__ __forceinline__ float fold5(float acc) {
-        const float q0 = __shfl_sync(0xffffffffu, acc, 0), q1 = __shfl_sync(0xffffffffu, acc, 1),
-                    q2 = __shfl_sync(0xffffffffu, acc, 2), q3 = __shfl_sync(0xffffffffu, acc, 3),
-                    tail = __shfl_sync(0xffffffffu, acc, 4);
-        return __fadd_rn(tail, __fadd_rn(__fadd_rn(q0, q2), __fadd_rn(q1, q3)));
+    // y / 3 (LkMap<32>).  OpenCV runs five float32 accumulators -- SIMD lanes 0..3 (pixels l and l + 4 of every row)
+    // and a scalar tail (pixels 8, 9) -- so the products are regrouped through shared memory into five chains of 20
+    // consecutive words (chain c: [row y][first | second pixel]) and lane 5 k + c sums chain c of component k
+    // sequentially (one 128-bit load per 4 terms); the fold of the five accumulators is OpenCV's.
+    static __device__ __forceinline__ int chain_slot(int lane, int s) {   // word index of the lane's pixel `s` in its component
+        const int x = lane % 10, y = lane / 10 + 3 * s;
+        return (x < 8 ? (x & 3) : 4) * 20 + y * 2 + (x < 8 ? (x >> 2) : x - 8);
     }
-    static __device__ __forceinline__ float cv_sum_prod(const int* a, const int* b, int lane) {
-        float f[4];
+    static __device__ __forceinline__ bool slot_valid(int lane, int s) { return lane < 30 && lane / 10 + 3 * s < 10; }
+    // acc (lanes 5 k .. 5 k + 4) -> tail + ((q0 + q2) + (q1 + q3)) in lane 5 k
+    static __device__ __forceinline__ float fold5(float acc) {
+        const float q1 = __shfl_down_sync(0xffffffffu, acc, 1), q2 = __shfl_down_sync(0xffffffffu, acc, 2),
+                    q3 = __shfl_down_sync(0xffffffffu, acc, 3), tail = __shfl_down_sync(0xffffffffu, acc, 4);
+        return __fadd_rn(tail, __fadd_rn(__fadd_rn(acc, q2), __fadd_rn(q1, q3)));
+    }
+    static __device__ __forceinline__ void cv_sum_prod3(const int* ix, const int* iy, int lane, unsigned* stage,
+                                                        float& a11, float& a12, float& a22) {
+        float* st = reinterpret_cast<float*>(stage);
+        __syncwarp();
 #pragma unroll
-        for (int s = 0; s < 4; ++s) f[s] = __fmul_rn((float)a[s], (float)b[s]);   // slots without a pixel hold zeros
-        const int c0 = lane < 4 ? lane : 8, step = lane < 4 ? 4 : 1;
+        for (int s = 0; s < 4; ++s)
+            if (slot_valid(lane, s)) {
+                const int o = chain_slot(lane, s);
+                const float fx = (float)ix[s], fy = (float)iy[s];
+                st[o] = __fmul_rn(fx, fx);
+                st[100 + o] = __fmul_rn(fx, fy);
+                st[200 + o] = __fmul_rn(fy, fy);
+            }
+        __syncwarp();
         float acc = 0.f;
+        if (lane < 15) {
+            const float4* src = reinterpret_cast<const float4*>(st + (lane / 5) * 100 + (lane % 5) * 20);
 #pragma unroll
-        for (int y = 0; y < 10; ++y) {
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-                acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, f[y / 3], (y % 3) * 10 + c0 + h * step));
+            for (int i = 0; i < 5; ++i) {
+                const float4 v = src[i];
+                acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v.x), v.y), v.z), v.w);
+            }
         }
-        return fold5(acc);
+        const float r = fold5(acc);
+        a11 = __shfl_sync(0xffffffffu, r, 0);
+        a12 = __shfl_sync(0xffffffffu, r, 5);
+        a22 = __shfl_sync(0xffffffffu, r, 10);
     }
     // p1 / p2: the integer products diff * Ix, diff * Iy of the lane's (up to) four pixels.  Chains 0..3 add the
     // products of pixels l and l + 4 as int32 before the conversion (v_dotprod), the tail converts each product.
-    static __device__ __forceinline__ void cv_sum_b(const int* p1, const int* p2, int lane, float& b1, float& b2) {
-        const bool main_chain = lane < 4;
-        const int c0 = main_chain ? lane : 8, step = main_chain ? 4 : 1;
-        float m1 = 0.f, m2 = 0.f;
+    static __device__ __forceinline__ void cv_sum_b(const int* p1, const int* p2, int lane, unsigned* stage, float& b1,
+                                                    float& b2) {
+        int* st = reinterpret_cast<int*>(stage);
+        __syncwarp();
 #pragma unroll
-        for (int y = 0; y < 10; ++y) {
-            const int s0 = (y % 3) * 10 + c0, s1 = s0 + step;
-            const int a0 = __shfl_sync(0xffffffffu, p1[y / 3], s0), a1 = __shfl_sync(0xffffffffu, p1[y / 3], s1);
-            const int e0 = __shfl_sync(0xffffffffu, p2[y / 3], s0), e1 = __shfl_sync(0xffffffffu, p2[y / 3], s1);
-            // main chains: one float per pair sum; tail: the two products one after the other (x + 0.f == x)
-            m1 = __fadd_rn(__fadd_rn(m1, main_chain ? (float)(a0 + a1) : (float)a0), main_chain ? 0.f : (float)a1);
-            m2 = __fadd_rn(__fadd_rn(m2, main_chain ? (float)(e0 + e1) : (float)e0), main_chain ? 0.f : (float)e1);
+        for (int s = 0; s < 4; ++s)
+            if (slot_valid(lane, s)) {
+                const int o = chain_slot(lane, s);
+                st[o] = p1[s];
+                st[100 + o] = p2[s];
+            }
+        __syncwarp();
+        float acc = 0.f;
+        if (lane < 10) {
+            const int4* src = reinterpret_cast<const int4*>(st + (lane / 5) * 100 + (lane % 5) * 20);
+            const bool pairs = lane % 5 < 4;   // x + 0.f == x: the tail's second term per pixel pair is a real addend
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                const int4 v = src[i];
+                acc = __fadd_rn(__fadd_rn(acc, pairs ? (float)(v.x + v.y) : (float)v.x), pairs ? 0.f : (float)v.y);
+                acc = __fadd_rn(__fadd_rn(acc, pairs ? (float)(v.z + v.w) : (float)v.z), pairs ? 0.f : (float)v.w);
+            }
         }
         // chains 0..3 = qb0[0], qb0[2], qb1[0], qb1[2] (pixels 0|4, 1|5, 2|6, 3|7): b = tail + ((c0 + c2) + (c1 + c3))
-        b1 = fold5(m1);
-        b2 = fold5(m2);
+        const float r = fold5(acc);
+        b1 = __shfl_sync(0xffffffffu, r, 0);
+        b2 = __shfl_sync(0xffffffffu, r, 5);
     }
-    // totals of the products and of their absolute values: while the absolute total stays below 2^24 every float32
-    // partial sum OpenCV forms is an exactly representable integer, i.e. the plain integer total
-    static __device__ __forceinline__ bool sum_b_exact(int s1, int s2, int a1, int a2, float& b1, float& b2) {
-        const unsigned t1 = __reduce_add_sync(0xffffffffu, (unsigned)a1), t2 = __reduce_add_sync(0xffffffffu, (unsigned)a2);
-        if (t1 > (1u << 24) || t2 > (1u << 24)) return false;
+    // totals of the products and of their absolute values (both components together): while the absolute total stays
+    // below 2^24 every float32 partial sum OpenCV forms is an exactly representable integer, i.e. the plain total
+    static __device__ __forceinline__ bool sum_b_exact(int s1, int s2, int a12, float& b1, float& b2) {
+        if (__reduce_add_sync(0xffffffffu, (unsigned)a12) > (1u << 24)) return false;
         b1 = (float)__reduce_add_sync(0xffffffffu, s1);
         b2 = (float)__reduce_add_sync(0xffffffffu, s2);
         return true;
@@ -1451,6 +1481,7 @@ constexpr int HYP_THREADS = 96, HYP_FIRST = 16;
 struct WarpRedD {
     static __device__ __forceinline__ void sync() { __syncwarp(); }
     static __device__ __forceinline__ void sync_all() { __syncthreads(); }
+    static __device__ __forceinline__ bool any(bool v) { return __any_sync(0xffffffffu, v); }
     static __device__ __forceinline__ double sumd(double v) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

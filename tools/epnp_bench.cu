@@ -14,6 +14,7 @@ using namespace svo;
 struct WarpRedD {
     static __device__ __forceinline__ void sync() { __syncwarp(); }
     static __device__ __forceinline__ void sync_all() { __syncthreads(); }
+    static __device__ __forceinline__ bool any(bool v) { return __any_sync(0xffffffffu, v); }
     static __device__ __forceinline__ double sumd(double v) { return v; }
 };
 __global__ void k(const float* X, const float* uv, Intrinsics K, double* out) {
