@@ -12,7 +12,8 @@ FRAMES_PER_STEP consecutive stereo frames through VisualOdometry::stereo_callbac
   e2e   : frames/s through the reference-facing C ABI with pinned HOST images (svo_submit_frame / svo_collect,
           <= 3 frames in flight; H2D copy of every frame, kernels, D2H of every result inside the timed region);
           e2e.sync_per_frame_value is the same through the synchronous svo_process_frame (one sync per frame).
-  N > 1 : one sequence per rank (weak scaling, no data-path collective), trajectories gathered over NCCL.
+  N > 1 : BASELINE.json configs[4] -- 64 independent sequences sharded s mod N, 64/N batched per GPU, strong
+          scaling, the NCCL gather of the transforms inside the timed region (run_config5).
 """
 from __future__ import annotations
 
@@ -52,13 +53,20 @@ def pyramid_bytes(w, h, levels=3):
 B_ALG_FRAME = 2 * W * H + 2 * pyramid_bytes(W, H)
 
 
-def render_frames(n_unique, seed):
+def render_frames(n_unique, seed, out_l=None, out_r=None, threads=None):
+    """n_unique stereo frames of synthetic sequence `seed` (synthdata.py; cv2 releases the GIL, so threads scale)."""
+    from concurrent.futures import ThreadPoolExecutor
     import synthdata as synth
     seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=n_unique, seed=seed)
-    L = np.empty((n_unique, H, W), np.uint8)
-    R = np.empty((n_unique, H, W), np.uint8)
-    for i in range(n_unique):
+    synth.texture_atlas(1234, seq.density)   # build the shared atlas once, before the threads start
+    L = np.empty((n_unique, H, W), np.uint8) if out_l is None else out_l
+    R = np.empty((n_unique, H, W), np.uint8) if out_r is None else out_r
+
+    def one(i):
         L[i], R[i] = seq.render(i)
+
+    with ThreadPoolExecutor(max_workers=threads or min(16, os.cpu_count() or 1)) as ex:
+        list(ex.map(one, range(n_unique)))
     return seq, L, R
 
 
@@ -172,6 +180,198 @@ def cpu_baseline(seq, L, R, budget_s=12.0):
     return {"value": out[best][0], "unit": "frames/s", "cores": best, "kind": "port",
             "sample": f"{out[best][1]} frames of the same sequence, cv2 oracle (OpenCV kernels the reference calls)",
             "single_thread_value": out[1][0], "stage_ms_single_thread": out[1][2]}
+
+
+N_SEQ5 = 64            # BASELINE.json configs[4]: batch of 64 independent sequences
+FRAMES5_PER_STEP = 25  # frames of every sequence per step
+T_OFF = 16             # svo_frame_result as float64[32]: transform = words 16..31, success = int32 word 0
+
+
+def run_config5(args, rank, world, local_rank):
+    """N > 1: BASELINE.json configs[4] -- 64 independent synthetic KITTI-shape sequences (generator seed = sequence
+    id), sequence s on rank s mod N (dist.shard_sequences), every rank batches its 64 / N sequences through one
+    context (sequence = grid dimension), no data-path collective.  All ranks time their shard between barriers; the
+    one exchange of the path -- the gather of the [n_local, frames, 16] transforms over NCCL -- is INSIDE the timed
+    region.  value = 64 x frames / max-over-ranks time (strong scaling: the total work is fixed)."""
+    import torch
+    import torch.distributed as dist
+    from stereo_visual_odometry_b200 import dist as svo_dist
+    from stereo_visual_odometry_b200._lib import FrameResult, check, default_params, lib, ptr
+
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L_ = lib()
+    fsz = C.sizeof(FrameResult)
+    mine = svo_dist.shard_sequences(N_SEQ5, rank, world)
+    n_local, U = len(mine), args.frames5
+    t_r = time.perf_counter()
+    Lh = torch.empty((U, n_local, H, W), dtype=torch.uint8).pin_memory()
+    Rh = torch.empty((U, n_local, H, W), dtype=torch.uint8).pin_memory()
+    Ln, Rn = Lh.numpy(), Rh.numpy()
+    seq0 = None
+    thr = max(1, (os.cpu_count() or 1) // world)
+    for q, sid in enumerate(mine):
+        seq, _, _ = render_frames(U, sid, Ln[:, q], Rn[:, q], threads=thr)
+        seq0 = seq0 or seq
+    render_s = time.perf_counter() - t_r
+    Ld, Rd = Lh.cuda(non_blocking=True), Rh.cuda(non_blocking=True)
+    torch.cuda.synchronize()
+
+    def make_ctx(n_seq):
+        p = default_params(W, H, n_seq=n_seq, device=local_rank)
+        ctx_ = L_.svo_create(C.byref(p))
+        if not ctx_:
+            raise RuntimeError("svo_create: " + L_.svo_last_error().decode())
+        Pl, Pr = np.ascontiguousarray(seq0.Pl), np.ascontiguousarray(seq0.Pr)
+        check(L_.svo_set_projection(ctx_, ptr(Pl, C.c_float), ptr(Pr, C.c_float)))
+        return ctx_
+
+    n_total = (args.warmup + args.steps) * FRAMES5_PER_STEP + 1
+    res_dev = torch.zeros((n_total, n_local, fsz // 8), dtype=torch.float64, device="cuda")
+    ctx = make_ctx(n_local)
+    stream = torch.cuda.ExternalStream(L_.svo_stream(ctx))
+    Lptr = [Ld[j].data_ptr() for j in range(U)]
+    Rptr = [Rd[j].data_ptr() for j in range(U)]
+    rp = res_dev.data_ptr()
+
+    def enqueue(i):
+        j = pingpong(i, U)
+        check(L_.svo_process_frame_batch_dev(ctx, Lptr[j], Rptr[j], W, W * H, rp + i * n_local * fsz))
+
+    k = 0
+    for _ in range(args.warmup * FRAMES5_PER_STEP + 1):
+        enqueue(k)
+        k += 1
+    check(L_.svo_synchronize(ctx))
+    # warm the NCCL communicator up (its first collective builds the rings): not part of the path's steady state
+    svo_dist.gather_results(torch.zeros((n_local, 4, 16), dtype=torch.float64, device="cuda"), dst=0)
+    dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = L_.svo_launch_count(ctx)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0 = k
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(args.steps * FRAMES5_PER_STEP):
+            enqueue(k)
+            k += 1
+        check(L_.svo_stream_join(ctx))   # the primary stream waits for the context's other streams
+        # the path's only exchange: transforms (+ success flags in word 0) of every sequence, one NCCL gather
+        local = res_dev[k0:k, :, T_OFF:T_OFF + 16].transpose(0, 1).contiguous()           # [n_local, frames, 16]
+        flags = res_dev[k0:k, :, 0].transpose(0, 1).contiguous()                          # int32 pair as one f64 word
+        gathered = svo_dist.gather_results(torch.cat([local, flags.unsqueeze(-1)], -1), dst=0)
+        e1.record(stream)
+    check(L_.svo_synchronize(ctx))
+    torch.cuda.synchronize()
+    ms = svo_dist.max_over_ranks(e0.elapsed_time(e1), device="cuda")
+    launches = L_.svo_launch_count(ctx) - launches0
+    clocks = sampler.stop()
+    n_frames = args.steps * FRAMES5_PER_STEP
+    value = N_SEQ5 * n_frames / (ms * 1e-3)
+
+    # ---------------- e2e: pinned HOST frames through svo_submit_frame_batch / svo_collect (H2D of every frame of
+    # every local sequence and D2H of every result inside the timed region), same sharding, max over ranks
+    ctx2 = make_ctx(n_local)
+    resv = (FrameResult * n_local)()
+    Lhp = [Lh[j].data_ptr() for j in range(U)]
+    Rhp = [Rh[j].data_ptr() for j in range(U)]
+    kk = 0
+
+    def run_stream(n):
+        nonlocal kk
+        ok = 0
+        for _ in range(n):
+            j = pingpong(kk, U)
+            check(L_.svo_submit_frame_batch(ctx2, Lhp[j], Rhp[j], W, W * H))
+            kk += 1
+            if L_.svo_pending(ctx2) > E2E_DEPTH:
+                ok += check(L_.svo_collect(ctx2, resv))
+        while L_.svo_pending(ctx2) > 0:
+            ok += check(L_.svo_collect(ctx2, resv))
+        return ok
+
+    run_stream(8)
+    dist.barrier()
+    n_e2e = min(n_frames, 4 * FRAMES5_PER_STEP)
+    t0 = time.perf_counter()
+    ok_e2e = run_stream(n_e2e)
+    dt = svo_dist.max_over_ranks(time.perf_counter() - t0, device="cuda")
+    L_.svo_destroy(ctx2)
+    e2e = {"value": N_SEQ5 * n_e2e / dt, "unit": "frames/s", "h2d_bytes_per_step": 2 * W * H * N_SEQ5 * FRAMES5_PER_STEP,
+           "d2h_bytes_per_step": fsz * N_SEQ5 * FRAMES5_PER_STEP, "frames_timed": N_SEQ5 * n_e2e,
+           "success_rate_rank0": ok_e2e / (n_e2e * n_local), "frames_in_flight": E2E_DEPTH,
+           "timing": "host wall clock, max over ranks, around svo_submit_frame_batch / svo_collect with pinned host "
+                     "frames (H2D of every frame and D2H of every result inside the timed region)"}
+
+    # ---------------- the same thing one sequence per GPU (weak scaling of configs[1]; round-1's N > 1 number)
+    ctx1 = make_ctx(1)
+    res1 = torch.zeros((n_total * 4, fsz // 8), dtype=torch.float64, device="cuda")
+    s1 = torch.cuda.ExternalStream(L_.svo_stream(ctx1))
+    L1 = [Ld[j, 0].data_ptr() for j in range(U)]
+    R1 = [Rd[j, 0].data_ptr() for j in range(U)]
+    for i in range(60):
+        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], W, W * H, None))
+    check(L_.svo_synchronize(ctx1))
+    dist.barrier()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(s1)
+    n_one = 800
+    for i in range(60, 60 + n_one):
+        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], W, W * H, None))
+    check(L_.svo_stream_join(ctx1))
+    a1.record(s1)
+    check(L_.svo_synchronize(ctx1))
+    ms_one = svo_dist.max_over_ranks(a0.elapsed_time(a1), device="cuda")
+    L_.svo_destroy(ctx1)
+
+    out = None
+    if rank == 0:
+        full = svo_dist.interleave_sharded([g.cpu() for g in gathered], N_SEQ5)            # [64, frames, 17]
+        succ = np.ascontiguousarray(full[:, :, 16].numpy()).view(np.int32).reshape(N_SEQ5, n_frames, 2)[:, :, 0]
+        # bit-for-bit check of sequences that other ranks own against a local re-run (a sequence's result does not
+        # depend on which GPU or which batch it runs in)
+        check_ids = sorted({1 % N_SEQ5, N_SEQ5 - 1} - set(mine)) or [mine[-1]]
+        Lc = torch.empty((U, len(check_ids), H, W), dtype=torch.uint8)
+        Rc = torch.empty((U, len(check_ids), H, W), dtype=torch.uint8)
+        for q, sid in enumerate(check_ids):
+            render_frames(U, sid, Lc.numpy()[:, q], Rc.numpy()[:, q])
+        Lcd, Rcd = Lc.cuda(), Rc.cuda()
+        ctxc = make_ctx(len(check_ids))
+        resc = torch.zeros((k, len(check_ids), fsz // 8), dtype=torch.float64, device="cuda")
+        for i in range(k):
+            j = pingpong(i, U)
+            check(L_.svo_process_frame_batch_dev(ctxc, Lcd[j].data_ptr(), Rcd[j].data_ptr(), W, W * H,
+                                                 resc.data_ptr() + i * len(check_ids) * fsz))
+        check(L_.svo_synchronize(ctxc))
+        torch.cuda.synchronize()
+        L_.svo_destroy(ctxc)
+        ref = resc[k0:k, :, T_OFF:T_OFF + 16].transpose(0, 1).cpu()
+        equal = all(bool(torch.equal(ref[q], full[sid, :, :16])) for q, sid in enumerate(check_ids))
+        out = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "batch of 64 independent synthetic KITTI-shape sequences 1241x376 uint8, kitti00.yaml "
+                                   "(BASELINE.json configs[4]), sequence s on GPU s mod N, 64/N sequences batched per GPU",
+                       "sequences": N_SEQ5, "sequences_per_gpu": n_local, "frames_per_step": FRAMES5_PER_STEP,
+                       "unique_frames_per_sequence": U, "playback": "ping-pong", "seed": "sequence id",
+                       "l2": "inputs larger than L2: %d MB of distinct frames per GPU cycle through a 126 MB L2" % (2 * U * n_local * W * H >> 20),
+                       "success_rate": float(succ.mean())},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "gather": {"inside_timed_region": True, "collective": "one NCCL gather of [n_local, frames, 17] float64 per rank",
+                       "bytes_per_rank": int(n_local * n_frames * 17 * 8)},
+            "verify": {"sequences_rerun_on_rank0": check_ids, "bit_equal_to_the_gathered_transforms": bool(equal)},
+            "one_sequence_per_gpu": {"value": world * n_one / (ms_one * 1e-3), "unit": "frames/s", "scaling": "weak",
+                                     "note": "configs[1] replicated: one single-sequence streaming context per GPU"},
+            "reference_arm_note": "--impl reference is ONE CPU process (all host threads) whatever --gpus says",
+            "render_s": render_s,
+        }
+        print(json.dumps(out))
+    L_.svo_destroy(ctx)
+    dist.barrier()
+    dist.destroy_process_group()
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -344,15 +544,18 @@ def run_gpu(args, rank, world, local_rank):
         n_b = max(1, 64 // world)
         batch = None
         try:
-            nfb = min(40, n_unique)
+            nfb, U5 = 40, args.frames5
             ctxb = make_ctx(n_seq=n_b)
-            idx = torch.tensor([[pingpong(f + 3 * s_, n_unique) for s_ in range(n_b)] for f in range(nfb)], device="cuda")
+            # 64 distinct sequences (generator seed = sequence id), U5 rendered frames each, ping-pong playback
+            Lb5 = torch.empty((U5, n_b, H, W), dtype=torch.uint8)
+            Rb5 = torch.empty((U5, n_b, H, W), dtype=torch.uint8)
+            for s_ in range(n_b):
+                render_frames(U5, s_, Lb5.numpy()[:, s_], Rb5.numpy()[:, s_])
+            Lb5d, Rb5d = Lb5.cuda(), Rb5.cuda()
             sb = torch.cuda.ExternalStream(L_.svo_stream(ctxb))
             check(L_.svo_enable_timers(ctxb, 0))
-            bl = torch.empty((n_b, H, W), dtype=torch.uint8, device="cuda")
-            br = torch.empty((n_b, H, W), dtype=torch.uint8, device="cuda")
-            Lb = [Ld[idx[f]] for f in range(nfb)]
-            Rb = [Rd[idx[f]] for f in range(nfb)]
+            Lb = [Lb5d[pingpong(f, U5)] for f in range(nfb)]
+            Rb = [Rb5d[pingpong(f, U5)] for f in range(nfb)]
             torch.cuda.synchronize()
             for f in range(5):
                 check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
@@ -440,7 +643,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=160, help="unique rendered frames (ping-pong playback)")
+    ap.add_argument("--frames", type=int, default=1000, help="unique rendered frames of the N = 1 sequence (configs[1]: 1000)")
+    ap.add_argument("--frames5", type=int, default=24, help="unique rendered frames per sequence of the 64-sequence batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -449,6 +653,8 @@ def main():
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif world > 1:
+        run_config5(args, rank, world, local_rank)
     else:
         run_gpu(args, rank, world, local_rank)
 
