@@ -23,6 +23,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX 3: ranges per stage (no-ops unless a tool is attached)
+
 #include "svo_kernels.cuh"
 
 using namespace svo;
@@ -589,6 +591,7 @@ struct TraceScope {
     bool on;
     size_t idx;
     TraceScope(svo_ctx* c_, const char* name, int sid, cudaStream_t st_) : c(c_), st(st_), on(false), idx(0) {
+        nvtxRangePushA(name);   // an NVTX range around the launches of every stage
         if (!c->trace_path || c->frames < 30 || c->frames >= 46) return;
         svo_ctx::TraceRec r{name, c->frames, sid, nullptr, nullptr};
         cudaEventCreate(&r.a);
@@ -600,6 +603,7 @@ struct TraceScope {
     }
     ~TraceScope() {
         if (on) cudaEventRecord(c->trace[idx].b, st);
+        nvtxRangePop();
     }
 };
 static void trace_dump(svo_ctx* c) {
@@ -705,6 +709,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         if (c->timers) cudaEventRecord(c->ev[2], sP);
         if (!tm) CU(cudaEventRecord(c->ev_bm[e], sP));
         if (tm) {
+            TraceScope ts(c, "klt", 3, sP);
             launch_klt(c->d, c->pg, c->pc, c->klt_blocks_full, prev, cur, sP);
         } else if (spec) {
             // normally nothing is left to track: a small grid on the chain's own SMs

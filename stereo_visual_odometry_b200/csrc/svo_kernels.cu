@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(FT_THREADS)
 fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h, int pitch, int thr_lo,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
-            BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min) {
+            BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min, int tiles_x, int tiles_y) {
     // low-threshold pass of the pipeline: only needed when the retry of vo.cpp:327-332 can happen at all, i.e. when
     // the thr_hi pass left fewer than gate_min buckets with a winner (every such bucket yields one bucketed feature)
     if (gate && gate[blockIdx.z] >= gate_min) return;
@@ -231,8 +231,13 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     __shared__ int n_list, n_hits;
     const int z = blockIdx.z;
     const uint8_t* src = img + (long long)z * img_stride;
-    const int x0 = blockIdx.x * FT_OW, y0 = blockIdx.y * FT_OH;
     const int tid = threadIdx.x, lane = tid & 31;
+    // ungated launches: one tile per block (2-D grid); the gated pass, which almost never has work, runs a few blocks
+    // per image that loop over all tiles, so that its early exit costs next to nothing
+    const int n_tiles = gate ? tiles_x * tiles_y : 1;
+    for (int tile_id = gate ? (int)blockIdx.x : 0; tile_id < n_tiles; tile_id += gridDim.x) {
+    const int x0 = (gate ? tile_id % tiles_x : (int)blockIdx.x) * FT_OW, y0 = (gate ? tile_id / tiles_x : (int)blockIdx.y) * FT_OH;
+    __syncthreads();   // the previous tile of this block is finished with the shared arrays
     if (tid == 0) n_list = n_hits = 0;
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
     // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
@@ -344,7 +349,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
                 }
             }
         }
-        return;
+        continue;
     }
     for (int i = tid; i < FT_OH * (FT_OW / 4); i += FT_THREADS) {
         const int oy = i / (FT_OW / 4), oq = i - oy * (FT_OW / 4);
@@ -390,15 +395,17 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             }
         }
     }
+    }   // tile loop
 }
 
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st,
                  int* countA, const int* gate, int gate_min) {
-    dim3 grid((w + FT_OW - 1) / FT_OW, (h + FT_OH - 1) / FT_OH, n_img);
-    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map,
-                                             map_stride, map_pitch, keysA, keysB, bg, countA, gate, gate_min);
+    const int tiles_x = (w + FT_OW - 1) / FT_OW, tiles_y = (h + FT_OH - 1) / FT_OH;
+    const dim3 grid = gate ? dim3(tiles_x * tiles_y < 48 ? tiles_x * tiles_y : 48, 1, n_img) : dim3(tiles_x, tiles_y, n_img);
+    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride,
+                                             map_pitch, keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y);
 }
 
 // ---- ordered compaction of the response map (row-major == cv::FAST output order)

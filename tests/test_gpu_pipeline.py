@@ -419,3 +419,32 @@ def test_padded_row_strides_equal_contiguous_images():
         ok0, T0 = a.stereo_callback(L, R)
         ok1, T1 = b.stereo_callback(big[0, :, :637], big[1, :, :637])
         assert ok0 == ok1 and np.array_equal(T0, T1)
+
+
+def test_switching_between_synchronous_and_streaming_calls():
+    """A caller may mix stereo_callback (serial frame on the whole GPU) with submit / collect bursts (partitioned,
+    speculative).  The first streamed frame after a serial one reads the pyramid slot and the FAST keys the SERIAL
+    frame's ingest wrote on another stream (svo_capi.cu: the speculative passes wait for ingest(f - 1) explicitly).
+    Every transform must equal the all-synchronous run, whatever the switching pattern."""
+    seq = synth.make_sequence(width=640, height=240, n_frames=30, seed=11)
+    frames = list(seq.frames())
+    a = V.VisualOdometry(640, 240)
+    a.initalize_projection_matricies(seq.Pl, seq.Pr)
+    want = [a.stereo_callback(L, R) for (L, R) in frames]
+    for pattern in ([2, 5, 1, 6, 3, 7, 6], [1, 1, 1, 9, 1, 8, 9], [4, 2, 4, 2, 4, 2, 12]):   # sync, burst, sync, burst ...
+        b = V.VisualOdometry(640, 240)
+        b.initalize_projection_matricies(seq.Pl, seq.Pr)
+        got, i = [], 0
+        for k, n in enumerate(pattern):
+            chunk = frames[i:i + n]
+            i += n
+            if k % 2 == 0:
+                got += [b.stereo_callback(L, R) for (L, R) in chunk]
+            else:
+                for (L, R) in chunk:
+                    b.submit(L, R)
+                got += [b.collect() for _ in chunk]
+        assert len(got) == len(frames)
+        for k, ((ok0, T0), (ok1, T1)) in enumerate(zip(want, got)):
+            assert ok0 == ok1 and np.array_equal(T0, T1), (pattern, k)
+        b.close()
