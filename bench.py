@@ -32,6 +32,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 W, H = 1241, 376
+PITCH = 1280   # row pitch of the device-resident frames (a multiple of 128 bytes)
 FRAMES_PER_STEP = 400
 E2E_DEPTH = 3
 # dram__bytes_read.sum + dram__bytes_write.sum of the ingest kernels per stereo frame in the 64-frame launch
@@ -214,7 +215,10 @@ def run_config5(args, rank, world, local_rank):
         seq, _, _ = render_frames(U, sid, Ln[:, q], Rn[:, q], threads=thr)
         seq0 = seq0 or seq
     render_s = time.perf_counter() - t_r
-    Ld, Rd = Lh.cuda(non_blocking=True), Rh.cuda(non_blocking=True)
+    Ld = torch.zeros((U, n_local, H, PITCH), dtype=torch.uint8, device="cuda")   # 128-byte aligned row pitch
+    Rd = torch.zeros((U, n_local, H, PITCH), dtype=torch.uint8, device="cuda")
+    Ld[..., :W].copy_(Lh, non_blocking=True)
+    Rd[..., :W].copy_(Rh, non_blocking=True)
     torch.cuda.synchronize()
 
     def make_ctx(n_seq):
@@ -236,7 +240,7 @@ def run_config5(args, rank, world, local_rank):
 
     def enqueue(i):
         j = pingpong(i, U)
-        check(L_.svo_process_frame_batch_dev(ctx, Lptr[j], Rptr[j], W, W * H, rp + i * n_local * fsz))
+        check(L_.svo_process_frame_batch_dev(ctx, Lptr[j], Rptr[j], PITCH, PITCH * H, rp + i * n_local * fsz))
 
     k = 0
     for _ in range(args.warmup * FRAMES5_PER_STEP + 1):
@@ -312,14 +316,14 @@ def run_config5(args, rank, world, local_rank):
     L1 = [Ld[j, 0].data_ptr() for j in range(U)]
     R1 = [Rd[j, 0].data_ptr() for j in range(U)]
     for i in range(60):
-        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], W, W * H, None))
+        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], PITCH, PITCH * H, None))
     check(L_.svo_synchronize(ctx1))
     dist.barrier()
     a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a0.record(s1)
     n_one = 800
     for i in range(60, 60 + n_one):
-        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], W, W * H, None))
+        check(L_.svo_process_frame_batch_dev(ctx1, L1[pingpong(i, U)], R1[pingpong(i, U)], PITCH, PITCH * H, None))
     check(L_.svo_stream_join(ctx1))
     a1.record(s1)
     check(L_.svo_synchronize(ctx1))
@@ -337,12 +341,15 @@ def run_config5(args, rank, world, local_rank):
         Rc = torch.empty((U, len(check_ids), H, W), dtype=torch.uint8)
         for q, sid in enumerate(check_ids):
             render_frames(U, sid, Lc.numpy()[:, q], Rc.numpy()[:, q])
-        Lcd, Rcd = Lc.cuda(), Rc.cuda()
+        Lcd = torch.zeros((U, len(check_ids), H, PITCH), dtype=torch.uint8, device="cuda")
+        Rcd = torch.zeros((U, len(check_ids), H, PITCH), dtype=torch.uint8, device="cuda")
+        Lcd[..., :W].copy_(Lc)
+        Rcd[..., :W].copy_(Rc)
         ctxc = make_ctx(len(check_ids))
         resc = torch.zeros((k, len(check_ids), fsz // 8), dtype=torch.float64, device="cuda")
         for i in range(k):
             j = pingpong(i, U)
-            check(L_.svo_process_frame_batch_dev(ctxc, Lcd[j].data_ptr(), Rcd[j].data_ptr(), W, W * H,
+            check(L_.svo_process_frame_batch_dev(ctxc, Lcd[j].data_ptr(), Rcd[j].data_ptr(), PITCH, PITCH * H,
                                                  resc.data_ptr() + i * len(check_ids) * fsz))
         check(L_.svo_synchronize(ctxc))
         torch.cuda.synchronize()
@@ -389,7 +396,12 @@ def run_gpu(args, rank, world, local_rank):
     seq, Lh, Rh = render_frames(n_unique, seed=rank)
     render_s = time.perf_counter() - t_r
     Lp, Rp = torch.from_numpy(Lh).pin_memory(), torch.from_numpy(Rh).pin_memory()
-    Ld, Rd = Lp.cuda(non_blocking=True), Rp.cuda(non_blocking=True)
+    # device-resident frames: rows padded to a 128-byte multiple (the caller's stride is a parameter of the C ABI), so
+    # that the source planes qualify for the TMA tile loads
+    Ld = torch.zeros((n_unique, H, PITCH), dtype=torch.uint8, device="cuda")
+    Rd = torch.zeros((n_unique, H, PITCH), dtype=torch.uint8, device="cuda")
+    Ld[:, :, :W].copy_(Lp, non_blocking=True)
+    Rd[:, :, :W].copy_(Rp, non_blocking=True)
     torch.cuda.synchronize()
 
     def make_ctx(n_seq=1):
@@ -419,7 +431,7 @@ def run_gpu(args, rank, world, local_rank):
 
     def enqueue(ctx_, i):
         j = pingpong(i, n_unique)
-        check(L_.svo_process_frame_batch_dev(ctx_, Ld_ptr[j], Rd_ptr[j], W, W * H, res_ptr + i * fsz))
+        check(L_.svo_process_frame_batch_dev(ctx_, Ld_ptr[j], Rd_ptr[j], PITCH, PITCH * H, res_ptr + i * fsz))
 
     enqueue(ctx, 0)
     k = 1
@@ -551,19 +563,22 @@ def run_gpu(args, rank, world, local_rank):
             Rb5 = torch.empty((U5, n_b, H, W), dtype=torch.uint8)
             for s_ in range(n_b):
                 render_frames(U5, s_, Lb5.numpy()[:, s_], Rb5.numpy()[:, s_])
-            Lb5d, Rb5d = Lb5.cuda(), Rb5.cuda()
+            Lb5d = torch.zeros((U5, n_b, H, PITCH), dtype=torch.uint8, device="cuda")
+            Rb5d = torch.zeros((U5, n_b, H, PITCH), dtype=torch.uint8, device="cuda")
+            Lb5d[..., :W].copy_(Lb5)
+            Rb5d[..., :W].copy_(Rb5)
             sb = torch.cuda.ExternalStream(L_.svo_stream(ctxb))
             check(L_.svo_enable_timers(ctxb, 0))
             Lb = [Lb5d[pingpong(f, U5)] for f in range(nfb)]
             Rb = [Rb5d[pingpong(f, U5)] for f in range(nfb)]
             torch.cuda.synchronize()
             for f in range(5):
-                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), PITCH, PITCH * H, None))
             check(L_.svo_synchronize(ctxb))
             b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             b0.record(sb)
             for f in range(5, nfb):
-                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), PITCH, PITCH * H, None))
             check(L_.svo_stream_join(ctxb))
             b1.record(sb)
             check(L_.svo_synchronize(ctxb))
@@ -571,7 +586,7 @@ def run_gpu(args, rank, world, local_rank):
             check(L_.svo_enable_timers(ctxb, 1))
             check(L_.svo_reset_timers(ctxb))
             for f in range(nfb - 1, nfb - 11, -1):
-                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), W, W * H, None))
+                check(L_.svo_process_frame_batch_dev(ctxb, Lb[f].data_ptr(), Rb[f].data_ptr(), PITCH, PITCH * H, None))
             msv, ln = C.c_double(0), C.c_longlong(0)
             L_.svo_get_stage_time(ctxb, 0, C.byref(msv), C.byref(ln))
             ing_us = 1e3 * msv.value / 10

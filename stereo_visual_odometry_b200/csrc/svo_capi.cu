@@ -427,6 +427,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.specT_it, C));
     CU(dev_alloc(c, &d.cntF, S));
     CU(dev_alloc(c, &d.cntT, S));
+    CU(dev_alloc(c, &d.fast_work, (size_t)2 * SVO_PYR_SLOTS));
     CU(dev_alloc(c, &d.listF, S * c->bg.nb));
     CU(dev_alloc(c, &d.nF, 2 * S));
     CU(dev_alloc(c, &d.predT, (size_t)2 * S * c->bg.nb));

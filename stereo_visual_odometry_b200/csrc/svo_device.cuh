@@ -105,6 +105,7 @@ struct DevArrays {
     float2* specF_pts; uint8_t* specF_st; int* specF_it;
     float2* specT_pts; uint8_t* specT_st; int* specT_it;
     int* cntF; int* cntT;             // [n_seq] work counters of the two speculative kernels
+    int* fast_work;                   // [slots][2] tile counter + finished-block counter of the persistent FAST launch
     int* predT;                       // [2][n_seq][nb] best predicted tracked score + 0x8000 per bucket of the NEXT frame (0: none)
     int* listF; int* nF;              // [n_seq][nb], [n_seq]: buckets holding a thr-20 FAST winner (any order)
     int* todo; int* n_todo;           // [n_seq][cap], [n_seq]: bucketed features whose result was not cached

@@ -10,6 +10,7 @@
 //                          341-364), ages++ (vo.cpp:70-72), triangulation (vo.cpp:89-94)
 //   pnp_hyp_kernel / pnp_final_kernel   cameraToWorld (vo.cpp:282-313) + the failure gates of
 //                          stereo_callback (vo.cpp:106-136)
+#include <cuda.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -17,6 +18,70 @@
 #include "svo_epnp.cuh"
 
 namespace svo {
+
+// ============================================================================
+// TMA (cp.async.bulk.tensor) tile loads: the image planes are described to the copy engine as 3-D uint8 tensors
+// (x, y, image); one elected thread per block arms an mbarrier with the tile's byte count and issues the copy,
+// the block waits on the barrier.  Out-of-range coordinates (negative starts, tiles hanging over the right / bottom
+// edge) are zero-filled by the hardware, so the loaders need no address clamping.
+// Requirements of the engine: base address and row / image strides multiples of 16 bytes, box width a multiple
+// of 16 bytes and <= 256; planes that do not qualify take the kernels' LDG loaders.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "SVO_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra SVO_MBAR_DONE;\n"
+        "bra SVO_MBAR_WAIT;\n"
+        "SVO_MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(phase)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int x, int y, int z, unsigned long long* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+        : "memory");
+}
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tma_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (getenv("SVO_NO_TMA") || cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+            qr != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+// uint8 planes [n_img][h][w] with row pitch `pitch` and image stride `img_stride` (bytes), box = box_w x box_h x 1
+bool make_tile_map(CUtensorMap* map, const void* base, int w, int h, int pitch, long long img_stride, int n_img, int box_w,
+                   int box_h) {
+    EncodeTiledFn enc = tma_encode_fn();
+    if (!enc || ((size_t)base & 15) || (pitch & 15) || box_w > 256 || (box_w & 15) || box_h > 256) return false;
+    if (n_img > 1 && (img_stride & 15)) return false;
+    const cuuint64_t gdim[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n_img};
+    const cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)(n_img > 1 ? img_stride : (long long)pitch * h)};
+    const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 // ============================================================================
 // helpers
@@ -162,7 +227,7 @@ __device__ __forceinline__ unsigned long long ld_key(const unsigned long long* p
 //            two adjacent compass points); quads that cannot hold a corner at thr_lo are dropped (~2/3)
 //   phase 2  the surviving quads, compacted through a shared list so no warp idles: the exact arc score
 //   phase 3  strict 3x3 NMS + per-bucket winners (64-bit atomicMax keys) / dense response map
-constexpr int FT_OW = 120, FT_OH = 14, FT_SW = 128, FT_SH = 16, FT_TW = 136, FT_TH = 22, FT_THREADS = 256;
+constexpr int FT_OW = 120, FT_OH = 14, FT_SW = 128, FT_SH = 16, FT_TW = 144, FT_TH = 22, FT_THREADS = 256;   // tile: 136 columns used, pitch 144
 constexpr int FT_TASKS = (FT_SW / 4) * FT_SH;   // 512 quads
 
 // bytes i, i + 1 of the 12-byte window w[0..2] as (b_i) | (b_{i+1} << 16)
@@ -220,25 +285,65 @@ __global__ void __launch_bounds__(FT_THREADS)
 fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h, int pitch, int thr_lo,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
-            BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min, int tiles_x, int tiles_y) {
+            BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min, int tiles_x, int tiles_y,
+            const __grid_constant__ CUtensorMap tmap, int use_tma, int n_img, int* __restrict__ work) {
     // low-threshold pass of the pipeline: only needed when the retry of vo.cpp:327-332 can happen at all, i.e. when
     // the thr_hi pass left fewer than gate_min buckets with a winner (every such bucket yields one bucketed feature)
     if (gate && gate[blockIdx.z] >= gate_min) return;
-    __shared__ __align__(16) uint8_t tile[FT_TH * FT_TW];
+    // Tiles are double buffered: in the ungated launches the blocks are persistent (1-D grid over all (image, tile)
+    // pairs) and the copy engine fetches tile k + 1 of a block while the block scores tile k.
+    __shared__ __align__(128) uint8_t tile2[2][(FT_TH * FT_TW + 127) & ~127];   // a TMA destination is 128-byte aligned
+    __shared__ __align__(8) unsigned long long tma_bar[2];
     __shared__ __align__(16) uint8_t score[FT_SH * FT_SW];
     __shared__ unsigned short list[FT_TASKS];
     __shared__ unsigned short hits[FT_OW * FT_OH];   // score-array positions of the nonzero scores among the outputs
     __shared__ int n_list, n_hits;
-    const int z = blockIdx.z;
-    const uint8_t* src = img + (long long)z * img_stride;
     const int tid = threadIdx.x, lane = tid & 31;
-    // ungated launches: one tile per block (2-D grid); the gated pass, which almost never has work, runs a few blocks
-    // per image that loop over all tiles, so that its early exit costs next to nothing
-    const int n_tiles = gate ? tiles_x * tiles_y : 1;
-    for (int tile_id = gate ? (int)blockIdx.x : 0; tile_id < n_tiles; tile_id += gridDim.x) {
-    const int x0 = (gate ? tile_id % tiles_x : (int)blockIdx.x) * FT_OW, y0 = (gate ? tile_id / tiles_x : (int)blockIdx.y) * FT_OH;
-    __syncthreads();   // the previous tile of this block is finished with the shared arrays
-    if (tid == 0) n_list = n_hits = 0;
+    if (use_tma && tid == 0) {
+        mbar_init(&tma_bar[0], 1);
+        mbar_init(&tma_bar[1], 1);
+    }
+    unsigned tma_phase[2] = {0u, 0u};
+    // ungated launches: persistent blocks over all tiles of all images; the gated pass, which almost never has work,
+    // runs a few blocks per image (blockIdx.z) that loop over its tiles, so that its early exit costs next to nothing
+    const int tpi = tiles_x * tiles_y, n_tiles = gate ? tpi : tpi * n_img;
+    auto decode = [&](int id, int& zz, int& xx, int& yy) {
+        zz = gate ? (int)blockIdx.z : id / tpi;
+        const int t = gate ? id : id - zz * tpi;
+        yy = (t / tiles_x) * FT_OH;
+        xx = (t - (t / tiles_x) * tiles_x) * FT_OW;
+    };
+    auto issue = [&](int id, int buf) {   // one bulk tensor copy: the 144 x 22 box at the aligned column at or below x0 - 8
+        int zz, xx, yy;
+        decode(id, zz, xx, yy);
+        mbar_expect_tx(&tma_bar[buf], FT_TH * FT_TW);
+        tma_load_3d(tile2[buf], &tmap, (xx - 8) & ~15, yy - 4, zz, &tma_bar[buf]);
+    };
+    // tile order: a global work counter when the launch has one (work[0]; the tiles cost very different amounts, so
+    // the persistent blocks take them dynamically; work[1] counts finished blocks and the last one re-arms both),
+    // else block b takes tiles b, b + gridDim.x, ...
+    __shared__ int next_id[2];
+    __syncthreads();
+    if (tid == 0) {
+        const int first = work ? atomicAdd(work, 1) : (int)blockIdx.x;
+        next_id[0] = first;
+        if (use_tma && first < n_tiles) issue(first, 0);
+    }
+    __syncthreads();
+    for (int iter = 0;; ++iter) {
+    const int buf = iter & 1;
+    const int tile_id = next_id[buf];
+    if (tile_id >= n_tiles) break;
+    uint8_t* tile = tile2[buf];
+    int z, x0, y0;
+    decode(tile_id, z, x0, y0);
+    const uint8_t* src = img + (long long)z * img_stride;
+    if (tid == 0) {
+        n_list = n_hits = 0;
+        const int nxt = work ? atomicAdd(work, 1) : tile_id + (int)gridDim.x;   // the block's next tile: prefetched now
+        next_id[buf ^ 1] = nxt;
+        if (use_tma && nxt < n_tiles) issue(nxt, buf ^ 1);
+    }
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
     // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
     const int tx0 = x0 - 8, ty0 = y0 - 4;
@@ -246,7 +351,14 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     // are fetched with the word column / row clamped into the plane (needs a word-aligned plane whose pitch
     // covers the last word that holds valid pixels).
     const bool fastpath = (pitch & 3) == 0 && (((size_t)src) & 3) == 0 && ((w + 3) & ~3) <= pitch;
-    if (fastpath) {
+    // the copy engine wants the box to start at a multiple of 16 bytes along x: the 144-byte box starts at the aligned
+    // column at or below tx0 (tx0 - 0 or tx0 - 8) and the 136 columns that are used sit `toff` bytes into each row
+    const int toff = use_tma ? (tx0 & 15) : 0;
+    const uint8_t* tl = tile + toff;
+    if (use_tma) {   // zero fill outside the image
+        mbar_wait(&tma_bar[buf], tma_phase[buf]);
+        tma_phase[buf] ^= 1u;
+    } else if (fastpath) {
         const int wmax = ((w + 3) >> 2) - 1;
         constexpr int NW = FT_TH * (FT_TW / 4), NIT = (NW + FT_THREADS - 1) / FT_THREADS;
         unsigned v[NIT];
@@ -278,9 +390,9 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     for (int s = 0; s < FT_TASKS / FT_THREADS; ++s) {
         const int t = tid + s * FT_THREADS;
         const int r = t >> 5, q = t & 31;
-        const unsigned* top = reinterpret_cast<const unsigned*>(tile + (r + 0) * FT_TW) + q;
-        const unsigned* mid = reinterpret_cast<const unsigned*>(tile + (r + 3) * FT_TW) + q;
-        const unsigned* bot = reinterpret_cast<const unsigned*>(tile + (r + 6) * FT_TW) + q;
+        const unsigned* top = reinterpret_cast<const unsigned*>(tl + (r + 0) * FT_TW) + q;
+        const unsigned* mid = reinterpret_cast<const unsigned*>(tl + (r + 3) * FT_TW) + q;
+        const unsigned* bot = reinterpret_cast<const unsigned*>(tl + (r + 6) * FT_TW) + q;
         const unsigned wt[3] = {top[0], top[1], top[2]}, wm[3] = {mid[0], mid[1], mid[2]}, wb[3] = {bot[0], bot[1], bot[2]};
         const unsigned ua = fast_pair_bound<4>(wt, wm, wb), ub = fast_pair_bound<6>(wt, wm, wb);
         // any half > thr_lo ?
@@ -302,7 +414,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
         unsigned rows[7][3];
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
-            const unsigned* p = reinterpret_cast<const unsigned*>(tile + (r + k) * FT_TW) + q;
+            const unsigned* p = reinterpret_cast<const unsigned*>(tl + (r + k) * FT_TW) + q;
             rows[k][0] = p[0]; rows[k][1] = p[1]; rows[k][2] = p[2];
         }
         const unsigned sa = fast_pair_score<4>(rows), sb = fast_pair_score<6>(rows);
@@ -349,6 +461,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
                 }
             }
         }
+        __syncthreads();   // every thread is done with this tile's shared arrays
         continue;
     }
     for (int i = tid; i < FT_OH * (FT_OW / 4); i += FT_THREADS) {
@@ -395,17 +508,42 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             }
         }
     }
+    __syncthreads();   // every thread is done with this tile's shared arrays
     }   // tile loop
+    if (work && tid == 0 && atomicAdd(work + 1, 1) == (int)gridDim.x - 1) {   // last block out: ready for the next launch
+        work[0] = 0;
+        work[1] = 0;
+    }
 }
 
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st,
-                 int* countA, const int* gate, int gate_min) {
+                 int* countA, const int* gate, int gate_min, int* work) {
     const int tiles_x = (w + FT_OW - 1) / FT_OW, tiles_y = (h + FT_OH - 1) / FT_OH;
-    const dim3 grid = gate ? dim3(tiles_x * tiles_y < 48 ? tiles_x * tiles_y : 48, 1, n_img) : dim3(tiles_x, tiles_y, n_img);
-    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride,
-                                             map_pitch, keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y);
+    // ungated: persistent blocks (a few per SM) over all (image, tile) pairs; gated: a few blocks per image
+    static int n_sm = 0;
+    if (!n_sm) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        if (n_sm <= 0) n_sm = 148;
+    }
+    static int bps = 0;   // persistent blocks per SM (SVO_FAST_BPS; what the register file holds is the useful maximum)
+    if (!bps) {
+        const char* e = getenv("SVO_FAST_BPS");
+        bps = e ? atoi(e) : 0;
+        if (bps <= 0 && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel, FT_THREADS, 0) != cudaSuccess) bps = 4;
+        if (bps <= 0) bps = 4;
+    }
+    const long long total = (long long)tiles_x * tiles_y * n_img, cap = (long long)bps * n_sm;
+    const dim3 grid = gate ? dim3(tiles_x * tiles_y < 48 ? tiles_x * tiles_y : 48, 1, n_img)
+                           : dim3((unsigned)(total < cap ? total : cap), 1, 1);
+    CUtensorMap tmap;
+    memset(&tmap, 0, sizeof(tmap));
+    const int use_tma = make_tile_map(&tmap, img, w, h, pitch, img_stride, n_img, FT_TW, FT_TH) ? 1 : 0;
+    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch,
+                                             keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work);
 }
 
 // ---- ordered compaction of the response map (row-major == cv::FAST output order)
@@ -477,7 +615,7 @@ void launch_compact_keypoints(const uint8_t* resp_map, int w, int h, int map_pit
 // read from HBM exactly once for both the level-0 copy and level 1.
 // RPT = output rows per thread (block = 128 x 4 * RPT outputs): 4 for batched launches (fewest row sums per output),
 // 2 or 1 when one frame's launch would otherwise be a handful of long blocks (latency instead of throughput).
-constexpr int PD_OW = 128, PD_TW = 2 * PD_OW + 32, PD_THREADS = 128;
+constexpr int PD_OW = 128, PD_TW = 2 * PD_OW + 32, PD_BW = 160, PD_THREADS = 128;
 struct PyrDownJob {
     const uint8_t* src[2];    // per camera (n_cam == 1: only [0])
     long long src_seq_stride;
@@ -489,6 +627,7 @@ struct PyrDownJob {
     long long copy_seq_stride;
     int cpitch;
     int n_cam;
+    int use_tma;              // tile loads by cp.async.bulk.tensor (the source planes qualify, see make_tile_map)
 };
 // the 4 bytes at an arbitrary byte address, from the two aligned words around it
 __device__ __forceinline__ unsigned ld_word_any(const uint8_t* p) {
@@ -510,9 +649,23 @@ __device__ __forceinline__ void pd_row_sums(unsigned w0, unsigned w1, unsigned w
     hB = e2 * 5u + g2 + __byte_perm(g1, g2, 0x5432u) + __byte_perm(e2, e3, 0x5432u);
 }
 template <int PD_ROWS_PER_THREAD>
-__global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) {
+__global__ void __launch_bounds__(PD_THREADS)
+pyrdown_tile_kernel(PyrDownJob j, const __grid_constant__ CUtensorMap map0, const __grid_constant__ CUtensorMap map1) {
     constexpr int PD_OH = 4 * PD_ROWS_PER_THREAD, PD_TH = 2 * PD_OH + 3;
-    __shared__ __align__(16) uint8_t tile[PD_TH * PD_TW];
+    // The 288-byte tile rows are kept as two overlapping 160-byte halves (columns 0..159 and 128..287): a TMA box is
+    // at most 256 bytes wide, and each half-warp's 16-byte windows then lie inside one half.
+    __shared__ __align__(128) uint8_t tileA[PD_TH * PD_BW];
+    __shared__ __align__(128) uint8_t tileB[PD_TH * PD_BW];
+    __shared__ __align__(8) unsigned long long tma_bar;
+    auto st_chunk = [&](int r, int k, const uint4& v) {   // 16-byte chunk k (tile columns 16 k ..) of tile row r
+        if (k <= 9) *reinterpret_cast<uint4*>(tileA + r * PD_BW + 16 * k) = v;
+        if (k >= 8) *reinterpret_cast<uint4*>(tileB + r * PD_BW + 16 * (k - 8)) = v;
+    };
+    auto ld_chunk = [&](int r, int k) -> uint4 {
+        return k <= 9 ? *reinterpret_cast<const uint4*>(tileA + r * PD_BW + 16 * k)
+                      : *reinterpret_cast<const uint4*>(tileB + r * PD_BW + 16 * (k - 8));
+    };
+    if (j.use_tma && threadIdx.x == 0) mbar_init(&tma_bar, 1);
     const int cam = j.n_cam == 2 ? (blockIdx.z & 1) : 0, seq = j.n_cam == 2 ? (blockIdx.z >> 1) : blockIdx.z;
     const uint8_t* src = j.src[cam] + (long long)seq * j.src_seq_stride;
     uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
@@ -527,6 +680,42 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
     constexpr int NCH = PD_TW / 16, NT = PD_TH * NCH, NIT = (NT + PD_THREADS - 1) / PD_THREADS;
     const bool al16 = (((size_t)src) & 15) == 0 && (j.spitch & 15) == 0;
     const int lo = al16 ? 0 : 4, lim = al16 ? 16 : 20;   // inner chunk: lo <= gx && gx + lim <= sw
+    if (j.use_tma) {
+        // ---- TMA: the two halves as two bulk tensor copies on one mbarrier (zero fill outside the plane), then
+        // BORDER_REFLECT_101 is restored in the tiles that touch an image edge: two columns per side within the
+        // rows that exist, then whole rows copied from their mirror rows inside the tile.
+        __syncthreads();   // barrier initialised
+        if (tid == 0) {
+            const CUtensorMap* map = cam ? &map1 : &map0;
+            mbar_expect_tx(&tma_bar, 2 * PD_TH * PD_BW);
+            tma_load_3d(tileA, map, sx0, sy0, seq, &tma_bar);
+            tma_load_3d(tileB, map, sx0 + 128, sy0, seq, &tma_bar);
+        }
+        mbar_wait(&tma_bar, 0);
+        if (sx0 < 0 || sx0 + PD_TW > j.sw || sy0 < 0 || sy0 + PD_TH > j.sh) {
+            auto get = [&](int r, int c) -> uint8_t { return c < PD_BW ? tileA[r * PD_BW + c] : tileB[r * PD_BW + c - 128]; };
+            auto put = [&](int r, int c, uint8_t v) {
+                if (c < PD_BW) tileA[r * PD_BW + c] = v;
+                if (c >= 128) tileB[r * PD_BW + c - 128] = v;
+            };
+            for (int i = tid; i < PD_TH * 4; i += PD_THREADS) {
+                const int r = i >> 2, e = i & 3, gy = sy0 + r;
+                const int gx = e < 2 ? e - 2 : j.sw + (e - 2), c = gx - sx0;
+                if (gy < 0 || gy >= j.sh || c < 0 || c >= PD_TW) continue;
+                put(r, c, get(r, reflect101(gx, j.sw) - sx0));
+            }
+            __syncthreads();
+            for (int i = tid; i < 4 * (2 * PD_BW / 16); i += PD_THREADS) {
+                const int e = i / (2 * PD_BW / 16), k = i - e * (2 * PD_BW / 16);
+                const int gy = e < 2 ? e - 2 : j.sh + (e - 2), r = gy - sy0;
+                if (r < 0 || r >= PD_TH) continue;
+                const int rs = reflect101(gy, j.sh) - sy0;
+                uint8_t* base = k < PD_BW / 16 ? tileA : tileB;
+                const int off = 16 * (k < PD_BW / 16 ? k : k - PD_BW / 16);
+                *reinterpret_cast<uint4*>(base + r * PD_BW + off) = *reinterpret_cast<const uint4*>(base + rs * PD_BW + off);
+            }
+        }
+    } else {
     if (j.sw >= lo + lim) {
         const int gx_hi = al16 ? ((j.sw - 16) & ~15) : (j.sw - 20);
         if (al16) {
@@ -542,7 +731,7 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
             for (int it = 0; it < NIT; ++it) {
                 const int i = tid + it * PD_THREADS;
                 const int gx = sx0 + 16 * (i % NCH);
-                if (i < NT && gx >= 0 && gx + 16 <= j.sw) reinterpret_cast<uint4*>(tile)[i] = v[it];
+                if (i < NT && gx >= 0 && gx + 16 <= j.sw) st_chunk(i / NCH, i % NCH, v[it]);
             }
         } else {
             unsigned a[NIT][5];
@@ -563,9 +752,9 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
                 // rows differ in alignment when the pitch is odd: the shift is the chunk's own
                 const unsigned sh = 8u * (unsigned)((size_t)(src + (long long)reflect101(sy0 + r, j.sh) * j.spitch + gx) & 3);
                 if (i < NT && gx >= 4 && gx + 20 <= j.sw)
-                    reinterpret_cast<uint4*>(tile)[i] =
-                        make_uint4(__funnelshift_r(a[it][0], a[it][1], sh), __funnelshift_r(a[it][1], a[it][2], sh),
-                                   __funnelshift_r(a[it][2], a[it][3], sh), __funnelshift_r(a[it][3], a[it][4], sh));
+                    st_chunk(i / NCH, i % NCH,
+                             make_uint4(__funnelshift_r(a[it][0], a[it][1], sh), __funnelshift_r(a[it][1], a[it][2], sh),
+                                        __funnelshift_r(a[it][2], a[it][3], sh), __funnelshift_r(a[it][3], a[it][4], sh)));
             }
         }
     }
@@ -591,9 +780,10 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
                     wv[q] = t;
                 }
             }
-            reinterpret_cast<uint4*>(tile)[r * NCH + k] = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+            st_chunk(r, k, make_uint4(wv[0], wv[1], wv[2], wv[3]));
         }
     }
+    }   // LDG loader
     __syncthreads();
     if (j.copy[cam]) {   // source rows 2*Y0 .. 2*Y0+31, columns 2*X0 .. 2*X0+255 = tile rows 2.., columns 16..
         uint8_t* cp = j.copy[cam] + (long long)seq * j.copy_seq_stride;
@@ -602,7 +792,7 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
             const int r = i >> 4, k = i & 15;
             const int gy = 2 * Y0 + r, gx = 2 * X0 + 16 * k;
             if (gy >= j.sh || gx >= j.sw) continue;
-            const uint4 v = *reinterpret_cast<const uint4*>(tile + (r + 2) * PD_TW + 16 + 16 * k);
+            const uint4 v = ld_chunk(r + 2, k + 1);
             uint8_t* o = cp + (long long)gy * j.cpitch + gx;
             if (cal16 && gx + 16 <= j.cpitch) {   // whole chunks: the copy plane's pitch is a multiple of 128
                 *reinterpret_cast<uint4*>(o) = v;
@@ -619,7 +809,7 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
     unsigned hA[2 * PD_ROWS_PER_THREAD + 3], hB[2 * PD_ROWS_PER_THREAD + 3];
 #pragma unroll
     for (int r = 0; r < 2 * PD_ROWS_PER_THREAD + 3; ++r) {
-        const uint8_t* t = tile + (2 * PD_ROWS_PER_THREAD * g + r) * PD_TW + 16 + 8 * c;
+        const uint8_t* t = (c < 16 ? tileA : tileB) + (2 * PD_ROWS_PER_THREAD * g + r) * PD_BW + 16 + 8 * c - (c < 16 ? 0 : 128);
         const unsigned w0 = *reinterpret_cast<const unsigned*>(t - 4);
         const uint2 w12 = *reinterpret_cast<const uint2*>(t);
         const unsigned w3 = *reinterpret_cast<const unsigned*>(t + 8);
@@ -643,17 +833,22 @@ __global__ void __launch_bounds__(PD_THREADS) pyrdown_tile_kernel(PyrDownJob j) 
         }
     }
 }
-static void launch_pyrdown_job(const PyrDownJob& j, int n_img, cudaStream_t st) {
+static void launch_pyrdown_job(const PyrDownJob& j_in, int n_img, cudaStream_t st) {
+    PyrDownJob j = j_in;
     const int gx = (j.dw + PD_OW - 1) / PD_OW;
     const auto blocks = [&](int rpt) { return (long long)gx * ((j.dh + 4 * rpt - 1) / (4 * rpt)) * n_img; };
     const long long enough = 4 * 148;   // a few blocks per SM
-    if (blocks(4) >= enough) {
-        pyrdown_tile_kernel<4><<<dim3(gx, (j.dh + 15) / 16, n_img), PD_THREADS, 0, st>>>(j);
-    } else if (blocks(2) >= enough) {
-        pyrdown_tile_kernel<2><<<dim3(gx, (j.dh + 7) / 8, n_img), PD_THREADS, 0, st>>>(j);
-    } else {
-        pyrdown_tile_kernel<1><<<dim3(gx, (j.dh + 3) / 4, n_img), PD_THREADS, 0, st>>>(j);
-    }
+    const int rpt = blocks(4) >= enough ? 4 : (blocks(2) >= enough ? 2 : 1);
+    // tensor maps of the source planes (x, y, sequence), one per camera; box = half a tile row x the tile height
+    CUtensorMap map[2];
+    memset(map, 0, sizeof(map));
+    const int th = 8 * rpt + 3, n_pl = j.n_cam == 2 ? n_img / 2 : n_img;
+    j.use_tma = j.sw >= 32 && j.sh >= 8;
+    for (int cam = 0; cam < (j.n_cam == 2 ? 2 : 1) && j.use_tma; ++cam)
+        j.use_tma = make_tile_map(&map[cam], j.src[cam], j.sw, j.sh, j.spitch, j.src_seq_stride, n_pl, PD_BW, th) ? 1 : 0;
+    if (rpt == 4) pyrdown_tile_kernel<4><<<dim3(gx, (j.dh + 15) / 16, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
+    else if (rpt == 2) pyrdown_tile_kernel<2><<<dim3(gx, (j.dh + 7) / 8, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
+    else pyrdown_tile_kernel<1><<<dim3(gx, (j.dh + 3) / 4, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
 }
 void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch, uint8_t* dst,
                     long long dst_stride, int dw, int dh, int dpitch, int n_img, cudaStream_t st) {
@@ -784,9 +979,9 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
     int* nA = d.fast_nA + (long long)slot * d.n_seq;
     const uint8_t* l0 = d.pyr + pg.base(0, slot, 0) + pg.off[0];
     launch_fast(l0, ctx_seq_stride, pc.width, pc.height, pg.pitch[0], d.n_seq, pc.thr_hi, pc.thr_hi, nullptr, 0, 0,
-                keysA, nullptr, bg, st, nA, nullptr, 0);
+                keysA, nullptr, bg, st, nA, nullptr, 0, d.fast_work + 2 * slot);
     launch_fast(l0, ctx_seq_stride, pc.width, pc.height, pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0,
-                nullptr, keysB, bg, st, nullptr, nA, pc.pre_matching_threshold);
+                nullptr, keysB, bg, st, nullptr, nA, pc.pre_matching_threshold, nullptr);
     return launches + 2;
 }
 

@@ -13,7 +13,8 @@ namespace svo {
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg,
-                 cudaStream_t st, int* countA = nullptr, const int* gate = nullptr, int gate_min = 0);
+                 cudaStream_t st, int* countA = nullptr, const int* gate = nullptr, int gate_min = 0,
+                 int* work = nullptr /* 2 zeroed ints: dynamic tile order for the persistent blocks */);
 // countA[i]: incremented once per bucket of image i that receives its first keysA entry.  gate: the blocks of image
 // i return at once when gate[i] >= gate_min (the pipeline's low-threshold pass behind the thr_hi pass).
 // ordered (row-major) compaction of a dense response map into a keypoint list
