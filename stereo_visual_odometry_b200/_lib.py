@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsvo_b200.so")
+LIB_PATH = os.environ.get("SVO_LIB_PATH") or os.path.join(_HERE, "libsvo_b200.so")   # (override: A/B builds)
 CSRC = os.path.join(_HERE, "csrc")
 
 

@@ -1165,6 +1165,12 @@ void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeCon
 // ============================================================================
 // KLT: one warp per feature, the whole circular chain L0->L1->R1->R0->L0 per work item
 constexpr int KLT_WARPS = 8;
+#ifndef SVO_KLT_MINB
+#define SVO_KLT_MINB 3       // resident blocks per SM the speculative kernels are compiled for (80 registers: measured best)
+#endif
+#ifndef SVO_KLT_MINB_SER
+#define SVO_KLT_MINB_SER 3   // ... and klt_kernel
+#endif
 __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom& pg) {
     LkPyramid p;
 #pragma unroll
@@ -1230,7 +1236,7 @@ __device__ __forceinline__ void circ_bases(const PyrGeom& pg, int seq, int slot_
 //
 // klt_kernel tracks the bucketed features listed in d.todo (the ones whose result was not found in the
 // speculative cache by bucket_merge_kernel; all of them when speculation is off).
-__global__ void __launch_bounds__(KLT_WARPS * 32)
+__global__ void __launch_bounds__(KLT_WARPS * 32, SVO_KLT_MINB_SER)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
@@ -1361,7 +1367,7 @@ __global__ void __launch_bounds__(256) spec_fast_list_kernel(DevArrays d, Bucket
     if (has && !late) list[bf + __popc(mf & below)] = b;
     if (late) list[bg.nb - 1 - (bl + __popc(ml & below))] = b;
 }
-__global__ void __launch_bounds__(KLT_WARPS * 32, 4)
+__global__ void __launch_bounds__(KLT_WARPS * 32, SVO_KLT_MINB)
 klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int keybuf,
                      int specbuf) {
     __shared__ LkScratch patch[KLT_WARPS];
@@ -1407,7 +1413,7 @@ klt_spec_fast_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int 
         }
     }
 }
-__global__ void __launch_bounds__(KLT_WARPS * 32, 4)
+__global__ void __launch_bounds__(KLT_WARPS * 32, SVO_KLT_MINB)
 klt_spec_trk_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, BucketGeom bg, int slot_prev, int slot_cur, int specbuf) {
     __shared__ LkScratch patch[KLT_WARPS];
     const int seq = blockIdx.y;
