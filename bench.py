@@ -501,6 +501,29 @@ def run_gpu(args, rank, world, local_rank):
             L_.svo_get_stage_time(ctx, s_, C.byref(msv), C.byref(ln))
             stages[nm] = {"us_per_frame": 1e3 * msv.value / n_t, "launches_per_frame": ln.value / n_t}
         check(L_.svo_enable_timers(ctx, 0))
+        # ---------------- look-ahead ingest of ONE trajectory: K frames per launch set
+        lookahead = {}
+        for K in (8, 16):
+            pk = default_params(W, H, device=local_rank, lookahead=K)
+            ck = L_.svo_create(C.byref(pk))
+            Plk, Prk = np.ascontiguousarray(seq.Pl), np.ascontiguousarray(seq.Pr)
+            check(L_.svo_set_projection(ck, ptr(Plk, C.c_float), ptr(Prk, C.c_float)))
+            check(L_.svo_enable_timers(ck, 1))
+            frk = FrameResult()
+            jj = 0
+            for rep in range(6):
+                if rep == 2:
+                    check(L_.svo_reset_timers(ck))
+                lp = (C.c_void_p * K)(*[Lp_ptr[pingpong(jj + q, n_unique)] for q in range(K)])
+                rp = (C.c_void_p * K)(*[Rp_ptr[pingpong(jj + q, n_unique)] for q in range(K)])
+                check(L_.svo_submit_frames(ck, K, lp, rp, W))
+                jj += K
+                while L_.svo_pending(ck) > 0:
+                    check(L_.svo_collect(ck, C.byref(frk)))
+            msv, ln = C.c_double(0), C.c_longlong(0)
+            L_.svo_get_stage_time(ck, 0, C.byref(msv), C.byref(ln))
+            lookahead[K] = 1e3 * msv.value / 4   # us per K-frame launch set
+            L_.svo_destroy(ck)
     L_.svo_destroy(ctx)
 
     e2e = None
@@ -629,6 +652,13 @@ def run_gpu(args, rank, world, local_rank):
                         "limiter": "SM issue (FAST 55 %, pyrDown 59-69 % issue-slot utilisation), not HBM: see profiles/"}
         else:
             roofline = dict(roofline_single, traffic=None, peak_source=peak_src)
+        # one trajectory with look-ahead: K = 8 frames per ingest launch set (svo_submit_frames)
+        roofline_lookahead = {}
+        for K_, usk in lookahead.items():
+            ak = K_ * B_ALG_FRAME / (usk * 1e-6) / 1e9
+            roofline_lookahead["K%d" % K_] = {"bound": "hbm", "kernel": "ingest of ONE trajectory, %d frames per launch set (svo_submit_frames)" % K_,
+                                              "achieved": ak, "peak": peak, "unit": "GB/s", "frac": ak / peak, "us_per_launch_set": usk,
+                                              "us_per_frame": usk / K_, "algorithmic_bytes_per_launch_set": K_ * B_ALG_FRAME}
         roofline_batch = roofline_single   # kept under the old key for continuity: the 1-frame figure
         cpu = cpu_baseline(seq, Lh, Rh) if not args.no_cpu_baseline else None
         out = {
@@ -643,7 +673,7 @@ def run_gpu(args, rank, world, local_rank):
                        "lk_iters_per_frame": mean_iters, "success_rate": success_rate,
                        "rel_translation_err_vs_gt_median": float(np.median(terr)) if terr else None},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "roofline_single_frame": roofline_batch, "stages": stages, "batch64": batch, "cpu_baseline": cpu,
+            "roofline_single_frame": roofline_batch, "roofline_lookahead": roofline_lookahead, "stages": stages, "batch64": batch, "cpu_baseline": cpu,
             "render_s": render_s,
         }
         print(json.dumps(out))

@@ -66,6 +66,8 @@ typedef struct svo_params {
     int channels;                 /* 1 = 8UC1 (default); 3 = interleaved 8UC3 exactly as the reference CLI feeds
                                      cv::imread's BGR images (src/main.cpp:37-46): FAST scans the first `width`
                                      bytes of every row, pyramids and LK run on all three channels        */
+    int lookahead;                /* K > 1: svo_submit_frames may hand over up to K frames per call; the context then
+                                     keeps 2 K + 3 pyramid ring slots instead of 3 (single sequence, 8UC1)        */
 } svo_params;
 
 /* Per-frame result of the pipeline (one per sequence). */
@@ -126,10 +128,17 @@ int svo_process_frame_batch_dev(svo_ctx* ctx, const uint8_t* left_dev, const uin
  * once; svo_collect blocks until the OLDEST uncollected frame is done and returns its result exactly as
  * svo_process_frame_batch would (frames are processed strictly in submission order, results are
  * identical to the synchronous calls).  The ingest of frame f + 1 (its own stream) overlaps the
- * tracking chain of frame f.  At most 8 frames may be pending (SVO_ERR_STATE beyond that). */
+ * tracking chain of frame f.  At most 32 frames may be pending (SVO_ERR_STATE beyond that). */
 int svo_submit_frame(svo_ctx* ctx, const uint8_t* left, const uint8_t* right, int stride);
 int svo_submit_frame_batch(svo_ctx* ctx, const uint8_t* left, const uint8_t* right, int stride,
                            long long seq_stride);
+/* Look-ahead form for ONE trajectory whose next K frames are already there (a recording, a camera buffer): the
+ * state-independent stages -- the pyramids of both images and FAST on the left one, src/vo.cpp:200-201, 325 -- run
+ * for all K frames in ONE launch set (the batched kernels, frame index in place of the sequence index), then the K
+ * frames go through the tracking chain one after the other exactly like K svo_submit_frame calls; results are
+ * identical and are collected with svo_collect in order.  Needs svo_params.lookahead >= K, n_seq == 1, 8UC1.
+ * lefts / rights: K host pointers (pinned memory recommended), all frames with the same stride. */
+int svo_submit_frames(svo_ctx* ctx, int n_frames, const uint8_t* const* lefts, const uint8_t* const* rights, int stride);
 int svo_collect(svo_ctx* ctx, svo_frame_result* results /* [n_seq], may be NULL */);
 int svo_pending(svo_ctx* ctx);                  /* submitted, not yet collected */
 /* Makes the context's primary stream (svo_stream) wait for everything enqueued so far on the context's

@@ -281,6 +281,8 @@ class VisualOdometry {
     svo_ctx* ctx_ = nullptr;                 /* device-resident state (pyramids, currentVOFeatures, R|t, last_transform) */
     cv::Mat imageRightT0_, imageLeftT0_;     /* t0 images for the public circularMatching(): fetched from the device on demand */
     bool t0_fetched_ = false;
+    int lookahead_ = 0;
+    std::vector<cv::Mat> keepAlive_;
     int cols_ = 0, rows_ = 0, type_ = 0;     /* geometry the context was created for */
     cv::Mat_<float64> last_transform = cv::Mat_<float64>::eye(4, 4);
     std::ofstream vo_log;
@@ -295,6 +297,7 @@ class VisualOdometry {
         rows_ = img.rows;
         type_ = img.type();
         svo_params p = detail::params_for(img);
+        p.lookahead = lookahead_;
         ctx_ = svo_create(&p);
         if (!ctx_) throw std::runtime_error(std::string("svo_create: ") + svo_last_error());
         if (!leftCameraProjection_.empty())
@@ -381,6 +384,34 @@ class VisualOdometry {
         pendingLeft_ = image_left;   /* shallow references: keep the buffers alive */
         pendingRight_ = image_right;
     }
+    /* Look-ahead form (svo_submit_frames): up to `lookahead` frames that are already there; their pyramids and FAST
+     * corners are computed in one launch set, the results come back one by one through collect_frame().  Set the
+     * look-ahead depth before the first frame with set_lookahead(K), K <= 16. */
+    void set_lookahead(int k) { lookahead_ = k; }
+    void submit_frames(const std::vector<cv::Mat>& lefts, const std::vector<cv::Mat>& rights) {
+        if (lefts.empty() || lefts.size() != rights.size()) throw std::runtime_error("svo: submit_frames needs equally many left and right frames");
+        std::vector<const uint8_t*> lp, rp;
+        int s0 = 0;
+        for (size_t i = 0; i < lefts.size(); ++i) {
+            int sl, sr;
+            lp.push_back(detail::gray(lefts[i], sl));
+            rp.push_back(detail::gray(rights[i], sr));
+            if (i == 0) s0 = sl;
+            if (sl != s0 || sr != s0 || lefts[i].rows != lefts[0].rows || lefts[i].cols != lefts[0].cols ||
+                rights[i].rows != lefts[0].rows || rights[i].cols != lefts[0].cols)
+                throw std::runtime_error("svo: submit_frames needs equally sized frames with equal strides");
+        }
+        ensure_ctx(lefts[0]);
+        if (leftCameraProjection_.empty()) {
+            float z[12] = {0};
+            detail::check(svo_set_projection(ctx_, z, z));
+        }
+        detail::check(svo_submit_frames(ctx_, (int)lp.size(), lp.data(), rp.data(), s0));
+        pendingLeft_ = lefts.back();
+        pendingRight_ = rights.back();
+        keepAlive_.insert(keepAlive_.end(), lefts.begin(), lefts.end());   /* shallow references until collected */
+        keepAlive_.insert(keepAlive_.end(), rights.begin(), rights.end());
+    }
     std::pair<bool, cv::Mat_<float64>> collect_frame() {
         svo_frame_result r;
         detail::check(svo_collect(ctx_, &r));
@@ -392,6 +423,7 @@ class VisualOdometry {
         if (svo_pending(ctx_) == 0) {   /* nothing in flight any more: drop the references to the caller's buffers */
             pendingLeft_ = cv::Mat();
             pendingRight_ = cv::Mat();
+            keepAlive_.clear();
         }
         return std::make_pair(r.success != 0, T);
     }

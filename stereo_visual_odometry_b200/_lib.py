@@ -33,7 +33,7 @@ class Params(C.Structure):
         ("ransac_reproj_error", C.c_float), ("ransac_iterations", C.c_int),
         ("ransac_hypotheses", C.c_int), ("ransac_confidence", C.c_float),
         ("max_translation_norm", C.c_double), ("max_rotation_norm", C.c_double),
-        ("ransac_seed", C.c_uint64), ("device", C.c_int), ("channels", C.c_int),
+        ("ransac_seed", C.c_uint64), ("device", C.c_int), ("channels", C.c_int), ("lookahead", C.c_int),
     ]
 
 
@@ -52,7 +52,7 @@ REASONS = {0: "", 1: "first", 2: "few_features", 3: "pnp_failed", 4: "too_big"}
 SYMBOLS = [
     "svo_version", "svo_last_error", "svo_device_count", "svo_default_params", "svo_create",
     "svo_destroy", "svo_set_projection", "svo_process_frame", "svo_process_frame_batch",
-    "svo_process_frame_batch_dev", "svo_submit_frame", "svo_submit_frame_batch", "svo_collect", "svo_pending", "svo_stream_join", "svo_pipeline_info",
+    "svo_process_frame_batch_dev", "svo_submit_frame", "svo_submit_frame_batch", "svo_submit_frames", "svo_collect", "svo_pending", "svo_stream_join", "svo_pipeline_info",
     "svo_synchronize", "svo_get_result", "svo_get_tap", "svo_get_frame_images", "svo_stream",
     "svo_launch_count", "svo_enable_timers", "svo_get_stage_time", "svo_reset_timers",
     "svo_fast_detect", "svo_bucket_filter", "svo_build_pyramid", "svo_lk_track",
@@ -96,6 +96,7 @@ def lib():
     L.svo_process_frame_batch_dev.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, vp]
     L.svo_submit_frame.argtypes = [vp, u8p, u8p, C.c_int]
     L.svo_submit_frame_batch.argtypes = [vp, u8p, u8p, C.c_int, C.c_longlong]
+    L.svo_submit_frames.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int]
     L.svo_collect.argtypes = [vp, C.POINTER(FrameResult)]
     L.svo_pending.argtypes = [vp]
     L.svo_stream_join.argtypes = [vp]

@@ -29,7 +29,9 @@
 
 using namespace svo;
 
-#define SVO_RESULT_RING 8
+#define SVO_RESULT_RING 32
+#define SVO_EV_RING 32   // per-frame events live in rings of this many frames
+#define SVO_EV_MASK (SVO_EV_RING - 1)
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) {
     g_err = msg;
@@ -85,6 +87,7 @@ extern "C" void svo_default_params(svo_params* p, int width, int height) {
     p->ransac_seed = 0;   /* unused: the sample stream is OpenCV's fixed RNG((uint64)-1) */
     p->device = 0;
     p->channels = 1;
+    p->lookahead = 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -98,11 +101,11 @@ struct svo_ctx {
     cudaStream_t stream_in = nullptr;   // ingest of the next frame (H2D, pyramid, FAST)
     cudaStream_t stream_k = nullptr;    // speculative KLT of the FAST-winner candidates (and the un-cached fallback)
     cudaStream_t stream_k2 = nullptr;   // speculative KLT of the matched-feature candidates (same partition)
-    cudaEvent_t ev_spf[4] = {nullptr, nullptr, nullptr, nullptr};   // FAST-winner candidates of frame f tracked
-    cudaEvent_t ev_bm[4] = {nullptr, nullptr, nullptr, nullptr};    // bucket merge of frame f done (predictions for f + 1)
+    cudaEvent_t ev_spf[SVO_EV_RING] = {};   // FAST-winner candidates of frame f tracked
+    cudaEvent_t ev_bm[SVO_EV_RING] = {};    // bucket merge of frame f done (predictions for f + 1)
     cudaStream_t stream_fb = nullptr;   // pose refit + result
     cudaStream_t stream_h2d = nullptr;  // host frames -> staging ring (copy engine only)
-    cudaEvent_t ev_h2d[4] = {nullptr, nullptr, nullptr, nullptr};   // staging copy of frame f complete
+    cudaEvent_t ev_h2d[SVO_EV_RING] = {};   // staging copy of frame f complete
     cudaStream_t stream_full = nullptr; // whole-GPU stream for serial frames (== stream when there are no partitions)
     int klt_blocks_full = 0;            // persistent KLT blocks per sequence on the whole GPU
     void* green[3] = {nullptr, nullptr, nullptr};   // CUgreenCtx of the chain / ingest / KLT partitions
@@ -114,12 +117,12 @@ struct svo_ctx {
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     int f_share = 59;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
-    cudaEvent_t ev_in[4] = {nullptr, nullptr, nullptr, nullptr};    // ingest(f) complete
-    cudaEvent_t ev_td[4] = {nullptr, nullptr, nullptr, nullptr};    // every bucketed feature of f has its circular-matching result
-    cudaEvent_t ev_sel[4] = {nullptr, nullptr, nullptr, nullptr};   // select(f) done: pyramids / keys of f - 1 are free
-    cudaEvent_t ev_trk[4] = {nullptr, nullptr, nullptr, nullptr};   // speculative KLT of frame f complete
-    cudaEvent_t ev_fa[4] = {nullptr, nullptr, nullptr, nullptr};    // chain of frame f complete
-    cudaEvent_t ev_fb[4] = {nullptr, nullptr, nullptr, nullptr};    // refit + result of frame f complete
+    cudaEvent_t ev_in[SVO_EV_RING] = {};    // ingest(f) complete
+    cudaEvent_t ev_td[SVO_EV_RING] = {};    // every bucketed feature of f has its circular-matching result
+    cudaEvent_t ev_sel[SVO_EV_RING] = {};   // select(f) done: pyramids / keys of f - 1 are free
+    cudaEvent_t ev_trk[SVO_EV_RING] = {};   // speculative KLT of frame f complete
+    cudaEvent_t ev_fa[SVO_EV_RING] = {};    // chain of frame f complete
+    cudaEvent_t ev_fb[SVO_EV_RING] = {};    // refit + result of frame f complete
     cudaEvent_t ev_done[SVO_RESULT_RING];                           // result of frame f in host_result ring
     std::vector<void*> allocs;
     uint8_t* stage_L = nullptr;
@@ -220,6 +223,9 @@ static int validate_params(const svo_params* p) {
     if (p->max_level < 0 || p->max_level >= SVO_MAX_LEVELS) return fail(SVO_ERR_INVALID, "max_level must be 0..3");
     if (p->buckets_along_height < 1 || p->buckets_along_width < 1) return fail(SVO_ERR_INVALID, "bad bucket grid");
     if (p->fast_threshold < 4 || p->fast_threshold > 255) return fail(SVO_ERR_INVALID, "fast_threshold must be 4..255");
+    if (p->lookahead < 0 || p->lookahead > 16) return fail(SVO_ERR_INVALID, "lookahead must be 0..16");
+    if (p->lookahead > 1 && (p->n_seq != 1 || p->channels == 3))
+        return fail(SVO_ERR_INVALID, "lookahead needs a single-sequence 8UC1 context");
     if (p->ransac_hypotheses < 1 || p->ransac_hypotheses > 4096)
         return fail(SVO_ERR_INVALID, "ransac_hypotheses must be 1..4096");
     return SVO_OK;
@@ -352,7 +358,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         int rc = create_streams(c, p);
         if (rc != SVO_OK) return rc;
     }
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < SVO_EV_RING; ++i) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_sel[i], cudaEventDisableTiming));
@@ -369,6 +375,8 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
     }
     c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size, channels_of(*p));
+    // look-ahead contexts: room for the batch being tracked and the batch being ingested
+    c->pg.n_slots = p->lookahead > 1 ? 2 * p->lookahead + 3 : SVO_PYR_SLOTS;
     c->bg = make_bucket_geom(p->height, p->width, p->buckets_along_height, p->buckets_along_width,
                              p->bucket_start_row, p->age_threshold, p->fast_threshold);
     PipeConfig& pc = c->pc;
@@ -398,9 +406,9 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     cap = (cap + 3) & ~3;   // word-aligned per-sequence status bytes
     d.cap = cap;
     const size_t S = (size_t)p->n_seq, C = S * (size_t)cap;
-    CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 2 * SVO_PYR_SLOTS * S));
-    CU(dev_alloc(c, &d.fastkeys, (size_t)2 * SVO_PYR_SLOTS * S * c->bg.nb));
-    CU(dev_alloc(c, &d.fast_nA, (size_t)SVO_PYR_SLOTS * S));
+    CU(dev_alloc(c, &d.pyr, (size_t)c->pg.image_bytes * 2 * c->pg.n_slots * S));
+    CU(dev_alloc(c, &d.fastkeys, (size_t)2 * c->pg.n_slots * S * c->bg.nb));
+    CU(dev_alloc(c, &d.fast_nA, (size_t)c->pg.n_slots * S));
     CU(dev_alloc(c, &d.trackkeys, S * c->bg.nb));
     CU(dev_alloc(c, &d.state, S));
     CU(dev_alloc(c, &d.result, S));
@@ -427,7 +435,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.specT_it, C));
     CU(dev_alloc(c, &d.cntF, S));
     CU(dev_alloc(c, &d.cntT, S));
-    CU(dev_alloc(c, &d.fast_work, (size_t)2 * SVO_PYR_SLOTS));
+    CU(dev_alloc(c, &d.fast_work, (size_t)2 * c->pg.n_slots));
     CU(dev_alloc(c, &d.listF, S * c->bg.nb));
     CU(dev_alloc(c, &d.nF, 2 * S));
     CU(dev_alloc(c, &d.predT, (size_t)2 * S * c->bg.nb));
@@ -444,8 +452,8 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
         CU(cudaStreamSynchronize(c->stream));
     }
     // staging ring for host frames: slot f % 3 (the copy of frame f + 1 runs while frame f is being ingested)
-    CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S * SVO_PYR_SLOTS, false));
-    CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S * SVO_PYR_SLOTS, false));
+    CU(dev_alloc(c, &c->stage_L, (size_t)c->pg.pitch[0] * p->height * S * c->pg.n_slots, false));
+    CU(dev_alloc(c, &c->stage_R, (size_t)c->pg.pitch[0] * p->height * S * c->pg.n_slots, false));
     CU(cudaMallocHost((void**)&c->host_result, sizeof(svo_frame_result) * S * SVO_RESULT_RING));
     // initial state: rotation = I, translation = 0, last_transform = I (vo.h:262-264)
     std::vector<SeqState> init(S);
@@ -512,7 +520,7 @@ extern "C" void svo_destroy(svo_ctx* c) {
         if (st) cudaStreamSynchronize(st);
     trace_dump(c);
     for (void* q : c->allocs) cudaFree(q);
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < SVO_EV_RING; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
         if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
         if (c->ev_sel[i]) cudaEventDestroy(c->ev_sel[i]);
@@ -646,11 +654,12 @@ static cudaStream_t ingest_stream(const svo_ctx* c, bool speculate) {
 // `left`/`right`: device planes, or nullptr when level 0 of the slot was already written (H2D in place).
 // to_host: also copy the result structs into the pinned host ring (slot tracked % SVO_RESULT_RING).
 static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, int stride, long long seq_stride,
-                         svo_frame_result* results_dev, bool to_host, bool speculate) {
+                         svo_frame_result* results_dev, bool to_host, bool speculate, bool ingested = false) {
     const long long f = c->frames;
     const bool first = f == 0;
-    const int cur = (int)(f % SVO_PYR_SLOTS), prev = (int)((f + SVO_PYR_SLOTS - 1) % SVO_PYR_SLOTS);
-    const int e = (int)(f & 3), e1 = (int)((f + 3) & 3);   // event slots of frame f and f - 1
+    const int NS = c->pg.n_slots;
+    const int cur = (int)(f % NS), prev = (int)((f + NS - 1) % NS);
+    const int e = (int)(f & SVO_EV_MASK), e1 = (int)((f + SVO_EV_MASK) & SVO_EV_MASK);   // event slots of frame f and f - 1
     // speculation pays when frames are in flight (its kernels then run beside the previous frame's pose chain);
     // a caller that waits for every result before sending the next frame, and the per-stage timers, get the
     // plain serial chain on one stream that owns the whole GPU
@@ -660,15 +669,19 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     cudaStream_t sI = tm ? sP : c->stream_in, sK = tm ? sP : c->stream_k, sB = tm ? sP : c->stream_fb;
     if (tm && !first) CU(cudaStreamWaitEvent(sP, c->ev_fb[e1], 0));   // the previous frame may have run on the partitions
     if (c->timers) cudaEventRecord(c->ev[0], sP);
-    int n_ingest;
-    {
-        TraceScope ts(c, "ingest", 0, sI);
-        n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
-    }
-    c->launches += n_ingest;
-    if (!tm) {
-        CU(cudaEventRecord(c->ev_in[e], sI));
+    int n_ingest = 0;
+    if (ingested) {   // pyramids + FAST keys of this frame came with a look-ahead launch set (svo_submit_frames): ev_in[e] is recorded
         CU(cudaStreamWaitEvent(sP, c->ev_in[e], 0));
+    } else {
+        {
+            TraceScope ts(c, "ingest", 0, sI);
+            n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
+        }
+        c->launches += n_ingest;
+        if (!tm) {
+            CU(cudaEventRecord(c->ev_in[e], sI));
+            CU(cudaStreamWaitEvent(sP, c->ev_in[e], 0));
+        }
     }
     if (spec && !first) {
         // the two candidate classes run side by side, each on its share (f_share) of the partition's block slots: F(f) as soon
@@ -788,7 +801,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
 // the ingest stream may not start writing slot f % 3 / key buffer f % 3 before frame f - 2 is done reading
 static int wait_ring(svo_ctx* c, bool speculate) {
     const long long f = c->frames;
-    if (f >= 2) CU(cudaStreamWaitEvent(ingest_stream(c, speculate), c->ev_sel[(f - 2) & 3], 0));
+    if (f >= 2) CU(cudaStreamWaitEvent(ingest_stream(c, speculate), c->ev_sel[(f - 2) & SVO_EV_MASK], 0));
     return SVO_OK;
 }
 
@@ -817,10 +830,10 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
     const long long plane = (long long)P0 * H;
     // host -> staging slot f % 3 on the copy stream: waits only for the ingest of frame f - 3 (the slot's last
     // reader), so the copy of the next frame runs ahead of everything the GPU is still doing for this one
-    uint8_t* sl = c->stage_L + (f % SVO_PYR_SLOTS) * plane * S;
-    uint8_t* sr = c->stage_R + (f % SVO_PYR_SLOTS) * plane * S;
+    uint8_t* sl = c->stage_L + (f % c->pg.n_slots) * plane * S;
+    uint8_t* sr = c->stage_R + (f % c->pg.n_slots) * plane * S;
     cudaStream_t sH = c->stream_h2d;
-    if (f >= SVO_PYR_SLOTS) CU(cudaStreamWaitEvent(sH, c->ev_in[(f - SVO_PYR_SLOTS) & 3], 0));
+    if (f >= c->pg.n_slots) CU(cudaStreamWaitEvent(sH, c->ev_in[(f - c->pg.n_slots) & SVO_EV_MASK], 0));
     if (S == 1 || seq_stride == (long long)stride * H) {
         CU(cudaMemcpy2DAsync(sl, P0, left, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sH));
         CU(cudaMemcpy2DAsync(sr, P0, right, stride, W, (size_t)H * S, cudaMemcpyHostToDevice, sH));
@@ -830,11 +843,11 @@ extern "C" int svo_submit_frame_batch(svo_ctx* c, const uint8_t* left, const uin
             CU(cudaMemcpy2DAsync(sr + s * plane, P0, right + s * seq_stride, stride, W, H, cudaMemcpyHostToDevice, sH));
         }
     }
-    CU(cudaEventRecord(c->ev_h2d[f & 3], sH));
+    CU(cudaEventRecord(c->ev_h2d[f & SVO_EV_MASK], sH));
     int rc = wait_ring(c, in_flight);
     if (rc != SVO_OK) return rc;
     cudaStream_t sI = ingest_stream(c, in_flight);
-    CU(cudaStreamWaitEvent(sI, c->ev_h2d[f & 3], 0));
+    CU(cudaStreamWaitEvent(sI, c->ev_h2d[f & SVO_EV_MASK], 0));
     return enqueue_frame(c, sl, sr, P0, plane, nullptr, true, in_flight);
 }
 
@@ -842,6 +855,66 @@ extern "C" int svo_submit_frame(svo_ctx* c, const uint8_t* left, const uint8_t* 
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     if (c->d.n_seq != 1) return fail(SVO_ERR_INVALID, "svo_submit_frame needs a context with n_seq == 1");
     return svo_submit_frame_batch(c, left, right, stride, 0);
+}
+
+extern "C" int svo_submit_frames(svo_ctx* c, int n_frames, const uint8_t* const* lefts, const uint8_t* const* rights,
+                                 int stride) {
+    if (!c || !lefts || !rights) return fail(SVO_ERR_INVALID, "NULL argument");
+    if (c->d.n_seq != 1 || c->pg.cn != 1) return fail(SVO_ERR_INVALID, "svo_submit_frames needs a single-sequence 8UC1 context");
+    if (n_frames < 1 || n_frames > (c->p.lookahead > 1 ? c->p.lookahead : 1))
+        return fail(SVO_ERR_INVALID, "n_frames must be 1..svo_params.lookahead");
+    if (!c->have_projection) return fail(SVO_ERR_STATE, "svo_set_projection has not been called");
+    if (stride < c->p.width) return fail(SVO_ERR_INVALID, "stride < width");
+    if (c->tracked - c->collected + n_frames > SVO_RESULT_RING)
+        return fail(SVO_ERR_STATE, "result ring full: call svo_collect before submitting more frames");
+    for (int i = 0; i < n_frames; ++i)
+        if (!lefts[i] || !rights[i]) return fail(SVO_ERR_INVALID, "NULL frame pointer");
+    if (n_frames == 1) return svo_submit_frame_batch(c, lefts[0], rights[0], stride, 0);
+    CU(cudaSetDevice(c->p.device));
+    const bool in_flight = c->tracked > c->collected;
+    const long long f = c->frames;
+    const int NS = c->pg.n_slots, W = c->p.width, H = c->p.height, P0 = c->pg.pitch[0];
+    const long long plane = (long long)P0 * H;
+    cudaStream_t sH = c->stream_h2d;
+    // staging slots (g % NS) are free once the ingest of frame g - NS has read them
+    if (f + n_frames - 1 >= NS) CU(cudaStreamWaitEvent(sH, c->ev_in[(f + n_frames - 1 - NS) & SVO_EV_MASK], 0));
+    for (int i = 0; i < n_frames; ++i) {
+        const long long slot = (f + i) % NS;
+        CU(cudaMemcpy2DAsync(c->stage_L + slot * plane, P0, lefts[i], stride, W, H, cudaMemcpyHostToDevice, sH));
+        CU(cudaMemcpy2DAsync(c->stage_R + slot * plane, P0, rights[i], stride, W, H, cudaMemcpyHostToDevice, sH));
+    }
+    CU(cudaEventRecord(c->ev_h2d[f & SVO_EV_MASK], sH));
+    cudaStream_t sI = ingest_stream(c, in_flight);
+    // ring slots / FAST key buffers of frames f .. f + n - 1 were last used by frames up to f + n - 1 - NS, whose
+    // pyramids frame f + n - NS still reads as "previous": its select must be done
+    const long long last_reader = f + n_frames - NS;
+    if (last_reader >= 0) CU(cudaStreamWaitEvent(sI, c->ev_sel[last_reader & SVO_EV_MASK], 0));
+    if (f >= 1) CU(cudaStreamWaitEvent(sI, c->ev_fb[(f - 1) & SVO_EV_MASK], 0));   // (a serial predecessor may have run elsewhere)
+    CU(cudaStreamWaitEvent(sI, c->ev_h2d[f & SVO_EV_MASK], 0));
+    if (c->timers) cudaEventRecord(c->ev[0], sI);
+    int n_launch = 0;
+    for (int done = 0; done < n_frames;) {   // consecutive slots; the ring may wrap once
+        const int slot0 = (int)((f + done) % NS);
+        const int cnt = n_frames - done < NS - slot0 ? n_frames - done : NS - slot0;
+        n_launch += launch_ingest_frames(c->d, c->pg, c->bg, c->pc, c->stage_L + slot0 * plane, c->stage_R + slot0 * plane, P0,
+                                         plane, slot0, cnt, sI);
+        done += cnt;
+    }
+    c->launches += n_launch;
+    for (int i = 0; i < n_frames; ++i) CU(cudaEventRecord(c->ev_in[(f + i) & SVO_EV_MASK], sI));
+    if (c->timers) {
+        cudaEventRecord(c->ev[1], sI);
+        CU(cudaStreamSynchronize(sI));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+        c->stage_ms[0] += ms;
+        c->stage_launches[0] += n_launch;
+    }
+    for (int i = 0; i < n_frames; ++i) {
+        const int rc = enqueue_frame(c, nullptr, nullptr, P0, plane, nullptr, true, in_flight || i > 0, true);
+        if (rc != SVO_OK) return rc;
+    }
+    return SVO_OK;
 }
 
 extern "C" int svo_pending(svo_ctx* c) { return c ? (int)(c->tracked - c->collected) : SVO_ERR_INVALID; }
@@ -896,7 +969,7 @@ extern "C" int svo_get_frame_images(svo_ctx* c, int seq, uint8_t* left_out, uint
     CU(cudaSetDevice(c->p.device));
     int rc = svo_synchronize(c);
     if (rc != SVO_OK) return rc;
-    const int slot = (int)((c->frames - 1) % SVO_PYR_SLOTS);
+    const int slot = (int)((c->frames - 1) % c->pg.n_slots);
     CU(cudaMemcpy2D(left_out, stride, c->d.pyr + c->pg.base(seq, slot, 0) + c->pg.off[0], c->pg.pitch[0], row_bytes,
                     c->p.height, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy2D(right_out, stride, c->d.pyr + c->pg.base(seq, slot, 1) + c->pg.off[0], c->pg.pitch[0], row_bytes,
@@ -939,7 +1012,7 @@ extern "C" int svo_stream_join(svo_ctx* c) {
     if (!c) return fail(SVO_ERR_INVALID, "NULL ctx");
     if (c->frames == 0 || c->timers) return SVO_OK;
     CU(cudaSetDevice(c->p.device));
-    const int e = (int)((c->frames - 1) & 3);
+    const int e = (int)((c->frames - 1) & SVO_EV_MASK);
     CU(cudaStreamWaitEvent(c->stream, c->ev_fb[e], 0));
     CU(cudaStreamWaitEvent(c->stream, c->ev_in[e], 0));
     if (c->spec && c->frames > 1) CU(cudaStreamWaitEvent(c->stream, c->ev_trk[e], 0));

@@ -26,9 +26,10 @@ struct PyrGeom {
     int w[SVO_MAX_LEVELS], h[SVO_MAX_LEVELS], pitch[SVO_MAX_LEVELS];
     long long off[SVO_MAX_LEVELS];   // byte offset of each level inside one image pyramid
     long long image_bytes;           // bytes of one image pyramid (all levels)
+    int n_slots;                     // pyramid ring slots per sequence (3, or lookahead + 3: svo_submit_frames)
     // pyramid of (seq, slot, cam)
     __host__ __device__ long long base(int seq, int slot, int cam) const {
-        return ((long long)(seq * SVO_PYR_SLOTS + slot) * 2 + cam) * image_bytes;
+        return ((long long)(seq * n_slots + slot) * 2 + cam) * image_bytes;
     }
 };
 

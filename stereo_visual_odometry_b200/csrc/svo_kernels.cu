@@ -286,7 +286,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
             BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min, int tiles_x, int tiles_y,
-            const __grid_constant__ CUtensorMap tmap, int use_tma, int n_img, int* __restrict__ work) {
+            const __grid_constant__ CUtensorMap tmap, int use_tma, int n_img, int* __restrict__ work, long long key_stride) {
     // low-threshold pass of the pipeline: only needed when the retry of vo.cpp:327-332 can happen at all, i.e. when
     // the thr_hi pass left fewer than gate_min buckets with a winner (every such bucket yields one bucketed feature)
     if (gate && gate[blockIdx.z] >= gate_min) return;
@@ -453,7 +453,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             if (br >= bg.start_row && 0 < bg.age_threshold) {
                 const unsigned long long key = bucket_key(bucket_score(0, v, bg.fast_threshold),
                                                           SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
-                const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
+                const long long bidx = (long long)z * key_stride + br * bg.n_bw + bc;
                 if (keysB) atomicMax(keysB + bidx, key);
                 if (keysA && v >= thr_hi) {
                     const unsigned long long old = atomicMax(keysA + bidx, key);
@@ -488,7 +488,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
                     if (br >= bg.start_row && 0 < bg.age_threshold) {
                         const unsigned long long key = bucket_key(bucket_score(0, v, bg.fast_threshold),
                                                                   SVO_FAST_ORDER_BASE + (unsigned)(gy * w + gx), v);
-                        const long long bidx = (long long)z * bg.nb + br * bg.n_bw + bc;
+                        const long long bidx = (long long)z * key_stride + br * bg.n_bw + bc;
                         if (keysB) atomicMax(keysB + bidx, key);
                         if (keysA && v >= thr_hi) {
                             const unsigned long long old = atomicMax(keysA + bidx, key);
@@ -519,7 +519,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
 void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pitch, int n_img,
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st,
-                 int* countA, const int* gate, int gate_min, int* work) {
+                 int* countA, const int* gate, int gate_min, int* work, long long key_stride) {
     const int tiles_x = (w + FT_OW - 1) / FT_OW, tiles_y = (h + FT_OH - 1) / FT_OH;
     // ungated: persistent blocks (a few per SM) over all (image, tile) pairs; gated: a few blocks per image
     static int n_sm = 0;
@@ -543,7 +543,8 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
     memset(&tmap, 0, sizeof(tmap));
     const int use_tma = make_tile_map(&tmap, img, w, h, pitch, img_stride, n_img, FT_TW, FT_TH) ? 1 : 0;
     fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch,
-                                             keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work);
+                                             keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work,
+                                             key_stride > 0 ? key_stride : (long long)bg.nb);
 }
 
 // ---- ordered compaction of the response map (row-major == cv::FAST output order)
@@ -982,6 +983,64 @@ int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, c
                 keysA, nullptr, bg, st, nA, nullptr, 0, d.fast_work + 2 * slot);
     launch_fast(l0, ctx_seq_stride, pc.width, pc.height, pg.pitch[0], d.n_seq, pc.thr_lo, pc.thr_hi, nullptr, 0, 0,
                 nullptr, keysB, bg, st, nullptr, nA, pc.pre_matching_threshold, nullptr);
+    return launches + 2;
+}
+
+// ---- look-ahead ingest for ONE trajectory: pyramids + FAST of `n_frames` consecutive frames in one
+// launch set, into the consecutive ring slots slot0 .. slot0 + n_frames - 1 (the stages at src/vo.cpp:200-201 and
+// src/vo.cpp:325 do not depend on the trajectory state).  The frame index takes the place of the sequence index of
+// the batched kernels; frame_stride = distance of consecutive source frames.
+int launch_ingest_frames(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                         const uint8_t* left, const uint8_t* right, int stride, long long frame_stride, int slot0,
+                         int n_frames, cudaStream_t st) {
+    int launches = 0;
+    const long long slot_stride = pg.base(0, 1, 0) - pg.base(0, 0, 0);
+    for (int l = 1; l < pg.nlevels; ++l) {
+        PyrDownJob j;
+        memset(&j, 0, sizeof(j));
+        for (int cam = 0; cam < 2; ++cam) {
+            uint8_t* img = d.pyr + pg.base(0, slot0, cam);
+            j.dst[cam] = img + pg.off[l];
+            j.src[cam] = img + pg.off[l - 1];
+            if (l == 1) {   // frames outside the context: read once, level-0 copy + level 1 from one tile
+                j.src[cam] = cam ? right : left;
+                j.copy[cam] = img + pg.off[0];
+            }
+        }
+        j.src_seq_stride = l == 1 ? frame_stride : slot_stride;
+        j.spitch = l == 1 ? stride : pg.pitch[l - 1];
+        j.sw = pg.w[l - 1]; j.sh = pg.h[l - 1];
+        j.dst_seq_stride = slot_stride;
+        j.dw = pg.w[l]; j.dh = pg.h[l]; j.dpitch = pg.pitch[l];
+        j.copy_seq_stride = slot_stride;
+        j.cpitch = pg.pitch[0];
+        j.n_cam = 2;
+        launch_pyrdown_job(j, n_frames * 2, st);
+        ++launches;
+    }
+    if (pg.nlevels == 1) {
+        PyrDownJob j;
+        memset(&j, 0, sizeof(j));
+        for (int cam = 0; cam < 2; ++cam) {
+            j.src[cam] = cam ? right : left;
+            j.copy[cam] = d.pyr + pg.base(0, slot0, cam) + pg.off[0];
+        }
+        j.src_seq_stride = frame_stride;
+        j.spitch = stride;
+        j.copy_seq_stride = slot_stride;
+        j.cpitch = pg.pitch[0];
+        copy_rows_kernel<<<dim3((pg.w[0] + 255) / 256, pg.h[0], n_frames * 2), 256, 0, st>>>(j, pg.w[0]);
+        ++launches;
+    }
+    // FAST keys of slot s: d.fastkeys + (s * 2 + {A, B}) * nb (n_seq == 1), i.e. a stride of 2 nb between frames
+    unsigned long long* keysA = d.fastkeys + (long long)(slot0 * 2 + 0) * bg.nb;
+    unsigned long long* keysB = d.fastkeys + (long long)(slot0 * 2 + 1) * bg.nb;
+    int* nA = d.fast_nA + slot0;
+    const uint8_t* l0 = d.pyr + pg.base(0, slot0, 0) + pg.off[0];
+    launch_fast(l0, slot_stride, pc.width, pc.height, pg.pitch[0], n_frames, pc.thr_hi, pc.thr_hi, nullptr, 0, 0, keysA,
+                nullptr, bg, st, nA, nullptr, 0, d.fast_work + 2 * slot0, 2ll * bg.nb);
+    launch_fast(l0, slot_stride, pc.width, pc.height, pg.pitch[0], n_frames, pc.thr_lo, pc.thr_hi, nullptr, 0, 0, nullptr,
+                keysB, bg, st, nullptr, nA, pc.pre_matching_threshold, nullptr, 2ll * bg.nb);
     return launches + 2;
 }
 

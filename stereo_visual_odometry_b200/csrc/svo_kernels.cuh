@@ -14,7 +14,8 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
                  int thr_lo, int thr_hi, uint8_t* resp_map, long long map_stride, int map_pitch,
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg,
                  cudaStream_t st, int* countA = nullptr, const int* gate = nullptr, int gate_min = 0,
-                 int* work = nullptr /* 2 zeroed ints: dynamic tile order for the persistent blocks */);
+                 int* work = nullptr /* 2 zeroed ints: dynamic tile order for the persistent blocks */,
+                 long long key_stride = 0 /* distance of the key buffers of consecutive images (0: bg.nb) */);
 // countA[i]: incremented once per bucket of image i that receives its first keysA entry.  gate: the blocks of image
 // i return at once when gate[i] >= gate_min (the pipeline's low-threshold pass behind the thr_hi pass).
 // ordered (row-major) compaction of a dense response map into a keypoint list
@@ -32,6 +33,11 @@ void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, in
 int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
                   cudaStream_t st);
+
+// look-ahead ingest of `n_frames` consecutive frames of ONE sequence into ring slots slot0 .. (n_seq == 1, 8UC1)
+int launch_ingest_frames(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
+                         const uint8_t* left, const uint8_t* right, int stride, long long frame_stride, int slot0,
+                         int n_frames, cudaStream_t st);
 
 // ---- per-frame pipeline stages (all sequences of the context per launch) ----
 void launch_first_frame(const DevArrays& d, cudaStream_t st);

@@ -270,6 +270,23 @@ class VisualOdometry:
         self._inflight = getattr(self, "_inflight", [])
         self._inflight.append((L, R))
 
+    def submit_frames(self, pairs):
+        """Look-ahead form of submit (svo_submit_frames): `pairs` = up to `lookahead` (left, right) frames that are
+        already there; pyramids + FAST of all of them run in one launch set, results are collected one by one."""
+        imgs = [(_img(L), _img(R)) for (L, R) in pairs]
+        L0 = imgs[0][0]
+        if any(a.shape != L0.shape or b.shape != L0.shape or a.strides[0] != L0.strides[0] or b.strides[0] != L0.strides[0]
+               for a, b in imgs):
+            raise SvoError("all frames of a look-ahead batch must share one layout")
+        if self._ctx is None:
+            self._create(L0.shape[1], L0.shape[0], 1)
+        n = len(imgs)
+        lp = (C.c_void_p * n)(*[a.ctypes.data for a, _ in imgs])
+        rp = (C.c_void_p * n)(*[b.ctypes.data for _, b in imgs])
+        check(lib().svo_submit_frames(self._ctx, n, lp, rp, L0.strides[0]))
+        self._inflight = getattr(self, "_inflight", [])
+        self._inflight += imgs
+
     def collect(self):
         """Result of the oldest submitted frame: (success, 4x4 float64), identical to stereo_callback's."""
         r = FrameResult()

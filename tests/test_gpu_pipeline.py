@@ -452,3 +452,43 @@ def test_switching_between_synchronous_and_streaming_calls():
         for k, ((ok0, T0), (ok1, T1)) in enumerate(zip(want, got)):
             assert ok0 == ok1 and np.array_equal(T0, T1), (pattern, k)
         b.close()
+
+
+def test_lookahead_batched_ingest_equals_synchronous_calls():
+    """svo_submit_frames runs pyramids + FAST of K frames of ONE trajectory in one launch set (ring of
+    2 K + 3 slots); the frames then go through the tracking chain one by one.  Transforms and per-frame counters must
+    equal the plain synchronous calls bit for bit, for full batches, a ragged last batch, single frames in between
+    and a batch that wraps the slot ring."""
+    import ctypes as C
+    from stereo_visual_odometry_b200._lib import FrameResult
+    seq = synth.make_sequence(n_frames=45, seed=4)
+    frames = list(seq.frames())
+    a = V.VisualOdometry(seq.width, seq.height)
+    a.initalize_projection_matricies(seq.Pl, seq.Pr)
+    want = []
+    for (L, R) in frames:
+        ok, T = a.stereo_callback(L, R)
+        r = a.last_result()
+        want.append((ok, T, (r.n_bucketed, r.n_matched, r.n_inliers, r.retry, r.lk_iters)))
+    a.close()
+    for K, plan in ((8, [8, 8, 1, 8, 3, 8, 8, 1]), (4, [4, 4, 4, 2, 1, 4, 4, 4, 4, 4, 4, 4, 2])):
+        assert sum(plan) == len(frames)
+        b = V.VisualOdometry(seq.width, seq.height, lookahead=K)
+        b.initalize_projection_matricies(seq.Pl, seq.Pr)
+        fr = FrameResult()
+        got, i = [], 0
+        for n in plan:
+            b.submit_frames(frames[i:i + n])
+            i += n
+            while V.lib().svo_pending(b._ctx) > 8 - K + 1:   # keep a few frames in flight across the batches
+                V.check(V.lib().svo_collect(b._ctx, C.byref(fr)))
+                got.append((bool(fr.success), np.array(fr.transform).reshape(4, 4), (fr.n_bucketed, fr.n_matched, fr.n_inliers, fr.retry, fr.lk_iters)))
+        while V.lib().svo_pending(b._ctx) > 0:
+            V.check(V.lib().svo_collect(b._ctx, C.byref(fr)))
+            got.append((bool(fr.success), np.array(fr.transform).reshape(4, 4), (fr.n_bucketed, fr.n_matched, fr.n_inliers, fr.retry, fr.lk_iters)))
+        assert len(got) == len(want)
+        for k, ((ok0, T0, c0), (ok1, T1, c1)) in enumerate(zip(want, got)):
+            assert ok0 == ok1 and np.array_equal(T0, T1) and c0 == c1, (K, k, c0, c1)
+        with pytest.raises(V.SvoError):
+            b.submit_frames(frames[:K + 1])   # more than the look-ahead depth
+        b.close()
