@@ -141,7 +141,7 @@ SVO_HD void lk_config_finish(LkConfig& c) {
 }
 
 #ifdef SVO_LK_COUNT
-static long long g_lk_count[3];
+static long long g_lk_count[8];
 #endif
 // Reduction policy for LANES == 1 (host unit tests).
 struct SerialRed {
@@ -154,18 +154,14 @@ struct SerialRed {
     // float32 window sums in OpenCV's order (cv_lk_sum_prod / cv_lk_sum_b below); one lane holds all 100 pixels
     static inline void cv_sum_prod3(const int* ix, const int* iy, int, unsigned*, float& a11, float& a12, float& a22);
     static inline void cv_sum_b(const int* p1, const int* p2, int, unsigned*, float& b1, float& b2);
-    // totals of the products and of their absolute values (both components together): below 2^24 the float32 sums
-    // are exact in any order
-    static SVO_HD bool sum_b_exact(long long s1, long long s2, long long a12, float& b1, float& b2) {
-#ifdef SVO_LK_COUNT
-        ++g_lk_count[a12 > (1 << 24) ? 1 : 0];
-        if (a12 > (1 << 24) && a12 <= (1 << 26)) ++g_lk_count[2];
-#endif
-        if (a12 > (1 << 24)) return false;
-        b1 = (float)s1;
-        b2 = (float)s2;
-        return true;
-    }
+    // OpenCV folds its five accumulators as tail + ((c0 + c2) + (c1 + c3)), c_k = the chain of pixels k | k + 4 of every
+    // row.  While the absolute products of a GROUP -- even columns < 8 (c0, c2), odd columns < 8 (c1, c3), columns 8, 9
+    // (tail) -- total <= 2^24, every float32 partial sum inside the group is an exactly representable integer in any
+    // order, so the result is fl(T + fl(A + B)) of the three exact integer group sums.  p1 / p2: the products per pixel.
+    static SVO_HD int lk_group(int col) { return col >= 8 ? 2 : (col & 1); }
+    static inline bool sum_b_grouped(const int* p1, const int* p2, int, long long, long long, long long, long long,
+                                     float& b1, float& b2);
+    static inline bool sum_prod3_grouped(const int* ix, const int* iy, int, float& a11, float& a12, float& a22);
 };
 
 // cvRound(float): round half to even.
@@ -403,7 +399,71 @@ inline void SerialRed::cv_sum_prod3(const int* ix, const int* iy, int, unsigned*
     a12 = cv_lk_sum_prod(ix, iy);
     a22 = cv_lk_sum_prod(iy, iy);
 }
-inline void SerialRed::cv_sum_b(const int* p1, const int* p2, int, unsigned*, float& b1, float& b2) { cv_lk_sum_b(p1, p2, b1, b2); }
+inline void SerialRed::cv_sum_b(const int* p1, const int* p2, int, unsigned*, float& b1, float& b2) {
+#ifdef SVO_LK_COUNT
+    {   // how many of the ten chains would pass a per-chain exactness bound
+        int bad = 0;
+        for (int k = 0; k < 2; ++k) {
+            const int* p = k ? p2 : p1;
+            for (int c = 0; c < 5; ++c) {
+                long long a = 0;
+                for (int y = 0; y < SVO_LK_WIN; ++y) {
+                    const int x0 = c < 4 ? c : 8, x1 = c < 4 ? c + 4 : 9;
+                    a += llabs((long long)p[y * SVO_LK_WIN + x0]) + llabs((long long)p[y * SVO_LK_WIN + x1]);
+                }
+                if (a > (1 << 24)) ++bad;
+            }
+        }
+        ++g_lk_count[bad == 0 ? 3 : 4];
+        g_lk_count[5] += bad;
+    }
+#endif
+    cv_lk_sum_b(p1, p2, b1, b2);
+}
+
+// While the absolute products of an accumulator group total <= 2^24 the group's float32 partial sums are exact
+// integers in any order: the result is the fold of the three integer group sums (see SerialRed).
+inline bool SerialRed::sum_b_grouped(const int* p1, const int* p2, int, long long, long long, long long, long long,
+                                     float& b1, float& b2) {
+    long long S[2][3] = {{0, 0, 0}, {0, 0, 0}}, A[2][3] = {{0, 0, 0}, {0, 0, 0}};
+    for (int s = 0; s < SVO_LK_NPIX; ++s) {
+        const int g = lk_group(s % SVO_LK_WIN);
+        S[0][g] += p1[s];
+        S[1][g] += p2[s];
+        A[0][g] += p1[s] < 0 ? -(long long)p1[s] : p1[s];
+        A[1][g] += p2[s] < 0 ? -(long long)p2[s] : p2[s];
+    }
+    bool ok = true;
+    for (int k = 0; k < 2; ++k)
+        for (int g = 0; g < 3; ++g) ok = ok && A[k][g] <= (1 << 24);
+#ifdef SVO_LK_COUNT
+    ++g_lk_count[ok ? 0 : 1];
+#endif
+    if (!ok) return false;
+    b1 = fadd((float)S[0][2], fadd((float)S[0][0], (float)S[0][1]));
+    b2 = fadd((float)S[1][2], fadd((float)S[1][0], (float)S[1][1]));
+    return true;
+}
+// the same for the structure tensor (every product of a group is exact when its squares total <= 2^24)
+inline bool SerialRed::sum_prod3_grouped(const int* ix, const int* iy, int, float& a11, float& a12, float& a22) {
+    long long S[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+    for (int s = 0; s < SVO_LK_NPIX; ++s) {
+        const int g = lk_group(s % SVO_LK_WIN);
+        S[0][g] += (long long)ix[s] * ix[s];
+        S[1][g] += (long long)ix[s] * iy[s];
+        S[2][g] += (long long)iy[s] * iy[s];
+    }
+    bool ok = true;
+    for (int g = 0; g < 3; ++g) ok = ok && S[0][g] <= (1 << 24) && S[2][g] <= (1 << 24);
+#ifdef SVO_LK_COUNT
+    ++g_lk_count[ok ? 6 : 7];
+#endif
+    if (!ok) return false;
+    a11 = fadd((float)S[0][2], fadd((float)S[0][0], (float)S[0][1]));
+    a12 = fadd((float)S[1][2], fadd((float)S[1][0], (float)S[1][1]));
+    a22 = fadd((float)S[2][2], fadd((float)S[2][0], (float)S[2][1]));
+    return true;
+}
 
 // Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
 // the same scalar control flow; window pixels are distributed by LkMap; Red sums across lanes).
@@ -475,8 +535,9 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         // ---- Scharr derivatives on the 11x11 positions of the window (zero outside the level:
         // derivBorder = BORDER_CONSTANT), packed (dx, dy) int16
         const bool dinside = ipx >= 0 && ipx + SVO_LK_DW <= I.w && ipy >= 0 && ipy + SVO_LK_DW <= I.h;
-        for (int idx = lane; idx < SVO_LK_DW * SVO_LK_DW; idx += LANES) {
-            const int y = idx / SVO_LK_DW, x = idx - y * SVO_LK_DW;
+        for (int idx = lane, y = lane / SVO_LK_DW, x = lane - y * SVO_LK_DW; idx < SVO_LK_DW * SVO_LK_DW;
+             idx += LANES, x += LANES % SVO_LK_DW, y += LANES / SVO_LK_DW + (x >= SVO_LK_DW ? 1 : 0),
+             x -= x >= SVO_LK_DW ? SVO_LK_DW : 0) {
             int dx = 0, dy = 0;
             if (dinside || (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h)) {
                 const uint8_t* p = sc.ipatch + y * SVO_LK_PATCH_PITCH + x + xo;   // top-left of the 3x3 around patch (x+1, y+1)
@@ -507,7 +568,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
         }
         // OpenCV accumulates the structure tensor in float32 (4 SIMD lanes + a scalar tail): same order, same roundings
         float A11, A12, A22;
-        Red::cv_sum_prod3(Ixv, Iyv, lane, sc.stage, A11, A12, A22);
+        if (!Red::sum_prod3_grouped(Ixv, Iyv, lane, A11, A12, A22)) Red::cv_sum_prod3(Ixv, Iyv, lane, sc.stage, A11, A12, A22);
         A11 = fmul(A11, FLT_SCALE);
         A12 = fmul(A12, FLT_SCALE);
         A22 = fmul(A22, FLT_SCALE);
@@ -552,9 +613,10 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
             lk_weights(fsub(cx, (float)inx), fsub(cy, (float)iny), iw00, iw01, iw10, iw11);
             const unsigned jt = pack_weights(iw00, iw01), jb = pack_weights(iw10, iw11);
             const unsigned short* jbase = sc.jp + (iny - jy0) * SVO_LK_JC + (inx - jx0);
-            // mismatch vector.  OpenCV sums it in float32 in a fixed order; while the sum of the absolute products stays
-            // below 2^24 every partial sum is an exactly representable integer, so the order is irrelevant and the plain
-            // integer total is the same number.  Otherwise the sums are formed in OpenCV's order (Red::cv_sum_b).
+            // mismatch vector.  OpenCV sums it in float32 in a fixed order; while the absolute products of each of the
+            // three accumulator groups stay below 2^24 every partial sum inside a group is an exactly representable
+            // integer and the result is the fold of the three integer group sums (Red::sum_b_grouped).  Otherwise the
+            // sums are formed term by term in OpenCV's order (Red::cv_sum_b).
             int p1[SLOTS], p2[SLOTS];
             typename LkAcc<LANES>::type sb1 = 0, sb2 = 0, sa1 = 0, sa2 = 0;   // <= 4 pixels per lane fit 32 bits
 #pragma unroll
@@ -570,7 +632,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
                 sa2 += p2[s] < 0 ? -p2[s] : p2[s];
             }
             float b1, b2;
-            if (!Red::sum_b_exact(sb1, sb2, sa1 + sa2, b1, b2)) Red::cv_sum_b(p1, p2, lane, sc.stage, b1, b2);
+            if (!Red::sum_b_grouped(p1, p2, lane, sb1, sb2, sa1, sa2, b1, b2)) Red::cv_sum_b(p1, p2, lane, sc.stage, b1, b2);
             b1 = fmul(b1, FLT_SCALE);
             b2 = fmul(b2, FLT_SCALE);
             const float ddx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);

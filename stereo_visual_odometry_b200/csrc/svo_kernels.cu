@@ -169,12 +169,71 @@ struct WarpRed {
         b1 = __shfl_sync(0xffffffffu, r, 0);
         b2 = __shfl_sync(0xffffffffu, r, 5);
     }
-    // totals of the products and of their absolute values (both components together): while the absolute total stays
-    // below 2^24 every float32 partial sum OpenCV forms is an exactly representable integer, i.e. the plain total
-    static __device__ __forceinline__ bool sum_b_exact(int s1, int s2, int a12, float& b1, float& b2) {
-        if (__reduce_add_sync(0xffffffffu, (unsigned)a12) > (1u << 24)) return false;
-        b1 = (float)__reduce_add_sync(0xffffffffu, s1);
-        b2 = (float)__reduce_add_sync(0xffffffffu, s2);
+    // Exact tiers (svo_core.cuh SerialRed::sum_b_grouped states the principle serially).  A lane's pixels share one
+    // column, i.e. one accumulator group: A = even columns < 8 (chains c0, c2), B = odd columns < 8 (c1, c3), T = columns
+    // 8, 9.  While the absolute products of every group total <= 2^24 the float32 sums inside a group are exact integers
+    // in any order; when A + B is exact as well, b = fl(T + (A + B)) is the correctly rounded integer total, i.e.
+    // (float)S of the plain warp total S.  Cost model (measured, tools/warp_ops_lat.cu): REDUX issues once per 8
+    // cycles per SM sub-partition, SHFL once per 4, a vote like an ALU op -- so the tiers are ordered by REDUX count:
+    //   V   every lane's own |sum| <= 2^24 / (lanes of its union): a vote, no REDUX beyond the two totals
+    //   G   group bounds as 16-bit fields of (|sum| >> 13) + 1 per lane in three REDUX (field <= 2048 proves the group
+    //       total < 2^24; <= 13 lanes x 2049 per field: no carry); A + B exact either because |A| + |B| <= 2^24 or,
+    //       with the two tail totals, because |S - T| <= 2^24
+    // otherwise the caller forms the sums term by term in OpenCV's order (cv_sum_b).
+    static __device__ __forceinline__ bool sum_b_grouped(const int*, const int*, int lane, int s1, int s2, int a1, int a2,
+                                                         float& b1, float& b2) {
+        const int x = lane % 10;
+        const bool gT = x >= 8, gB = !gT && (x & 1);
+        const int S1 = __reduce_add_sync(0xffffffffu, s1), S2 = __reduce_add_sync(0xffffffffu, s2);
+        // V: 26 lanes hold A u B (24 + the two idle lanes, which hold zeros), 6 lanes hold T
+        const int lim = gT ? (1 << 24) / 6 : (1 << 24) / 26;
+        if (__all_sync(0xffffffffu, max(a1, a2) <= lim)) {
+            b1 = (float)S1;
+            b2 = (float)S2;
+            return true;
+        }
+        const unsigned f1 = min((unsigned)a1 >> 13, 2048u) + 1u, f2 = min((unsigned)a2 >> 13, 2048u) + 1u;
+        const unsigned sh = gB ? 16u : 0u;
+        const unsigned r1 = __reduce_add_sync(0xffffffffu, gT ? 0u : f1 << sh);            // component 1: A | B
+        const unsigned r2 = __reduce_add_sync(0xffffffffu, gT ? 0u : f2 << sh);            // component 2: A | B
+        const unsigned r3 = __reduce_add_sync(0xffffffffu, gT ? (f1 | (f2 << 16)) : 0u);   // tail: component 1 | 2
+        constexpr unsigned K = 0x77FF77FFu;   // field + 0x77FF reaches bit 15 iff field > 2048
+        if (((r1 + K) | (r2 + K) | (r3 + K)) & 0x80008000u) return false;
+        if (max((r1 & 0xFFFFu) + (r1 >> 16), (r2 & 0xFFFFu) + (r2 >> 16)) > 2048u) {   // |A| + |B| may exceed 2^24: look at A + B
+            const int T1 = __reduce_add_sync(0xffffffffu, gT ? s1 : 0), T2 = __reduce_add_sync(0xffffffffu, gT ? s2 : 0);
+            if (max(abs(S1 - T1), abs(S2 - T2)) > (1 << 24)) return false;
+        }
+        b1 = (float)S1;
+        b2 = (float)S2;
+        return true;
+    }
+    // structure tensor: the squares bound the mixed products (|ix iy| <= (ix^2 + iy^2) / 2), so the two diagonal sums
+    // of a group <= 2^24 prove all three exact.  The terms are squares -- no cancellation, A + B usually needs its own
+    // rounding -- so the three group sums are formed separately (nine REDUX); a vote on the lanes' own sums decides
+    // first whether that can pay (bucket winners are strong corners: it holds for about a fifth of the windows).
+    static __device__ __forceinline__ bool sum_prod3_grouped(const int* ix, const int* iy, int lane, float& a11, float& a12,
+                                                             float& a22) {
+        const int x = lane % 10;
+        const bool gT = x >= 8, gB = !gT && (x & 1), gA = !gT && !(x & 1);
+        unsigned u11 = 0, u22 = 0;
+        int s12 = 0;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            u11 += (unsigned)(ix[s] * ix[s]);
+            u22 += (unsigned)(iy[s] * iy[s]);
+            s12 += ix[s] * iy[s];
+        }
+        const unsigned lim = gT ? (1u << 24) / 6 : (1u << 24) / 13;   // 12 lanes + one idle lane per group, 6 tail lanes
+        if (!__all_sync(0xffffffffu, max(u11, u22) <= lim)) return false;
+        const unsigned A11 = __reduce_add_sync(0xffffffffu, gA ? u11 : 0u), B11 = __reduce_add_sync(0xffffffffu, gB ? u11 : 0u),
+                       T11 = __reduce_add_sync(0xffffffffu, gT ? u11 : 0u);
+        const unsigned A22 = __reduce_add_sync(0xffffffffu, gA ? u22 : 0u), B22 = __reduce_add_sync(0xffffffffu, gB ? u22 : 0u),
+                       T22 = __reduce_add_sync(0xffffffffu, gT ? u22 : 0u);
+        const int A12 = __reduce_add_sync(0xffffffffu, gA ? s12 : 0), B12 = __reduce_add_sync(0xffffffffu, gB ? s12 : 0),
+                  T12 = __reduce_add_sync(0xffffffffu, gT ? s12 : 0);
+        a11 = __fadd_rn((float)T11, __fadd_rn((float)A11, (float)B11));
+        a12 = __fadd_rn((float)T12, __fadd_rn((float)A12, (float)B12));
+        a22 = __fadd_rn((float)T22, __fadd_rn((float)A22, (float)B22));
         return true;
     }
     // any 64-bit per-lane value (multi-channel windows)
@@ -1833,18 +1892,43 @@ struct BlockInlierEval {
             pnp_accumulate(P, K, X3 + 3 * i, uvf, acc, jac);
         }
         const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        // warp sums of the 28 accumulators by recursive halving: at every step a lane keeps one half of its vector and
+        // trades the other half with its partner (28 -> 14 -> 7 -> 4 -> 2 -> 1 values: 28 exchanges instead of the
+        // 28 x 5 of one butterfly per value; SHFL issues once per 4 cycles, it was 60 % of this kernel).  Lane l ends
+        // with the warp total of accumulator halving_slot(l) in acc[0].
+        static_assert(SVO_PNP_ACC == 28, "the halving schedule below is written for 28 accumulators");
+        {
+            const bool up4 = lane & 16, up3 = lane & 8, up2 = lane & 4, up1 = lane & 2, up0 = lane & 1;
 #pragma unroll
-        for (int i = 0; i < SVO_PNP_ACC; ++i) {
-            double v = acc[i];
+            for (int i = 0; i < 14; ++i) {
+                const double send = up4 ? acc[i] : acc[i + 14], keep = up4 ? acc[i + 14] : acc[i];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            acc[i] = v;
+            for (int i = 0; i < 7; ++i) {
+                const double send = up3 ? acc[i] : acc[i + 7], keep = up3 ? acc[i + 7] : acc[i];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+            acc[7] = 0.0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const double send = up2 ? acc[i] : acc[i + 4], keep = up2 ? acc[i + 4] : acc[i];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const double send = up1 ? acc[i] : acc[i + 2], keep = up1 ? acc[i + 2] : acc[i];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            {
+                const double send = up0 ? acc[0] : acc[1], keep = up0 ? acc[1] : acc[0];
+                acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+            }
         }
+        const int sub = ((lane & 4) ? 4 : 0) + ((lane & 2) ? 2 : 0) + (lane & 1);   // 7 = the padding value of a group of 7
+        const int slot = ((lane & 16) ? 14 : 0) + ((lane & 8) ? 7 : 0) + sub;
         __syncthreads();
-        if (lane == 0) {
-#pragma unroll
-            for (int i = 0; i < SVO_PNP_ACC; ++i) sm[wid * SVO_PNP_ACC + i] = acc[i];
-        }
+        if (sub < 7) sm[wid * SVO_PNP_ACC + slot] = acc[0];
         __syncthreads();
         if (threadIdx.x < SVO_PNP_ACC) {   // fixed summation order -> every thread sees identical totals
             double v = 0.0;

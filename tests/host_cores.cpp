@@ -89,6 +89,11 @@ static void build_pyr(HostPyr& hp, const uint8_t* img, int w, int h, int stride,
     }
 }
 
+#ifdef SVO_LK_COUNT
+void hc_lk_counts(long long* out) {
+    for (int i = 0; i < 8; ++i) out[i] = g_lk_count[i];
+}
+#endif
 static int* g_iters_out = nullptr;   // optional per-feature iteration counts (analysis scripts)
 void hc_lk_set_iters_out(int* p) { g_iters_out = p; }
 int hc_lk(const uint8_t* prev, const uint8_t* next, int w, int h, int stride, int max_level, int max_iters,
