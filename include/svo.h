@@ -237,6 +237,32 @@ int svo_camera_to_world(const svo_params* p, const float K[9], const float* cam_
 /* getInverseTransform, vo.h:469-470 / vo.cpp:246-258 (host, FP64). */
 int svo_get_inverse_transform(const double R[9], const double t[3], double T_out[16]);
 
+/* ---- allocation-free entry point ---------------------------------------------
+ * No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same result as svo_fast_detect, but every pointer
+ * is a DEVICE pointer and the call allocates nothing: the response map and the row
+ * counts of the ordered compaction live in one static device array of
+ * SVO_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   - img_dev: width x height bytes, `pitch` bytes per row (a 16-byte aligned base and
+ *     pitch let the kernel use TMA tile loads; any pitch >= width works);
+ *   - xy_out_dev[2*cap], resp_out_dev[cap], n_out_dev[1] (the keypoint count, which may
+ *     exceed cap exactly like svo_fast_detect's return value);
+ *   - stream: a cudaStream_t (NULL = the default stream).  The launches are enqueued
+ *     and the call returns; it does not synchronise.
+ * Limit: ((width+127)&~127) * height, rounded up to 256, + 4 * (height+1) bytes must fit
+ * in SVO_NOALLOC_SCRATCH_BYTES (e.g. 2048 x 2040); larger images are rejected with
+ * SVO_ERR_CAPACITY and a message naming both numbers.
+ * Every call on one device shares the array: calls that overlap on the GPU (different
+ * streams, or graphs replayed concurrently) race; serialise them.  The array keeps the
+ * last call's contents, and every byte a call reads it has written first.  The first
+ * call on each device looks the array's device address up (cudaGetSymbolAddress): make
+ * that call outside stream capture. */
+#define SVO_NOALLOC_SCRATCH_BYTES (4 << 20)
+int svo_fast_detect_noalloc(const uint8_t* img_dev, int width, int height, int pitch, int threshold,
+                            float* xy_out_dev, float* resp_out_dev, int cap, int* n_out_dev,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,7 +57,7 @@ SYMBOLS = [
     "svo_launch_count", "svo_enable_timers", "svo_get_stage_time", "svo_reset_timers",
     "svo_fast_detect", "svo_bucket_filter", "svo_build_pyramid", "svo_lk_track",
     "svo_circular_match", "svo_matching_features", "svo_find_close_points", "svo_compact",
-    "svo_triangulate", "svo_camera_to_world", "svo_get_inverse_transform",
+    "svo_triangulate", "svo_camera_to_world", "svo_get_inverse_transform", "svo_fast_detect_noalloc",
 ]
 
 _lib = None
@@ -113,6 +113,7 @@ def lib():
     L.svo_get_stage_time.argtypes = [vp, C.c_int, dp, C.POINTER(C.c_longlong)]
     L.svo_reset_timers.argtypes = [vp]
     L.svo_fast_detect.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp, C.c_int]
+    L.svo_fast_detect_noalloc.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, vp, vp]
     L.svo_bucket_filter.argtypes = [fp, ip, ip] + [C.c_int] * 9
     L.svo_build_pyramid.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_longlong]
     L.svo_lk_track.argtypes = [C.POINTER(Params), u8p, u8p, C.c_int, fp, C.c_int, fp, u8p]

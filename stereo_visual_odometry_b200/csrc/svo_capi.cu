@@ -20,6 +20,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1547,5 +1548,69 @@ extern "C" int svo_get_inverse_transform(const double R[9], const double t[3], d
     }
     for (int i = 0; i < 4; ++i)
         for (int j = 0; j < 4; ++j) T_out[i * 4 + j] = A[i][4 + j];
+    return SVO_OK;
+}
+
+// ===========================================================================
+// svo_fast_detect_noalloc: svo_fast_detect for callers that may not allocate (CUDA graph capture, serving loops).
+// No counterpart in the reference.  The response map and the row
+// counts of the ordered compaction -- what svo_fast_detect cudaMallocs per call -- live in ONE file-scope device
+// array that every GPU loading the library holds until exit; every call on a device shares it.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SVO_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNoallocMaxDev = 64;
+// g_noalloc_scratch is a host-side stand-in here: the device address is looked up once per device (that device
+// current) and is what the kernels get.
+int noalloc_scratch_ptr(unsigned char** out) {
+    static unsigned char* ptrs[kNoallocMaxDev] = {};
+    static std::mutex mu;
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoallocMaxDev) return fail(SVO_ERR_INVALID, "svo_fast_detect_noalloc: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail(SVO_ERR_CUDA, "svo_fast_detect_noalloc: cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = ptrs[dev];
+    return SVO_OK;
+}
+}  // namespace
+
+extern "C" int svo_fast_detect_noalloc(const uint8_t* img_dev, int width, int height, int pitch, int threshold,
+                                       float* xy_out_dev, float* resp_out_dev, int cap, int* n_out_dev, void* stream) {
+    if (!img_dev || !xy_out_dev || !resp_out_dev || !n_out_dev || width < 7 || height < 7 || pitch < width ||
+        threshold < 1 || threshold > 254 || cap < 0)
+        return fail(SVO_ERR_INVALID, "bad argument");
+    const long long map_pitch = ((long long)width + 127) & ~127ll;
+    const long long map_bytes = (map_pitch * height + 255) & ~255ll;            // response map, then the row counts
+    const long long need = map_bytes + (long long)sizeof(int) * (height + 1);
+    if (need > (long long)SVO_NOALLOC_SCRATCH_BYTES) {
+        char msg[192];
+        snprintf(msg, sizeof(msg),
+                 "svo_fast_detect_noalloc: a %d x %d image needs %lld bytes of scratch, the static array holds %lld "
+                 "(SVO_NOALLOC_SCRATCH_BYTES); use svo_fast_detect",
+                 width, height, need, (long long)SVO_NOALLOC_SCRATCH_BYTES);
+        return fail(SVO_ERR_CAPACITY, msg);
+    }
+    int rc = need_device();
+    if (rc != SVO_OK) return rc;
+    unsigned char* scratch = nullptr;
+    rc = noalloc_scratch_ptr(&scratch);
+    if (rc != SVO_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint8_t* dmap = scratch;
+    int* rows = reinterpret_cast<int*>(scratch + map_bytes);
+    // Nothing of the last call survives into this one's result: fast_kernel writes every pixel of the width x height
+    // map, kp_rowcount_kernel every row count, scan_kernel the total -- so there is nothing to clear.
+    BucketGeom bg;
+    memset(&bg, 0, sizeof(bg));
+    launch_fast(img_dev, 0, width, height, pitch, 1, threshold, threshold, dmap, 0, (int)map_pitch, nullptr, nullptr, bg, st);
+    launch_compact_keypoints(dmap, width, height, (int)map_pitch, threshold, rows, reinterpret_cast<float2*>(xy_out_dev),
+                             resp_out_dev, cap, n_out_dev, st);
+    CU(cudaPeekAtLastError());
     return SVO_OK;
 }
