@@ -270,15 +270,34 @@ SVO_HD int dp2a_lo_su(unsigned a, unsigned b, int c) {
 }
 SVO_HD unsigned pack_weights(int lo, int hi) { return ((unsigned)lo & 0xFFFFu) | ((unsigned)hi << 16); }
 
-// __byte_perm(a, b, sel): byte i of the result = byte sel[4i+3:4i] of the 8-byte pool {b, a}
+// __byte_perm(a, b, sel): byte i of the result = byte sel[4i+2:4i] of the 8-byte pool {b, a} (bit 4i+3: its sign bit
+// replicated instead)
 SVO_HD unsigned byte_perm(unsigned a, unsigned b, unsigned sel) {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(a, b, sel);
+    return __byte_perm(a, b, sel);   // NB: masks the selector to three bits per nibble; sign mode: byte_perm_sx
 #else
     const uint64_t pool = ((uint64_t)b << 32) | a;
     unsigned r = 0;
-    for (int i = 0; i < 4; ++i) r |= (unsigned)((pool >> (8 * ((sel >> (4 * i)) & 7))) & 0xFFu) << (8 * i);
+    for (int i = 0; i < 4; ++i) {
+        const unsigned n = (sel >> (4 * i)) & 15u;
+        unsigned byte = (unsigned)((pool >> (8 * (n & 7u))) & 0xFFu);
+        if (n & 8u) byte = (byte & 0x80u) ? 0xFFu : 0u;   // selector bit 3: replicate the byte's sign bit
+        r |= byte << (8 * i);
+    }
     return r;
+#endif
+}
+
+// prmt.b32 with the full selector: bit 3 of a nibble replicates the selected byte's sign bit over the result byte
+// (__byte_perm() cannot express that)
+template <unsigned SEL>
+SVO_HD unsigned byte_perm_sx(unsigned a, unsigned b) {
+#if defined(__CUDA_ARCH__)
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "n"(SEL));
+    return r;
+#else
+    return byte_perm(a, b, SEL);   // the host statement implements the sign mode
 #endif
 }
 

@@ -15,6 +15,7 @@
 #include <string.h>
 
 #include "svo_kernels.cuh"
+#include "svo_fast_packed.cuh"
 #include "svo_epnp.cuh"
 
 namespace svo {
@@ -281,66 +282,18 @@ __device__ __forceinline__ unsigned long long ld_key(const unsigned long long* p
 // ============================================================================
 // FAST-9/16 + 3x3 NMS.  One block = 120 x 14 output pixels; scores are computed on the 128 x 16 region around
 // them from a 136 x 22 byte tile in shared memory.  A thread scores a QUAD of 4 horizontally adjacent pixels as
-// two int16x2 lanes (DPX min / max on packed halves, ring pixels extracted from 12-byte row windows by PRMT):
-//   phase 1  every quad: an upper bound of the arc score from the four compass ring pixels (any 9-arc contains
-//            two adjacent compass points); quads that cannot hold a corner at thr_lo are dropped (~2/3)
-//   phase 2  the surviving quads, compacted through a shared list so no warp idles: the exact arc score
+// two int16x2 lanes (DPX min / max on packed halves, ring pixels extracted from 12-byte row windows by PRMT;
+// arithmetic: svo_fast_packed.cuh, checked on the host against the scalar statement):
+//   phase 1  every quad: the compass test (any 9-arc contains two adjacent compass pixels) on raw ring pixels, six
+//            packed min / max per pixel pair; quads that cannot hold a corner at thr_lo are dropped (~3/4)
+//   phase 2  the surviving quads, compacted through a shared list so no warp idles: the exact arc score (arcs
+//            folded in pairs, 75 packed operations per pixel pair)
 //   phase 3  strict 3x3 NMS + per-bucket winners (64-bit atomicMax keys) / dense response map
-constexpr int FT_OW = 120, FT_OH = 14, FT_SW = 128, FT_SH = 16, FT_TW = 144, FT_TH = 22, FT_THREADS = 256;   // tile: 136 columns used, pitch 144
+constexpr int FT_OW = 120, FT_OH = 14, FT_SW = 128, FT_SH = 16, FT_TW = 144, FT_TH = 22;   // tile: 136 columns used, pitch 144
 constexpr int FT_TASKS = (FT_SW / 4) * FT_SH;   // 512 quads
 
-// bytes i, i + 1 of the 12-byte window w[0..2] as (b_i) | (b_{i+1} << 16)
-__device__ __forceinline__ unsigned pick2(const unsigned* w, int i) {
-    const int wi = i >> 2, bi = i & 3;
-    if (bi < 3) return __byte_perm(w[wi], 0u, (unsigned)(bi | (4 << 4) | ((bi + 1) << 8) | (4 << 12)));
-    return __byte_perm(w[wi], w[wi + 1], 0x4433u) & 0x00FF00FFu;
-}
-// exact arc scores of the pixel pair whose first pixel is byte `c0` of the row windows; rows[r] = the 12-byte
-// window of tile row (centre row - 3 + r).  Returns the two scores + 256 packed as int16x2.
-template <int C0>
-__device__ __forceinline__ unsigned fast_pair_score(const unsigned (&rows)[7][3]) {
-    constexpr int RDX[16] = SVO_FAST_RING_DX;
-    constexpr int RDY[16] = SVO_FAST_RING_DY;
-    const unsigned vc = pick2(rows[3], C0) + 0x01000100u;   // centre + 256 per half: all differences stay positive
-    unsigned d[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = vc - pick2(rows[3 + RDY[k]], C0 + RDX[k]);
-    unsigned lo2[16], hi2[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo2[k] = __vmins2(d[k], d[(k + 1) & 15]);
-        hi2[k] = __vmaxs2(d[k], d[(k + 1) & 15]);
-    }
-    unsigned lo4[16], hi4[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo4[k] = __vmins2(lo2[k], lo2[(k + 2) & 15]);
-        hi4[k] = __vmaxs2(hi2[k], hi2[(k + 2) & 15]);
-    }
-    unsigned a = 0u, b = 0x7FFF7FFFu;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        a = __vmaxs2(a, __vimin3_s16x2(lo4[k], lo4[(k + 4) & 15], d[(k + 8) & 15]));
-        b = __vmins2(b, __vimax3_s16x2(hi4[k], hi4[(k + 4) & 15], d[(k + 8) & 15]));
-    }
-    // score + 256 = max(a, 512 - b) per half (kept biased: both halves positive, so the packed subtraction cannot
-    // borrow across the halves)
-    return __vmaxs2(a, 0x02000200u - b);
-}
-// upper bound of the arc scores of a pixel pair from the compass ring pixels k = 0, 4, 8, 12
-template <int C0>
-__device__ __forceinline__ unsigned fast_pair_bound(const unsigned* top, const unsigned* mid, const unsigned* bot) {
-    const unsigned vc = pick2(mid, C0) + 0x01000100u;
-    const unsigned d0 = vc - pick2(bot, C0), d4 = vc - pick2(mid, C0 + 3), d8 = vc - pick2(top, C0),
-                   d12 = vc - pick2(mid, C0 - 3);
-    const unsigned a = __vmaxs2(__vmaxs2(__vmins2(d0, d4), __vmins2(d4, d8)),
-                                     __vmaxs2(__vmins2(d8, d12), __vmins2(d12, d0)));
-    const unsigned b = __vmins2(__vmins2(__vmaxs2(d0, d4), __vmaxs2(d4, d8)),
-                                     __vmins2(__vmaxs2(d8, d12), __vmaxs2(d12, d0)));
-    return __vmaxs2(a, 0x02000200u - b);   // bound + 256 per half
-}
-
-__global__ void __launch_bounds__(FT_THREADS)
+template <int NT>
+__global__ void __launch_bounds__(NT)
 fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h, int pitch, int thr_lo,
             int thr_hi, uint8_t* __restrict__ resp_map, long long map_stride, int map_pitch,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
@@ -357,51 +310,52 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     __shared__ unsigned short list[FT_TASKS];
     __shared__ unsigned short hits[FT_OW * FT_OH];   // score-array positions of the nonzero scores among the outputs
     __shared__ int n_list, n_hits;
+    __shared__ int tinfo[2][4];   // per tile buffer: tile id, image, x0, y0 (decoded once, by the thread that fetches the id)
     const int tid = threadIdx.x, lane = tid & 31;
     if (use_tma && tid == 0) {
         mbar_init(&tma_bar[0], 1);
         mbar_init(&tma_bar[1], 1);
     }
-    unsigned tma_phase[2] = {0u, 0u};
+    unsigned tma_phase = 0u;   // bit b: the phase buffer b's barrier completes next
     // ungated launches: persistent blocks over all tiles of all images; the gated pass, which almost never has work,
     // runs a few blocks per image (blockIdx.z) that loop over its tiles, so that its early exit costs next to nothing
     const int tpi = tiles_x * tiles_y, n_tiles = gate ? tpi : tpi * n_img;
-    auto decode = [&](int id, int& zz, int& xx, int& yy) {
-        zz = gate ? (int)blockIdx.z : id / tpi;
+    // thread 0 only: decode tile `id` into tinfo[buf] and start its bulk tensor copy (the 144 x 22 box at the aligned
+    // column at or below x0 - 8)
+    auto fetch = [&](int id, int buf) {
+        tinfo[buf][0] = id;
+        if (id >= n_tiles) return;
+        const int zz = gate ? (int)blockIdx.z : id / tpi;
         const int t = gate ? id : id - zz * tpi;
-        yy = (t / tiles_x) * FT_OH;
-        xx = (t - (t / tiles_x) * tiles_x) * FT_OW;
-    };
-    auto issue = [&](int id, int buf) {   // one bulk tensor copy: the 144 x 22 box at the aligned column at or below x0 - 8
-        int zz, xx, yy;
-        decode(id, zz, xx, yy);
-        mbar_expect_tx(&tma_bar[buf], FT_TH * FT_TW);
-        tma_load_3d(tile2[buf], &tmap, (xx - 8) & ~15, yy - 4, zz, &tma_bar[buf]);
+        const int ty = t / tiles_x;
+        const int yy = ty * FT_OH, xx = (t - ty * tiles_x) * FT_OW;
+        tinfo[buf][1] = zz;
+        tinfo[buf][2] = xx;
+        tinfo[buf][3] = yy;
+        if (use_tma) {
+            mbar_expect_tx(&tma_bar[buf], FT_TH * FT_TW);
+            tma_load_3d(tile2[buf], &tmap, (xx - 8) & ~15, yy - 4, zz, &tma_bar[buf]);
+        }
     };
     // tile order: a global work counter when the launch has one (work[0]; the tiles cost very different amounts, so
     // the persistent blocks take them dynamically; work[1] counts finished blocks and the last one re-arms both),
     // else block b takes tiles b, b + gridDim.x, ...
-    __shared__ int next_id[2];
     __syncthreads();
-    if (tid == 0) {
-        const int first = work ? atomicAdd(work, 1) : (int)blockIdx.x;
-        next_id[0] = first;
-        if (use_tma && first < n_tiles) issue(first, 0);
-    }
+    if (tid == 0) fetch(work ? atomicAdd(work, 1) : (int)blockIdx.x, 0);
     __syncthreads();
+    const unsigned kt = (unsigned)(0x8000 - thr_lo - 1) * 0x00010001u;           // compass test (fast_pair_compass)
+    const unsigned kz = (unsigned)(0x8000 - (thr_lo + 256) - 1) * 0x00010001u;   // score > thr_lo (fast_quad_pack)
+    const float inv_bh = 1.f / (float)bg.bh, inv_bw = 1.f / (float)bg.bw;
     for (int iter = 0;; ++iter) {
     const int buf = iter & 1;
-    const int tile_id = next_id[buf];
+    const int tile_id = tinfo[buf][0];
     if (tile_id >= n_tiles) break;
     uint8_t* tile = tile2[buf];
-    int z, x0, y0;
-    decode(tile_id, z, x0, y0);
+    const int z = tinfo[buf][1], x0 = tinfo[buf][2], y0 = tinfo[buf][3];
     const uint8_t* src = img + (long long)z * img_stride;
     if (tid == 0) {
         n_list = n_hits = 0;
-        const int nxt = work ? atomicAdd(work, 1) : tile_id + (int)gridDim.x;   // the block's next tile: prefetched now
-        next_id[buf ^ 1] = nxt;
-        if (use_tma && nxt < n_tiles) issue(nxt, buf ^ 1);
+        fetch(work ? atomicAdd(work, 1) : tile_id + (int)gridDim.x, buf ^ 1);   // the block's next tile: prefetched now
     }
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
     // whose score is forced to 0).  Word loads when the block is inside the image and the plane is word aligned.
@@ -415,26 +369,26 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     const int toff = use_tma ? (tx0 & 15) : 0;
     const uint8_t* tl = tile + toff;
     if (use_tma) {   // zero fill outside the image
-        mbar_wait(&tma_bar[buf], tma_phase[buf]);
-        tma_phase[buf] ^= 1u;
+        mbar_wait(&tma_bar[buf], (tma_phase >> buf) & 1u);
+        tma_phase ^= 1u << buf;
     } else if (fastpath) {
         const int wmax = ((w + 3) >> 2) - 1;
-        constexpr int NW = FT_TH * (FT_TW / 4), NIT = (NW + FT_THREADS - 1) / FT_THREADS;
+        constexpr int NW = FT_TH * (FT_TW / 4), NIT = (NW + NT - 1) / NT;
         unsigned v[NIT];
 #pragma unroll
         for (int it = 0; it < NIT; ++it) {   // all loads of a thread in flight before the first store
-            const int i = min(tid + it * FT_THREADS, NW - 1);
+            const int i = min(tid + it * NT, NW - 1);
             const int r = i / (FT_TW / 4), k = i - r * (FT_TW / 4);
             const int gy = min(max(ty0 + r, 0), h - 1), gk = min(max((tx0 >> 2) + k, 0), wmax);
             v[it] = __ldg(reinterpret_cast<const unsigned*>(src + (long long)gy * pitch) + gk);
         }
 #pragma unroll
         for (int it = 0; it < NIT; ++it) {
-            const int i = tid + it * FT_THREADS;
+            const int i = tid + it * NT;
             if (i < NW) reinterpret_cast<unsigned*>(tile)[i] = v[it];
         }
     } else {
-        for (int i = tid; i < FT_TH * FT_TW; i += FT_THREADS) {
+        for (int i = tid; i < FT_TH * FT_TW; i += NT) {
             const int r = i / FT_TW, c = i - r * FT_TW;
             const int gy = min(max(ty0 + r, 0), h - 1), gx = min(max(tx0 + c, 0), w - 1);
             tile[i] = __ldg(src + (long long)gy * pitch + gx);
@@ -442,32 +396,42 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     }
     __syncthreads();
 
-    // ---- phase 1: compass bound.  Task t: score row t / 32, quad t % 32 (score col 4q <-> tile col 4q + 4,
-    // score row r <-> tile row r + 3).  The 12-byte row window of a quad starts at tile col 4q.
-    const unsigned thr2 = (unsigned)(thr_lo + 256) | ((unsigned)(thr_lo + 256) << 16);   // scores are biased by 256
+    // ---- phase 1: compass test.  Task t: score row t / 32, quad t % 32 (score col 4q <-> tile col 4q + 4,
+    // score row r <-> tile row r + 3).  The 12-byte row window of a quad starts at tile col 4q.  A warp's tasks are
+    // whole score rows; its survivors are appended to the list with one shared atomic per warp.
+    {
+        constexpr int TPT = FT_TASKS / NT;
+        unsigned m[TPT];
+        int total = 0;
 #pragma unroll
-    for (int s = 0; s < FT_TASKS / FT_THREADS; ++s) {
-        const int t = tid + s * FT_THREADS;
-        const int r = t >> 5, q = t & 31;
-        const unsigned* top = reinterpret_cast<const unsigned*>(tl + (r + 0) * FT_TW) + q;
-        const unsigned* mid = reinterpret_cast<const unsigned*>(tl + (r + 3) * FT_TW) + q;
-        const unsigned* bot = reinterpret_cast<const unsigned*>(tl + (r + 6) * FT_TW) + q;
-        const unsigned wt[3] = {top[0], top[1], top[2]}, wm[3] = {mid[0], mid[1], mid[2]}, wb[3] = {bot[0], bot[1], bot[2]};
-        const unsigned ua = fast_pair_bound<4>(wt, wm, wb), ub = fast_pair_bound<6>(wt, wm, wb);
-        // any half > thr_lo ?
-        const bool pass = (__vmaxs2(ua, ub) != __vmins2(__vmaxs2(ua, ub), thr2));
-        reinterpret_cast<unsigned*>(score)[t] = 0u;
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        for (int s = 0; s < TPT; ++s) {
+            const int t = tid + s * NT;
+            const int r = t >> 5, q = t & 31;
+            const unsigned* top = reinterpret_cast<const unsigned*>(tl + (r + 0) * FT_TW) + q;
+            const unsigned* mid = reinterpret_cast<const unsigned*>(tl + (r + 3) * FT_TW) + q;
+            const unsigned* bot = reinterpret_cast<const unsigned*>(tl + (r + 6) * FT_TW) + q;
+            const unsigned wt[3] = {top[0], top[1], top[2]}, wm[3] = {mid[0], mid[1], mid[2]}, wb[3] = {bot[0], bot[1], bot[2]};
+            const unsigned pass = (fast_pair_compass<4>(wt, wm, wb, kt) | fast_pair_compass<6>(wt, wm, wb, kt)) & 0x80008000u;
+            reinterpret_cast<unsigned*>(score)[t] = 0u;
+            m[s] = __ballot_sync(0xffffffffu, pass != 0u);
+            total += __popc(m[s]);
+        }
         int base = 0;
-        if (lane == 0 && m) base = atomicAdd(&n_list, __popc(m));
+        if (lane == 0 && total) base = atomicAdd(&n_list, total);
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (pass) list[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)t;
+        const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int s = 0; s < TPT; ++s) {
+            if ((m[s] >> lane) & 1u) list[base + __popc(m[s] & lt)] = (unsigned short)(tid + s * NT);
+            base += __popc(m[s]);
+        }
     }
     __syncthreads();
 
     // ---- phase 2: exact scores of the surviving quads
     const int n = n_list;
-    for (int i = tid; i < n; i += FT_THREADS) {
+    const bool edge_tile = x0 - 4 < 3 || x0 + FT_SW - 4 > w - 3 || y0 - 1 < 3 || y0 + FT_SH - 1 > h - 3;
+    for (int i = tid; i < n; i += NT) {
         const int t = list[i];
         const int r = t >> 5, q = t & 31;
         unsigned rows[7][3];
@@ -476,31 +440,35 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             const unsigned* p = reinterpret_cast<const unsigned*>(tl + (r + k) * FT_TW) + q;
             rows[k][0] = p[0]; rows[k][1] = p[1]; rows[k][2] = p[2];
         }
-        const unsigned sa = fast_pair_score<4>(rows), sb = fast_pair_score<6>(rows);
-        const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * q;
-        const bool rowok = gy >= 3 && gy < h - 3;
-        unsigned out = 0;
+        unsigned out = fast_quad_pack(fast_pair_score_ring<4>(rows), fast_pair_score_ring<6>(rows), kz);
+        if (edge_tile) {   // the 3-pixel image border never holds a keypoint
+            const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * q;
+            if (gy < 3 || gy >= h - 3) out = 0u;
+            if (gx < 3 || gx + 3 >= w - 3) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int sc = (int)(((e < 2 ? sa : sb) >> (16 * (e & 1))) & 0xFFFFu) - 256;
-            const int x = gx + e;
-            if (rowok && x >= 3 && x < w - 3 && sc > thr_lo) {
-                out |= (unsigned)(sc - 1) << (8 * e);
-                // an output pixel (not the 1-pixel score halo) with a score: a candidate for phase 3
-                if (!resp_map && r >= 1 && r <= FT_OH && 4 * q + e >= 4 && 4 * q + e < 4 + FT_OW)
-                    hits[atomicAdd(&n_hits, 1)] = (unsigned short)(r * FT_SW + 4 * q + e);
+                for (int e = 0; e < 4; ++e)
+                    if (gx + e < 3 || gx + e >= w - 3) out &= ~(0xFFu << (8 * e));
             }
         }
+        if (out == 0u) continue;
         reinterpret_cast<unsigned*>(score)[t] = out;
+        // scores among the block's outputs (not the 1-pixel score halo: rows 1 .. FT_OH, quads 1 .. FT_OW / 4) are the
+        // candidates of phase 3
+        if (!resp_map && r >= 1 && r <= FT_OH && q >= 1 && q <= FT_OW / 4) {
+            const int cnt = (out & 0xFFu ? 1 : 0) + (out & 0xFF00u ? 1 : 0) + (out & 0xFF0000u ? 1 : 0) + (out >> 24 ? 1 : 0);
+            int hb;   // one shared atomic per thread with hits (few per warp: cheaper than a warp-aggregated prefix scan)
+            asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(hb) : "r"(smem_u32(&n_hits)), "r"(cnt) : "memory");
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if ((out >> (8 * e)) & 0xFFu) hits[hb++] = (unsigned short)(r * FT_SW + 4 * q + e);
+        }
     }
     __syncthreads();
 
-    // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs, one output quad per task: most score
-    // words are zero and are dismissed with one load
-    const float inv_bh = 1.f / (float)bg.bh, inv_bw = 1.f / (float)bg.bw;
+    // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs
     if (!resp_map) {   // pipeline mode (bucket keys only): one thread per nonzero score instead of the dense sweep
         const int nh = n_hits;
-        for (int i = tid; i < nh; i += FT_THREADS) {
+        for (int i = tid; i < nh; i += NT) {
             const int idx = hits[i];
             const uint8_t* sp = score + idx;
             const int v = *sp;
@@ -523,7 +491,8 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
         __syncthreads();   // every thread is done with this tile's shared arrays
         continue;
     }
-    for (int i = tid; i < FT_OH * (FT_OW / 4); i += FT_THREADS) {
+    // dense sweep, one output quad per task: most score words are zero and are dismissed with one load
+    for (int i = tid; i < FT_OH * (FT_OW / 4); i += NT) {
         const int oy = i / (FT_OW / 4), oq = i - oy * (FT_OW / 4);
         const int gx0 = x0 + 4 * oq, gy = y0 + oy;
         if (gx0 >= w || gy >= h) continue;
@@ -557,14 +526,12 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
                 }
             }
         }
-        if (resp_map) {
-            uint8_t* o = resp_map + (long long)z * map_stride + (long long)gy * map_pitch + gx0;
-            if (gx0 + 3 < w && (map_pitch & 3) == 0 && ((size_t)(resp_map + (long long)z * map_stride) & 3) == 0) {
-                *reinterpret_cast<unsigned*>(o) = outw;
-            } else {
-                for (int e = 0; e < 4; ++e)
-                    if (gx0 + e < w) o[e] = (uint8_t)(outw >> (8 * e));
-            }
+        uint8_t* o = resp_map + (long long)z * map_stride + (long long)gy * map_pitch + gx0;
+        if (gx0 + 3 < w && (map_pitch & 3) == 0 && ((size_t)(resp_map + (long long)z * map_stride) & 3) == 0) {
+            *reinterpret_cast<unsigned*>(o) = outw;
+        } else {
+            for (int e = 0; e < 4; ++e)
+                if (gx0 + e < w) o[e] = (uint8_t)(outw >> (8 * e));
         }
     }
     __syncthreads();   // every thread is done with this tile's shared arrays
@@ -580,7 +547,7 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
                  unsigned long long* keysA, unsigned long long* keysB, BucketGeom bg, cudaStream_t st,
                  int* countA, const int* gate, int gate_min, int* work, long long key_stride) {
     const int tiles_x = (w + FT_OW - 1) / FT_OW, tiles_y = (h + FT_OH - 1) / FT_OH;
-    // ungated: persistent blocks (a few per SM) over all (image, tile) pairs; gated: a few blocks per image
+    // ungated: persistent blocks (as many as stay resident) over all (image, tile) pairs; gated: a few blocks per image
     static int n_sm = 0;
     if (!n_sm) {
         int dev = 0;
@@ -588,12 +555,18 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
         if (n_sm <= 0) n_sm = 148;
     }
+    static int nt = 0;    // threads per block (SVO_FAST_NT = 128 | 256)
     static int bps = 0;   // persistent blocks per SM (SVO_FAST_BPS; what the register file holds is the useful maximum)
     if (!bps) {
-        const char* e = getenv("SVO_FAST_BPS");
+        const char* e = getenv("SVO_FAST_NT");
+        nt = e && atoi(e) == 256 ? 256 : 128;
+        e = getenv("SVO_FAST_BPS");
         bps = e ? atoi(e) : 0;
-        if (bps <= 0 && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel, FT_THREADS, 0) != cudaSuccess) bps = 4;
-        if (bps <= 0) bps = 4;
+        if (bps <= 0) {
+            const cudaError_t rc = nt == 256 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<256>, 256, 0)
+                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<128>, 128, 0);
+            if (rc != cudaSuccess || bps <= 0) bps = nt == 256 ? 4 : 8;
+        }
     }
     const long long total = (long long)tiles_x * tiles_y * n_img, cap = (long long)bps * n_sm;
     const dim3 grid = gate ? dim3(tiles_x * tiles_y < 48 ? tiles_x * tiles_y : 48, 1, n_img)
@@ -601,9 +574,13 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
     CUtensorMap tmap;
     memset(&tmap, 0, sizeof(tmap));
     const int use_tma = make_tile_map(&tmap, img, w, h, pitch, img_stride, n_img, FT_TW, FT_TH) ? 1 : 0;
-    fast_kernel<<<grid, FT_THREADS, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch,
-                                             keysA, keysB, bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work,
-                                             key_stride > 0 ? key_stride : (long long)bg.nb);
+    const long long ks = key_stride > 0 ? key_stride : (long long)bg.nb;
+    if (nt == 256)
+        fast_kernel<256><<<grid, 256, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+                                               bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
+    else
+        fast_kernel<128><<<grid, 128, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+                                               bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
 }
 
 // ---- ordered compaction of the response map (row-major == cv::FAST output order)
@@ -1354,6 +1331,17 @@ __device__ __forceinline__ void circ_bases(const PyrGeom& pg, int seq, int slot_
 //
 // klt_kernel tracks the bucketed features listed in d.todo (the ones whose result was not found in the
 // speculative cache by bucket_merge_kernel; all of them when speculation is off).
+#ifdef SVO_KLT_PROBE   // debug build only (tools/klt_probe.py): per work item start / duration (ns) / LK iterations / SM
+__device__ int g_klt_probe[4 * 16384];
+extern "C" int svo_debug_klt_probe(int* out, int n) {
+    return (int)cudaMemcpyFromSymbol(out, g_klt_probe, sizeof(int) * (size_t)n);
+}
+__device__ __forceinline__ unsigned long long probe_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
 __global__ void __launch_bounds__(KLT_WARPS * 32, SVO_KLT_MINB_SER)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
@@ -1373,7 +1361,20 @@ klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) 
         if (t >= n) break;
         const int f = todo[t];
         const long long o = (long long)seq * d.cap + f;
+#ifdef SVO_KLT_PROBE
+        const unsigned long long pt0 = probe_ns();
+#endif
         const Circ r = track_circular(d, pg, pc, base, d.bk_xy[o], lane, patch[wid]);
+#ifdef SVO_KLT_PROBE
+        if (lane == 0 && seq == 0 && t < 16384) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_klt_probe[4 * t + 0] = (int)(unsigned)pt0;
+            g_klt_probe[4 * t + 1] = (int)(probe_ns() - pt0);
+            g_klt_probe[4 * t + 2] = r.iters;
+            g_klt_probe[4 * t + 3] = (int)smid;
+        }
+#endif
         if (lane == 0) {
             d.lk_L1[o] = r.a;
             d.lk_R1[o] = r.b;

@@ -11,6 +11,7 @@
 
 #include "../stereo_visual_odometry_b200/csrc/svo_core.cuh"
 #include "../stereo_visual_odometry_b200/csrc/svo_epnp.cuh"
+#include "../stereo_visual_odometry_b200/csrc/svo_fast_packed.cuh"
 
 using namespace svo;
 
@@ -51,6 +52,46 @@ int hc_fast_map(const uint8_t* img, int w, int h, int stride, int thr, uint8_t* 
             n += keep;
         }
     return n;
+}
+
+// the packed pixel-pair FAST arithmetic of fast_kernel (svo_fast_packed.cuh) against the scalar statement, for every
+// quad whose 12-byte row windows lie inside the image.  Returns the number of disagreements: a score that differs, a
+// compass bit that differs from the scalar compass bound, or a corner (score > thr) the compass test would drop.
+int hc_fast_packed_check(const uint8_t* img, int w, int h, int stride, int thr) {
+    static const int RDX[16] = SVO_FAST_RING_DX;
+    static const int RDY[16] = SVO_FAST_RING_DY;
+    const unsigned kt = (unsigned)(0x8000 - thr - 1) * 0x00010001u;
+    int bad = 0;
+    for (int y = 3; y < h - 3; ++y)
+        for (int x0 = 4; x0 + 8 <= w; ++x0) {   // quad = pixels x0 .. x0 + 3, windows = bytes x0 - 4 .. x0 + 7
+            unsigned rows[7][3];
+            for (int r = 0; r < 7; ++r)
+                for (int k = 0; k < 3; ++k) {
+                    const uint8_t* p = img + (size_t)(y - 3 + r) * stride + x0 - 4 + 4 * k;
+                    rows[r][k] = p[0] | (p[1] << 8) | (p[2] << 16) | ((unsigned)p[3] << 24);
+                }
+            const unsigned s[2] = {fast_pair_score_ring<4>(rows), fast_pair_score_ring<6>(rows)};
+            const unsigned cp[2] = {fast_pair_compass<4>(rows[0], rows[3], rows[6], kt),
+                                    fast_pair_compass<6>(rows[0], rows[3], rows[6], kt)};
+            const unsigned packed = fast_quad_pack(s[0], s[1], (unsigned)(0x8000 - (thr + 256) - 1) * 0x00010001u);
+            for (int e = 0; e < 4; ++e) {
+                const int x = x0 + e, v = img[(size_t)y * stride + x];
+                int r[16];
+                for (int k = 0; k < 16; ++k) r[k] = img[(size_t)(y + RDY[k]) * stride + x + RDX[k]];
+                const int ref = fast9_arc_score(v, r);
+                const int got = (int)((s[e >> 1] >> (16 * (e & 1))) & 0xFFFFu) - 256;
+                const int d0 = v - r[0], d4 = v - r[4], d8 = v - r[8], d12 = v - r[12];
+                const int a = imax(imax(imin(d0, d4), imin(d4, d8)), imax(imin(d8, d12), imin(d12, d0)));
+                const int b = imin(imin(imax(d0, d4), imax(d4, d8)), imin(imax(d8, d12), imax(d12, d0)));
+                const bool ref_pass = imax(a, -b) > thr;
+                const bool got_pass = ((cp[e >> 1] >> (16 * (e & 1) + 15)) & 1u) != 0;
+                const int want_byte = ref > thr ? ref - 1 : 0;
+                if (ref != got || ref_pass != got_pass || (ref > thr && !got_pass) ||
+                    (int)((packed >> (8 * e)) & 0xFFu) != want_byte)
+                    ++bad;
+            }
+        }
+    return bad;
 }
 
 void hc_pyrdown(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dpitch) {

@@ -35,6 +35,20 @@ def test_fast_bit_exact(hostcores, run1):
             assert n == len(rp) and np.array_equal(pts, rp) and np.array_equal(resp, rr)
 
 
+def test_fast_packed_pair_arithmetic(hostcores, run1):
+    """svo_fast_packed.cuh (what fast_kernel executes per pixel pair) == the scalar arc score, compass bound and
+    response byte on every quad, incl. saturated and flat images."""
+    rng = np.random.default_rng(1)
+    imgs = [run1["gray"][0][0], rng.integers(0, 256, (40, 90), dtype=np.uint8),
+            rng.integers(0, 2, (40, 90), dtype=np.uint8) * 255, np.full((20, 40), 255, np.uint8),
+            np.zeros((20, 40), np.uint8), rng.integers(0, 256, (30, 64), dtype=np.uint8) // 64 * 85]
+    for img in imgs:
+        img = np.ascontiguousarray(img)
+        h, w = img.shape
+        for thr in (1, 5, 20, 60, 200):
+            assert hostcores.hc_fast_packed_check(P(img, u8p), w, h, img.strides[0], thr) == 0
+
+
 def test_pyrdown_bit_exact(hostcores, run1):
     import cv2
     rng = np.random.default_rng(1)
