@@ -118,6 +118,8 @@ struct svo_ctx {
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     int f_share = 59;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
+    int t_share = 0;                    // % of them the tracked-feature kernel is launched with (SVO_TSHARE; 0 = 100 - f_share): blocks
+                                        // beyond its resident share start as the FAST-candidate kernel's blocks leave
     cudaEvent_t ev_in[SVO_EV_RING] = {};    // ingest(f) complete
     cudaEvent_t ev_td[SVO_EV_RING] = {};    // every bucketed feature of f has its circular-matching result
     cudaEvent_t ev_sel[SVO_EV_RING] = {};   // select(f) done: pyramids / keys of f - 1 are free
@@ -256,6 +258,10 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
     if (const char* e = getenv("SVO_FSHARE")) {
         const int v = atoi(e);
         if (v >= 10 && v <= 90) c->f_share = v;
+    }
+    if (const char* e = getenv("SVO_TSHARE")) {
+        const int v = atoi(e);
+        if (v >= 10 && v <= 100) c->t_share = v;
     }
     if (!c->spec || p->n_seq != 1) want_chain = want_in = 0;
     cudaDeviceProp prop;
@@ -703,7 +709,8 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         CU(cudaStreamWaitEvent(sK2, c->ev_td[e1], 0));   // the bucketed list of f - 1 with its keep bits
         {
             TraceScope ts(c, "spec_trk", 2, sK2);
-            launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, c->klt_blocks_k - half, prev, cur, (int)(f & 1), sK2);
+            const int tb = c->t_share > 0 ? (int)((long long)c->klt_blocks_k * c->t_share / 100) : c->klt_blocks_k - half;
+            launch_klt_spec_trk(c->d, c->pg, c->pc, c->bg, tb > 0 ? tb : 1, prev, cur, (int)(f & 1), sK2);
         }
         CU(cudaEventRecord(c->ev_trk[e], sK2));
         CU(cudaStreamWaitEvent(sP, c->ev_spf[e], 0));

@@ -124,6 +124,7 @@ struct LkLevel {
 #define SVO_MAX_LEVELS 4
 struct LkPyramid {
     LkLevel lv[SVO_MAX_LEVELS];
+    SVO_HD LkLevel level(int l) const { return lv[l]; }
 };
 
 struct LkConfig {
@@ -487,8 +488,10 @@ inline bool SerialRed::sum_prod3_grouped(const int* ix, const int* iy, int, floa
 // Track ONE feature through all pyramid levels.  Executed by LANES cooperating lanes (every lane runs
 // the same scalar control flow; window pixels are distributed by LkMap; Red sums across lanes).
 // Returns status (1 = tracked) and writes the output position.
-template <int LANES, class Red>
-SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const LkConfig& cfg,
+// Pyr: anything with `LkLevel level(int) const` (LkPyramid; the kernels pass a view that reads the level geometry from
+// the kernel parameters, so that no per-leg pyramid struct has to live in local memory).
+template <int LANES, class Red, class Pyr>
+SVO_HD int lk_track_feature(const Pyr& Ipyr, const Pyr& Jpyr, const LkConfig& cfg,
                             float ptx, float pty, int lane, LkScratch& sc, float& outx,
                             float& outy, int& iters_out) {
     typedef LkMap<LANES> Map;
@@ -515,8 +518,8 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
     }
 
     for (int level = cfg.nlevels - 1; level >= 0; --level) {
-        const LkLevel I = Ipyr.lv[level];
-        const LkLevel J = Jpyr.lv[level];
+        const LkLevel I = Ipyr.level(level);
+        const LkLevel J = Jpyr.level(level);
         const float scale = 1.f / (float)(1 << level);
         float prx = fmul(ptx, scale), pry = fmul(pty, scale);
         float nxt_x, nxt_y;
@@ -680,7 +683,7 @@ SVO_HD int lk_track_feature(const LkPyramid& Ipyr, const LkPyramid& Jpyr, const 
     // OPTFLOW_LK_GET_MIN_EIGENVALS: OpenCV re-checks the final window position.
     if (status) {
         const int fx = floor_int(fsub(nx, half_win)), fy = floor_int(fsub(ny, half_win));
-        const LkLevel J0 = Jpyr.lv[0];
+        const LkLevel J0 = Jpyr.level(0);
         if (fx < -SVO_LK_WIN || fx >= J0.w || fy < -SVO_LK_WIN || fy >= J0.h) status = 0;
     }
     outx = nx;

@@ -1277,6 +1277,25 @@ __device__ __forceinline__ LkPyramid make_pyr(const uint8_t* base, const PyrGeom
     }
     return p;
 }
+// one image pyramid of the context as lk_track_feature sees it: the level geometry is read from the kernel parameter
+// (constant bank, indexable by the level) instead of a per-leg LkPyramid copy in local memory
+struct GeomPyr {
+    const uint8_t* base;
+    const PyrGeom& pg;
+    __device__ __forceinline__ LkLevel level(int l) const {   // selects over constant indices: operands straight from the parameter bank
+        long long off = pg.off[0];
+        int w = pg.w[0], h = pg.h[0], pitch = pg.pitch[0];
+#pragma unroll
+        for (int k = 1; k < SVO_MAX_LEVELS; ++k)
+            if (l == k) {
+                off = pg.off[k];
+                w = pg.w[k];
+                h = pg.h[k];
+                pitch = pg.pitch[k];
+            }
+        return LkLevel{base + off, w, h, pitch};
+    }
+};
 struct Circ {
     float2 a, b, c, e;   // pL1, pR1, pR0, pL0'
     unsigned st;         // bit l = status of leg l, bit 4 = keep (findClosePoints + status AND + bounds)
@@ -1292,8 +1311,7 @@ __device__ __forceinline__ Circ track_circular(const DevArrays& d, const PyrGeom
     unsigned st = 0;
 #pragma unroll 1
     for (int leg = 0; leg < 4; ++leg) {
-        const LkPyramid I = make_pyr(d.pyr + base[leg], pg);
-        const LkPyramid J = make_pyr(d.pyr + base[(leg + 1) & 3], pg);
+        const GeomPyr I{d.pyr + base[leg], pg}, J{d.pyr + base[(leg + 1) & 3], pg};
         int it;
         float ox, oy;
         const float ix = leg == 0 ? pts[0].x : (leg == 1 ? pts[1].x : (leg == 2 ? pts[2].x : pts[3].x));
