@@ -118,7 +118,7 @@ struct svo_ctx {
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
     int f_share = 59;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE), the rest to the tracked one
-    int t_share = 0;                    // % of them the tracked-feature kernel is launched with (SVO_TSHARE; 0 = 100 - f_share): blocks
+    int t_share = 100;                  // % of them the tracked-feature kernel is launched with (SVO_TSHARE; 0 = 100 - f_share): blocks
                                         // beyond its resident share start as the FAST-candidate kernel's blocks leave
     cudaEvent_t ev_in[SVO_EV_RING] = {};    // ingest(f) complete
     cudaEvent_t ev_td[SVO_EV_RING] = {};    // every bucketed feature of f has its circular-matching result
@@ -261,7 +261,7 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
     }
     if (const char* e = getenv("SVO_TSHARE")) {
         const int v = atoi(e);
-        if (v >= 10 && v <= 100) c->t_share = v;
+        if (v == 0 || (v >= 10 && v <= 100)) c->t_share = v;
     }
     if (!c->spec || p->n_seq != 1) want_chain = want_in = 0;
     cudaDeviceProp prop;
@@ -383,7 +383,14 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     }
     c->pg = make_pyr_geom(p->width, p->height, p->max_level, p->win_size, channels_of(*p));
     // look-ahead contexts: room for the batch being tracked and the batch being ingested
-    c->pg.n_slots = p->lookahead > 1 ? 2 * p->lookahead + 3 : SVO_PYR_SLOTS;
+    // ring slots: 3 are the minimum (previous, current, being ingested); a single-sequence context takes a fourth so
+    // that the ingest -- and with it the FAST-candidate pass -- of frame f + 1 need not wait for select(f - 1)
+    // (measured with SVO_TSHARE=100: +5 % resident, +11 % end to end); look-ahead contexts hold two batches
+    c->pg.n_slots = p->lookahead > 1 ? 2 * p->lookahead + 3 : (p->n_seq == 1 ? SVO_PYR_SLOTS + 1 : SVO_PYR_SLOTS);
+    if (const char* e = getenv("SVO_SLOTS")) {
+        const int v = atoi(e);
+        if (p->lookahead <= 1 && v >= SVO_PYR_SLOTS && v <= 8) c->pg.n_slots = v;
+    }
     c->bg = make_bucket_geom(p->height, p->width, p->buckets_along_height, p->buckets_along_width,
                              p->bucket_start_row, p->age_threshold, p->fast_threshold);
     PipeConfig& pc = c->pc;
@@ -700,6 +707,9 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
         CU(cudaStreamWaitEvent(sK, c->ev_in[e1], 0));
         CU(cudaStreamWaitEvent(sK2, c->ev_in[e1], 0));
         CU(cudaStreamWaitEvent(sK, c->ev_in[e], 0));
+        // the FAST-candidate cache is double buffered (f & 1): bucket_merge(f - 2) has to be done reading this half (with
+        // three ring slots the ingest's own wait implies it)
+        if (f >= 2) CU(cudaStreamWaitEvent(sK, c->ev_bm[(f - 2) & SVO_EV_MASK], 0));
         {
             TraceScope ts(c, "spec_fast", 1, sK);
             launch_klt_spec_fast(c->d, c->pg, c->pc, c->bg, half, prev, cur, prev, (int)(f & 1), sK);
@@ -806,10 +816,11 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     return SVO_OK;
 }
 
-// the ingest stream may not start writing slot f % 3 / key buffer f % 3 before frame f - 2 is done reading
+// the ingest stream may not start writing slot f % NS / key buffer f % NS before its last reader, frame f - NS + 1
+// (which tracks from slot (f - NS) % NS), is done with it and has cleared the keys (select)
 static int wait_ring(svo_ctx* c, bool speculate) {
-    const long long f = c->frames;
-    if (f >= 2) CU(cudaStreamWaitEvent(ingest_stream(c, speculate), c->ev_sel[(f - 2) & SVO_EV_MASK], 0));
+    const long long f = c->frames, back = c->pg.n_slots - 1;
+    if (f >= back) CU(cudaStreamWaitEvent(ingest_stream(c, speculate), c->ev_sel[(f - back) & SVO_EV_MASK], 0));
     return SVO_OK;
 }
 

@@ -559,17 +559,20 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
     static int bps = 0;   // persistent blocks per SM (SVO_FAST_BPS; what the register file holds is the useful maximum)
     if (!bps) {
         const char* e = getenv("SVO_FAST_NT");
-        nt = e && atoi(e) == 256 ? 256 : 128;
+        nt = e && atoi(e) == 256 ? 256 : (e && atoi(e) == 64 ? 64 : 128);
         e = getenv("SVO_FAST_BPS");
         bps = e ? atoi(e) : 0;
         if (bps <= 0) {
             const cudaError_t rc = nt == 256 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<256>, 256, 0)
-                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<128>, 128, 0);
-            if (rc != cudaSuccess || bps <= 0) bps = nt == 256 ? 4 : 8;
+                                   : nt == 64 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<64>, 64, 0)
+                                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fast_kernel<128>, 128, 0);
+            if (rc != cudaSuccess || bps <= 0) bps = 1024 / nt;
         }
     }
     const long long total = (long long)tiles_x * tiles_y * n_img, cap = (long long)bps * n_sm;
-    const dim3 grid = gate ? dim3(tiles_x * tiles_y < 48 ? tiles_x * tiles_y : 48, 1, n_img)
+    // (gated pass: 3072 blocks that return at once measured 4.4 us per 64 images, 1024 about half of that)
+    const int gated_blocks = 2048 / nt;
+    const dim3 grid = gate ? dim3(tiles_x * tiles_y < gated_blocks ? tiles_x * tiles_y : gated_blocks, 1, n_img)
                            : dim3((unsigned)(total < cap ? total : cap), 1, 1);
     CUtensorMap tmap;
     memset(&tmap, 0, sizeof(tmap));
@@ -578,6 +581,9 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
     if (nt == 256)
         fast_kernel<256><<<grid, 256, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
                                                bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
+    else if (nt == 64)
+        fast_kernel<64><<<grid, 64, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+                                             bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
     else
         fast_kernel<128><<<grid, 128, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
                                                bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
@@ -1259,7 +1265,10 @@ void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeCon
 
 // ============================================================================
 // KLT: one warp per feature, the whole circular chain L0->L1->R1->R0->L0 per work item
-constexpr int KLT_WARPS = 8;
+#ifndef SVO_KLT_WARPS
+#define SVO_KLT_WARPS 8
+#endif
+constexpr int KLT_WARPS = SVO_KLT_WARPS;
 #ifndef SVO_KLT_MINB
 #define SVO_KLT_MINB 3       // resident blocks per SM the speculative kernels are compiled for (80 registers: measured best)
 #endif
@@ -1363,43 +1372,49 @@ __device__ __forceinline__ unsigned long long probe_ns() {
 __global__ void __launch_bounds__(KLT_WARPS * 32, SVO_KLT_MINB_SER)
 klt_kernel(DevArrays d, PyrGeom pg, PipeConfig pc, int slot_prev, int slot_cur) {
     __shared__ LkScratch patch[KLT_WARPS];
-    const int seq = blockIdx.y;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    SeqState* s = d.state + seq;
-    const int n = d.n_todo[seq];
-    if (n <= 0) return;
-    long long base[4];
-    circ_bases(pg, seq, slot_prev, slot_cur, base);
-    int* counter = d.klt_next + seq;
-    const int* todo = d.todo + (long long)seq * d.cap;
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(counter, 1);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= n) break;
-        const int f = todo[t];
-        const long long o = (long long)seq * d.cap + f;
+    // A warp works through its own sequence's list first and then helps the other sequences of the batch (the
+    // sequences differ in feature count and convergence, and a launch lasts as long as its slowest sequence; which
+    // warp tracks a feature never changes the result).  Warps never synchronise with each other.
+    for (int k = 0; k < d.n_seq; ++k) {
+        int seq = (int)blockIdx.y + k;
+        if (seq >= d.n_seq) seq -= d.n_seq;
+        const int n = d.n_todo[seq];
+        int* counter = d.klt_next + seq;
+        if (n <= 0 || (k > 0 && __ldcg(counter) >= n)) continue;   // nothing (left) to do there
+        SeqState* s = d.state + seq;
+        long long base[4];
+        circ_bases(pg, seq, slot_prev, slot_cur, base);
+        const int* todo = d.todo + (long long)seq * d.cap;
+        for (;;) {
+            int t = 0;
+            if (lane == 0) t = atomicAdd(counter, 1);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            if (t >= n) break;
+            const int f = todo[t];
+            const long long o = (long long)seq * d.cap + f;
 #ifdef SVO_KLT_PROBE
-        const unsigned long long pt0 = probe_ns();
+            const unsigned long long pt0 = probe_ns();
 #endif
-        const Circ r = track_circular(d, pg, pc, base, d.bk_xy[o], lane, patch[wid]);
+            const Circ r = track_circular(d, pg, pc, base, d.bk_xy[o], lane, patch[wid]);
 #ifdef SVO_KLT_PROBE
-        if (lane == 0 && seq == 0 && t < 16384) {
-            unsigned smid;
-            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-            g_klt_probe[4 * t + 0] = (int)(unsigned)pt0;
-            g_klt_probe[4 * t + 1] = (int)(probe_ns() - pt0);
-            g_klt_probe[4 * t + 2] = r.iters;
-            g_klt_probe[4 * t + 3] = (int)smid;
-        }
+            if (lane == 0 && seq == 0 && t < 16384) {
+                unsigned smid;
+                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+                g_klt_probe[4 * t + 0] = (int)(unsigned)pt0;
+                g_klt_probe[4 * t + 1] = (int)(probe_ns() - pt0);
+                g_klt_probe[4 * t + 2] = r.iters;
+                g_klt_probe[4 * t + 3] = (int)smid;
+            }
 #endif
-        if (lane == 0) {
-            d.lk_L1[o] = r.a;
-            d.lk_R1[o] = r.b;
-            d.lk_R0[o] = r.c;
-            d.lk_C[o] = r.e;
-            d.lk_status[o] = (uint8_t)r.st;
-            atomicAdd(&s->lk_iters, r.iters);
+            if (lane == 0) {
+                d.lk_L1[o] = r.a;
+                d.lk_R1[o] = r.b;
+                d.lk_R0[o] = r.c;
+                d.lk_C[o] = r.e;
+                d.lk_status[o] = (uint8_t)r.st;
+                atomicAdd(&s->lk_iters, r.iters);
+            }
         }
     }
 }
