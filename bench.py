@@ -35,12 +35,10 @@ W, H = 1241, 376
 PITCH = 1280   # row pitch of the device-resident frames (a multiple of 128 bytes)
 FRAMES_PER_STEP = 400
 E2E_DEPTH = 3
-# dram__bytes_read.sum + dram__bytes_write.sum of the ingest kernels per stereo frame in the 64-frame launch
-# (ncu --set full, profiles/r01_ncu_summary.md): mostly reads, the written planes stay in the 126 MB L2
 # dram__bytes_read.sum + dram__bytes_write.sum of the five launches of one 64-frame ingest set, from the round-2
-# ncu --set full capture profiles/r02_ingest_full.raw.csv (rows 3, 4, 5, 6, 2): pyrDown 62.01 + 52.67, 15.44 + 0.37,
-# 4.70 + 0.00, FAST 35.53 + 0.32, gated FAST 0.03 MB
-NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 171.07e6 / 64
+# ncu --set full capture profiles/r02_ingest_full.raw.csv (rows 0..4): pyrDown 62.00 + 51.77, 15.44 + 0.34, 4.70 + 0.00,
+# FAST 35.51 + 0.06, gated FAST 0.03 MB
+NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 169.85e6 / 64
 REF_FRAMES_PER_STEP = 8
 METRIC = "stereo frames/s at KITTI 1241x376"
 
@@ -645,14 +643,14 @@ def run_gpu(args, rank, world, local_rank):
         if batch and "ingest_GBps" in batch:
             nfl = batch["sequences_per_launch"]
             roofline = {"bound": "hbm",
-                        "kernel": "ingest: pyrdown_tile_kernel x3 (level-0 copy fused) + fast_kernel x2 (thr-20 pass, gated low-threshold pass), %d frames per launch" % nfl,
+                        "kernel": "ingest: pyrdown_tile_kernel x3 (level-0 copy fused) + fast_kernel<128> x2 (thr-20 pass, gated low-threshold pass), %d frames per launch" % nfl,
                         "achieved": batch["ingest_GBps"], "peak": peak, "unit": "GB/s",
                         "frac": batch["ingest_GBps"] / peak, "traffic": (NCU_INGEST_TRAFFIC_BYTES_PER_FRAME * nfl) if NCU_INGEST_TRAFFIC_BYTES_PER_FRAME else None,
                         "traffic_source": "ncu --set full capture of the same launches: profiles/r02_ingest_full.raw.csv (summary: profiles/r02_ncu_summary.md)",
                         "peak_source": peak_src, "frames_per_launch": nfl,
                         "algorithmic_bytes_per_launch_set": B_ALG_FRAME * nfl,
                         "us_per_launch_set": batch["ingest_us_per_launch"],
-                        "limiter": "SM issue (FAST 57 %, pyrDown 50-61 % issue-slot utilisation; FAST is 158 of the 229 us), not HBM: see profiles/r02_ncu_summary.md"}
+                        "limiter": "SM issue (FAST 62 %, pyrDown 50-61 % issue-slot utilisation; FAST is 91 of the 161 us), not HBM: see profiles/r02_ncu_summary.md"}
         else:
             roofline = dict(roofline_single, traffic=None, peak_source=peak_src)
         # one trajectory with look-ahead: K = 8 frames per ingest launch set (svo_submit_frames)

@@ -257,7 +257,7 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
     }
     if (const char* e = getenv("SVO_FSHARE")) {
         const int v = atoi(e);
-        if (v >= 10 && v <= 90) c->f_share = v;
+        if (v >= 10 && v <= 100) c->f_share = v;
     }
     if (const char* e = getenv("SVO_TSHARE")) {
         const int v = atoi(e);

@@ -341,7 +341,10 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     // the persistent blocks take them dynamically; work[1] counts finished blocks and the last one re-arms both),
     // else block b takes tiles b, b + gridDim.x, ...
     __syncthreads();
-    if (tid == 0) fetch(work ? atomicAdd(work, 1) : (int)blockIdx.x, 0);
+    if (tid == 0) {
+        n_list = 0;
+        fetch(work ? atomicAdd(work, 1) : (int)blockIdx.x, 0);
+    }
     __syncthreads();
     const unsigned kt = (unsigned)(0x8000 - thr_lo - 1) * 0x00010001u;           // compass test (fast_pair_compass)
     const unsigned kz = (unsigned)(0x8000 - (thr_lo + 256) - 1) * 0x00010001u;   // score > thr_lo (fast_quad_pack)
@@ -354,7 +357,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
     const int z = tinfo[buf][1], x0 = tinfo[buf][2], y0 = tinfo[buf][3];
     const uint8_t* src = img + (long long)z * img_stride;
     if (tid == 0) {
-        n_list = n_hits = 0;
+        n_hits = 0;   // (n_list is reset after phase 2: with TMA tiles there is no barrier between here and phase 1)
         fetch(work ? atomicAdd(work, 1) : tile_id + (int)gridDim.x, buf ^ 1);   // the block's next tile: prefetched now
     }
     // ---- tile rows [y0 - 4, y0 + 18) x cols [x0 - 8, x0 + 128), clamped (clamped values only ever reach pixels
@@ -394,7 +397,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             tile[i] = __ldg(src + (long long)gy * pitch + gx);
         }
     }
-    __syncthreads();
+    if (!use_tma) __syncthreads();   // TMA tiles: every thread has waited on the tile's mbarrier itself
 
     // ---- phase 1: compass test.  Task t: score row t / 32, quad t % 32 (score col 4q <-> tile col 4q + 4,
     // score row r <-> tile row r + 3).  The 12-byte row window of a quad starts at tile col 4q.  A warp's tasks are
@@ -464,6 +467,7 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
         }
     }
     __syncthreads();
+    if (tid == 0) n_list = 0;   // every thread has read it; the next tile's phase 1 comes after the barrier that ends this tile
 
     // ---- phase 3: NMS (strict maximum over the 8 neighbours) + outputs
     if (!resp_map) {   // pipeline mode (bucket keys only): one thread per nonzero score instead of the dense sweep

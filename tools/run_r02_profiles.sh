@@ -11,7 +11,7 @@ python bench.py --impl reference --steps 3 --warmup 1 > $O/r02_bench_ref.json 2>
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/r02_launches.csv \
     python bench.py --frames 40 --steps 1 --warmup 1 --no-cpu-baseline > $O/r02_launches_run.log 2>&1; echo "launch list rc $?"
 # full captures
-ncu --set full --clock-control none --import-source on -k regex:"fast_kernel|pyrdown" -s 7 -c 7 -f -o $O/r02_ingest_full \
+ncu --set full --clock-control none --import-source on -k regex:"fast_kernel|pyrdown" -s 5 -c 5 -f -o $O/r02_ingest_full \
     python tools/ingest_probe.py 4 > $O/r02_ingest_full.log 2>&1; echo "ingest full rc $?"
 ncu --set full --clock-control none --import-source on -k regex:"klt_kernel" -s 2 -c 2 -f -o $O/r02_klt_batch_full \
     python tools/ingest_probe.py 4 > $O/r02_klt_batch_full.log 2>&1; echo "klt full rc $?"
