@@ -690,7 +690,8 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     } else {
         {
             TraceScope ts(c, "ingest", 0, sI);
-            n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI);
+            // (programmatic dependent launch where the set owns its SMs: serial frames and batched contexts)
+            n_ingest = launch_ingest(c->d, c->pg, c->bg, c->pc, left, right, stride, seq_stride, cur, sI, tm || c->d.n_seq > 1);
         }
         c->launches += n_ingest;
         if (!tm) {

@@ -28,6 +28,41 @@ namespace svo {
 // Requirements of the engine: base address and row / image strides multiples of 16 bytes, box width a multiple
 // of 16 bytes and <= 256; planes that do not qualify take the kernels' LDG loaders.
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+// ---- programmatic dependent launch (the ingest is five short launches in a row): a kernel launched with the attribute
+// may be set up while its predecessor in the stream still runs; it must not touch global memory before pdl_wait()
+// (which returns when the predecessor has completed and flushed).  pdl_trigger() lets the successor's launch begin
+// once every block of this grid has called it.  Both are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Only launch sets that own their SMs ask for it (batched contexts, serial frames): an early-launched grid waits ON
+// the SMs, and on the shared 16-SM chain / ingest partition of the streaming pipeline that starves the pose chain.
+static thread_local bool g_pdl_allow = false;
+struct PdlScope {
+    bool prev;
+    explicit PdlScope(bool on) : prev(g_pdl_allow) { g_pdl_allow = on; }
+    ~PdlScope() { g_pdl_allow = prev; }
+};
+static bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("SVO_PDL");
+        on = e ? (atoi(e) != 0) : 1;
+    }
+    return on != 0;
+}
+template <class... KArgs, class... Args>
+static void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = g_pdl_allow && pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -299,6 +334,8 @@ fast_kernel(const uint8_t* __restrict__ img, long long img_stride, int w, int h,
             unsigned long long* __restrict__ keysA, unsigned long long* __restrict__ keysB,
             BucketGeom bg, int* __restrict__ countA, const int* __restrict__ gate, int gate_min, int tiles_x, int tiles_y,
             const __grid_constant__ CUtensorMap tmap, int use_tma, int n_img, int* __restrict__ work, long long key_stride) {
+    pdl_wait();      // the pyramid kernels (level 0) / the threshold-20 pass (gate) in front of this launch are complete
+    pdl_trigger();
     // low-threshold pass of the pipeline: only needed when the retry of vo.cpp:327-332 can happen at all, i.e. when
     // the thr_hi pass left fewer than gate_min buckets with a winner (every such bucket yields one bucketed feature)
     if (gate && gate[blockIdx.z] >= gate_min) return;
@@ -583,13 +620,13 @@ void launch_fast(const uint8_t* img, long long img_stride, int w, int h, int pit
     const int use_tma = make_tile_map(&tmap, img, w, h, pitch, img_stride, n_img, FT_TW, FT_TH) ? 1 : 0;
     const long long ks = key_stride > 0 ? key_stride : (long long)bg.nb;
     if (nt == 256)
-        fast_kernel<256><<<grid, 256, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+        launch_pdl(fast_kernel<256>, grid, dim3(256), st, img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
                                                bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
     else if (nt == 64)
-        fast_kernel<64><<<grid, 64, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+        launch_pdl(fast_kernel<64>, grid, dim3(64), st, img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
                                              bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
     else
-        fast_kernel<128><<<grid, 128, 0, st>>>(img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
+        launch_pdl(fast_kernel<128>, grid, dim3(128), st, img, img_stride, w, h, pitch, thr_lo, thr_hi, resp_map, map_stride, map_pitch, keysA, keysB,
                                                bg, countA, gate, gate_min, tiles_x, tiles_y, tmap, use_tma, n_img, gate ? nullptr : work, ks);
 }
 
@@ -713,6 +750,8 @@ pyrdown_tile_kernel(PyrDownJob j, const __grid_constant__ CUtensorMap map0, cons
                       : *reinterpret_cast<const uint4*>(tileB + r * PD_BW + 16 * (k - 8));
     };
     if (j.use_tma && threadIdx.x == 0) mbar_init(&tma_bar, 1);
+    pdl_wait();      // the level this launch reads is complete
+    pdl_trigger();
     const int cam = j.n_cam == 2 ? (blockIdx.z & 1) : 0, seq = j.n_cam == 2 ? (blockIdx.z >> 1) : blockIdx.z;
     const uint8_t* src = j.src[cam] + (long long)seq * j.src_seq_stride;
     uint8_t* dst = j.dst[cam] + (long long)seq * j.dst_seq_stride;
@@ -893,9 +932,9 @@ static void launch_pyrdown_job(const PyrDownJob& j_in, int n_img, cudaStream_t s
     j.use_tma = j.sw >= 32 && j.sh >= 8;
     for (int cam = 0; cam < (j.n_cam == 2 ? 2 : 1) && j.use_tma; ++cam)
         j.use_tma = make_tile_map(&map[cam], j.src[cam], j.sw, j.sh, j.spitch, j.src_seq_stride, n_pl, PD_BW, th) ? 1 : 0;
-    if (rpt == 4) pyrdown_tile_kernel<4><<<dim3(gx, (j.dh + 15) / 16, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
-    else if (rpt == 2) pyrdown_tile_kernel<2><<<dim3(gx, (j.dh + 7) / 8, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
-    else pyrdown_tile_kernel<1><<<dim3(gx, (j.dh + 3) / 4, n_img), PD_THREADS, 0, st>>>(j, map[0], map[1]);
+    if (rpt == 4) launch_pdl(pyrdown_tile_kernel<4>, dim3(gx, (j.dh + 15) / 16, n_img), dim3(PD_THREADS), st, j, map[0], map[1]);
+    else if (rpt == 2) launch_pdl(pyrdown_tile_kernel<2>, dim3(gx, (j.dh + 7) / 8, n_img), dim3(PD_THREADS), st, j, map[0], map[1]);
+    else launch_pdl(pyrdown_tile_kernel<1>, dim3(gx, (j.dh + 3) / 4, n_img), dim3(PD_THREADS), st, j, map[0], map[1]);
 }
 void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, int spitch, uint8_t* dst,
                     long long dst_stride, int dw, int dh, int dpitch, int n_img, cudaStream_t st) {
@@ -976,7 +1015,8 @@ void launch_pyrdown_cn(const uint8_t* src, int sw, int sh, int spitch, uint8_t* 
 // ---- context ingest into pyramid slot `slot` (host-known ring, frame f -> f % 3)
 int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
-                  cudaStream_t st) {
+                  cudaStream_t st, bool pdl) {
+    PdlScope pdl_scope(pdl);
     int launches = 0;
     const long long ctx_seq_stride = pg.base(1, 0, 0) - pg.base(0, 0, 0);
     if (pg.cn != 1) launches = launch_ingest_cn(d, pg, left, right, stride, seq_stride, slot, st);
@@ -1853,7 +1893,11 @@ struct WarpRedD {
     }
 };
 
-__global__ void __launch_bounds__(HYP_THREADS) pnp_hyp_kernel(DevArrays d, PipeConfig pc, int hyp0) {
+// MINB: resident blocks per SM the kernel is compiled for.  1 (255 registers) is the fastest single hypothesis and what a
+// single sequence gets; a batch of sequences launches 16 x n_seq blocks and is wave bound, so it takes the 168-register
+// build (4 per SM: 64 sequences 709 -> 421 us per frame, one sequence 146 -> 148).
+template <int MINB>
+__global__ void __launch_bounds__(HYP_THREADS, MINB) pnp_hyp_kernel(DevArrays d, PipeConfig pc, int hyp0) {
     __shared__ EpnpWork work;
     __shared__ int sm_cnt[HYP_THREADS / 32];
     const int seq = blockIdx.y;
@@ -2151,8 +2195,13 @@ __global__ void __launch_bounds__(FIN_THREADS) pnp_final_b_kernel(DevArrays d, P
 }
 void launch_pnp_hyp(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     const int first = d.n_hyp < HYP_FIRST ? d.n_hyp : HYP_FIRST;
-    pnp_hyp_kernel<<<dim3(first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, 0);
-    if (d.n_hyp > first) pnp_hyp_kernel<<<dim3(d.n_hyp - first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, first);
+    if (d.n_seq > 1) {
+        pnp_hyp_kernel<4><<<dim3(first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, 0);
+        if (d.n_hyp > first) pnp_hyp_kernel<4><<<dim3(d.n_hyp - first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, first);
+    } else {
+        pnp_hyp_kernel<1><<<dim3(first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, 0);
+        if (d.n_hyp > first) pnp_hyp_kernel<1><<<dim3(d.n_hyp - first, d.n_seq), HYP_THREADS, 0, st>>>(d, pc, first);
+    }
 }
 void launch_pnp_final_a(const DevArrays& d, const PipeConfig& pc, cudaStream_t st) {
     pnp_final_a_kernel<<<d.n_seq, FIN_THREADS, 0, st>>>(d, pc);

@@ -32,7 +32,7 @@ void launch_pyrdown(const uint8_t* src, long long src_stride, int sw, int sh, in
 // fastkeys[slot].  Returns the number of kernel launches.
 int launch_ingest(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
                   const uint8_t* left, const uint8_t* right, int stride, long long seq_stride, int slot,
-                  cudaStream_t st);
+                  cudaStream_t st, bool pdl = false);
 
 // look-ahead ingest of `n_frames` consecutive frames of ONE sequence into ring slots slot0 .. (n_seq == 1, 8UC1)
 int launch_ingest_frames(const DevArrays& d, const PyrGeom& pg, const BucketGeom& bg, const PipeConfig& pc,
