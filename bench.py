@@ -34,7 +34,7 @@ sys.path.insert(0, ROOT)
 W, H = 1241, 376
 PITCH = 1280   # row pitch of the device-resident frames (a multiple of 128 bytes)
 FRAMES_PER_STEP = 400
-E2E_DEPTH = 3
+E2E_DEPTH = int(os.environ.get("SVO_BENCH_DEPTH", "3"))   # frames in flight of the e2e arm
 # dram__bytes_read.sum + dram__bytes_write.sum of the five launches of one 64-frame ingest set, from the round-2
 # ncu --set full capture profiles/r02_ingest_full.raw.csv (rows 0..4): pyrDown 62.00 + 51.77, 15.44 + 0.34, 4.70 + 0.00,
 # FAST 35.51 + 0.06, gated FAST 0.03 MB
