@@ -118,8 +118,10 @@ struct svo_ctx {
     const char* trace_path = nullptr;
     bool pipeline_ctx = true;           // false: private helper context of a stateless call (plain streams, no speculation)
     int klt_blocks_k = 0;               // persistent KLT blocks per sequence on the KLT partition
-    int f_share = 70;                   // % of them given to the FAST-candidate kernel (SVO_FSHARE; measured with the full T grid: 59 %
-                                        // 2749 / 2845, 70 % 2900 / 2953, 80 % 2930-3010 / 2870-3040 frames/s resident / e2e, above that bistable)
+    int f_share = 100;                  // % of them the FAST-candidate kernel is launched with (SVO_FSHARE).  Both speculative passes get the
+                                        // full grid: T's stream has the higher priority and F(f + 1) may not start before T(f) is ready, so
+                                        // T's blocks are placed first and F fills what T leaves (59 % 2749 / 2845, 70 % 2915 / 2980,
+                                        // 85 % 3038 / 3056, 100 % 3094 / 3075 frames/s resident / e2e)
     int t_share = 100;                  // % of them the tracked-feature kernel is launched with (SVO_TSHARE; 0 = 100 - f_share): blocks
                                         // beyond its resident share start as the FAST-candidate kernel's blocks leave
     cudaEvent_t ev_in[SVO_EV_RING] = {};    // ingest(f) complete
