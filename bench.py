@@ -36,9 +36,9 @@ PITCH = 1280   # row pitch of the device-resident frames (a multiple of 128 byte
 FRAMES_PER_STEP = 400
 E2E_DEPTH = int(os.environ.get("SVO_BENCH_DEPTH", "3"))   # frames in flight of the e2e arm
 # dram__bytes_read.sum + dram__bytes_write.sum of the five launches of one 64-frame ingest set, from the round-2
-# ncu --set full capture profiles/r02_ingest_full.raw.csv (rows 0..4): pyrDown 62.00 + 51.77, 15.44 + 0.34, 4.70 + 0.00,
-# FAST 35.51 + 0.06, gated FAST 0.03 MB
-NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 169.85e6 / 64
+# ncu --set full capture profiles/r02_ingest_full.raw.csv (rows 0..4): pyrDown 62.02 + 52.13, 15.44 + 0.37, 4.70 + 0.00,
+# FAST 35.53 + 0.07, gated FAST 0.03 MB
+NCU_INGEST_TRAFFIC_BYTES_PER_FRAME = 170.29e6 / 64
 REF_FRAMES_PER_STEP = 8
 METRIC = "stereo frames/s at KITTI 1241x376"
 
@@ -650,7 +650,7 @@ def run_gpu(args, rank, world, local_rank):
                         "peak_source": peak_src, "frames_per_launch": nfl,
                         "algorithmic_bytes_per_launch_set": B_ALG_FRAME * nfl,
                         "us_per_launch_set": batch["ingest_us_per_launch"],
-                        "limiter": "SM issue (FAST 62 %, pyrDown 50-61 % issue-slot utilisation; FAST is 91 of the 161 us), not HBM: see profiles/r02_ncu_summary.md"}
+                        "limiter": "SM issue (FAST 62 %, pyrDown 50-61 % issue-slot utilisation; FAST is 89 of the 149 us), not HBM: see profiles/r02_ncu_summary.md"}
         else:
             roofline = dict(roofline_single, traffic=None, peak_source=peak_src)
         # one trajectory with look-ahead: K = 8 frames per ingest launch set (svo_submit_frames)
