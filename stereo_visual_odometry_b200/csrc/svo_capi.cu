@@ -244,7 +244,7 @@ static int validate_params(const svo_params* p) {
 // the ingest shares the chain partition; default 16,0 of the 148 SMs: the rest tracks).  Batched contexts are throughput bound and use plain streams on the whole GPU.
 // SVO_SPEC=0/1 overrides whether the speculative tracking runs (default: single-sequence contexts only).
 static int create_streams(svo_ctx* c, const svo_params* p) {
-    int want_chain = 16, want_in = 0;
+    int want_chain = 8, want_in = 0;   // (measured, resident / e2e frames/s: 8 SMs 3186 / 3178, 16 SMs 3093 / 3107, 16 + 8 for the ingest 2986 / 2986)
     c->spec = p->n_seq == 1 && c->pipeline_ctx && channels_of(*p) == 1;   // 8UC3 mode: plain serial frames
     if (const char* e = getenv("SVO_SPEC"))
         if (c->pipeline_ctx && channels_of(*p) == 1) c->spec = atoi(e) != 0;
