@@ -328,8 +328,10 @@ static int create_streams(svo_ctx* c, const svo_params* p) {
             if (dbg) fprintf(stderr, "svo: SM partitions chain %u ingest %u klt %u (groups %u, ok %d)\n", sm_cnt[0], sm_cnt[1], sm_cnt[2], ngrp, (int)ok);
             for (int i = 0; i < 3 && ok; ++i)
                 if (i != 1 || n_in > 0) TRY(p_cuGreenCtxCreate(&gc[i], dc[i], p->device, CU_GREEN_CTX_DEFAULT_STREAM));
-            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[0], gc[0], CU_STREAM_NON_BLOCKING, 0));
-            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[1], gc[0], CU_STREAM_NON_BLOCKING, 0));
+            // the pose chain shares its SMs with the ingest: its blocks are placed first (stream priority; SVO_CHAIN_PRIO=0 for equal)
+            const int chain_prio = getenv("SVO_CHAIN_PRIO") ? atoi(getenv("SVO_CHAIN_PRIO")) : -1;
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[0], gc[0], CU_STREAM_NON_BLOCKING, chain_prio));
+            if (ok) TRY(p_cuGreenCtxStreamCreate(&st[1], gc[0], CU_STREAM_NON_BLOCKING, chain_prio));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[2], n_in > 0 ? gc[1] : gc[0], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[3], gc[2], CU_STREAM_NON_BLOCKING, 0));
             if (ok) TRY(p_cuGreenCtxStreamCreate(&st[4], gc[2], CU_STREAM_NON_BLOCKING, -1));
@@ -429,6 +431,7 @@ static int ctx_init(svo_ctx* c, const svo_params* p, int cap_override) {
     CU(dev_alloc(c, &d.fastkeys, (size_t)2 * c->pg.n_slots * S * c->bg.nb));
     CU(dev_alloc(c, &d.fast_nA, (size_t)c->pg.n_slots * S));
     CU(dev_alloc(c, &d.trackkeys, S * c->bg.nb));
+    CU(dev_alloc(c, &d.tile_cnt, S * 16));
     CU(dev_alloc(c, &d.state, S));
     CU(dev_alloc(c, &d.result, S));
     CU(dev_alloc(c, &d.fs_xy, C));  CU(dev_alloc(c, &d.fs_age, C));  CU(dev_alloc(c, &d.fs_str, C));
@@ -786,7 +789,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
             TraceScope ts(c, "final_a", 3, sP);
             launch_pnp_final_a(c->d, c->pc, sP);
         }
-        c->launches += 7;
+        c->launches += 8;
     }
     if (!tm) {
         CU(cudaEventRecord(c->ev_fa[e], sP));
@@ -817,7 +820,7 @@ static int enqueue_frame(svo_ctx* c, const uint8_t* left, const uint8_t* right, 
     if (c->timers) {
         CU(cudaStreamSynchronize(sP));
         const int nst = first ? 1 : 6;
-        const int nl[6] = {n_ingest, 1, 1, 1, 2, 2};
+        const int nl[6] = {n_ingest, 3, 1, 1, 2, 2};   // bucket = keys + count + merge
         for (int i = 0; i < nst; ++i) {
             float ms = 0.f;
             cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]);

@@ -77,6 +77,7 @@ struct DevArrays {
     unsigned long long* fastkeys;     // [3][2][n_seq][nb]
     int* fast_nA;                     // [3][n_seq] buckets with a thr_hi FAST winner (gates the thr_lo pass)
     unsigned long long* trackkeys;    // [n_seq][nb]
+    int* tile_cnt;                    // [n_seq][16] winners per 1024-bucket tile: without | with the thr/4 FAST set << 16 (bucket_count_kernel)
     SeqState* state;                  // [n_seq]
     svo_frame_result* result;         // [n_seq]
     // tracked feature set (currentVOFeatures)

@@ -1152,11 +1152,14 @@ void launch_first_frame(const DevArrays& d, cudaStream_t st) {
 // ============================================================================
 // bucket merge: tracked features + FAST winners -> bucketed list, incl. the retry.  Two kernels:
 //   bucket_keys_kernel   every tracked feature atomicMax-es its key into its bucket (grid over the features)
-//   bucket_merge_kernel  block t owns buckets [1024 t, 1024 t + 1024): it reads ALL keys once (coalesced, L2
-//                        resident, 350 KB) to count the winners before its tile and in total -- the total decides
-//                        the low-threshold retry (vo.cpp:327-332) -- so the blocks need no inter-block hand-off;
-//                        then one ballot + one block scan order its own winners, which are written together with
-//                        their circular-matching result from the speculative cache (or queued for klt_kernel).
+//   bucket_count_kernel  block t counts the winners of buckets [1024 t, 1024 t + 1024), without and with the
+//                        low-threshold FAST set (two __syncthreads_count)
+//   bucket_merge_kernel  block t owns the same buckets: the 15 tile counts give it the winners before its tile and in
+//                        total -- the total decides the low-threshold retry (vo.cpp:327-332); one block scan orders
+//                        its own winners, which are written together with their circular-matching result from the
+//                        speculative cache (or queued for klt_kernel).  (One kernel in which every block re-counted
+//                        all 14720 x 3 keys took 24 us on 16 SMs and 52 us on the 8-SM chain partition -- on the
+//                        loop that bounds the streaming rate.)
 // The key buffers are cleared by select_kernel (every block here reads all of them).
 __global__ void __launch_bounds__(256) bucket_keys_kernel(DevArrays d, BucketGeom bg) {
     const int seq = blockIdx.y;
@@ -1178,7 +1181,20 @@ __global__ void __launch_bounds__(256) bucket_keys_kernel(DevArrays d, BucketGeo
     if (br >= bg.start_row && br < bg.n_bh && bc >= 0 && bc < bg.n_bw && age < bg.age_threshold)
         atomicMax(keyT + br * bg.n_bw + bc, bucket_key(bucket_score(age, str, bg.fast_threshold), (unsigned)i, str));
 }
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(1024) bucket_count_kernel(DevArrays d, BucketGeom bg, int keybuf) {
+    const int seq = blockIdx.y, b = (blockIdx.x << 10) + threadIdx.x;
+    const unsigned long long* keyT = d.trackkeys + (long long)seq * bg.nb;
+    const unsigned long long* keyA = d.fastkeys + ((long long)(keybuf * 2 + 0) * d.n_seq + seq) * bg.nb;
+    const unsigned long long* keyB = d.fastkeys + ((long long)(keybuf * 2 + 1) * d.n_seq + seq) * bg.nb;
+    bool w1 = false, w2 = false;
+    if (b < bg.nb) {
+        w1 = (ld_key(keyT + b) | ld_key(keyA + b)) != 0ull;
+        w2 = w1 || ld_key(keyB + b) != 0ull;
+    }
+    const int c1 = __syncthreads_count(w1), c2 = __syncthreads_count(w2);
+    if (threadIdx.x == 0) d.tile_cnt[seq * 16 + blockIdx.x] = c1 | (c2 << 16);
+}
+__global__ void __launch_bounds__(1024, 2)   // 32 registers: two blocks per SM, the 15 blocks of a frame fit the 8-SM chain partition
 bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int specbuf, int use_spec) {
     __shared__ int sm[33];
     __shared__ int sm_iters;
@@ -1193,30 +1209,26 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
     int* pred_out = use_spec ? d.predT + ((long long)(specbuf ^ 1) * d.n_seq + seq) * bg.nb : nullptr;
     if (tid == 0) sm_iters = 0;
 
-    // winners without / with the thr/4 FAST set: in total and before this tile (low 16 bits | high 16 bits)
+    // winners without / with the thr/4 FAST set: in total and before this tile (low 16 bits | high 16 bits), from the
+    // per-tile counts of bucket_count_kernel
     const int ntiles = (bg.nb + 1023) >> 10;
-    int tot = 0, pre = 0;   // packed: count(w1 != 0) | count(w1 != 0 || kb != 0) << 16
+    int tot_all = 0, pre_all = 0;   // packed: count(w1 != 0) | count(w1 != 0 || kb != 0) << 16
+    for (int j = 0; j < ntiles; ++j) {
+        const int c = __ldcg(d.tile_cnt + seq * 16 + j);
+        tot_all += c;
+        if (j < tile) pre_all += c;
+    }
     unsigned long long my_w1 = 0ull, my_kb = 0ull;
     bool my_isA = false;
-#pragma unroll 4
-    for (int j = 0; j < ntiles; ++j) {
-        const int b = (j << 10) + tid;
+    {
+        const int b = (tile << 10) + tid;
         if (b < bg.nb) {
-            const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b), kb = ld_key(keyB + b);
-            const unsigned long long w1 = kt > ka ? kt : ka;
-            const int c = ((w1 != 0ull) ? 1 : 0) | (((w1 != 0ull || kb != 0ull) ? 1 : 0) << 16);
-            tot += c;
-            if (j < tile) pre += c;
-            if (j == tile) {
-                my_w1 = w1;
-                my_kb = kb;
-                my_isA = ka != 0ull && !(kt > ka);   // the winner is this bucket's thr-20 FAST winner (cached)
-            }
+            const unsigned long long kt = ld_key(keyT + b), ka = ld_key(keyA + b);
+            my_kb = ld_key(keyB + b);
+            my_w1 = kt > ka ? kt : ka;
+            my_isA = ka != 0ull && !(kt > ka);   // the winner is this bucket's thr-20 FAST winner (cached)
         }
     }
-    int tot_all, pre_all;
-    block_excl_scan<1024>(tot, &tot_all, sm);
-    block_excl_scan<1024>(pre, &pre_all, sm);
     const int n1 = tot_all & 0xFFFF;
     const bool retry = n1 < pc.pre_matching_threshold;   // vo.cpp:327-332
     const int total = retry ? (tot_all >> 16) : n1;
@@ -1304,6 +1316,7 @@ bucket_merge_kernel(DevArrays d, BucketGeom bg, PipeConfig pc, int keybuf, int s
 void launch_bucket_merge(const DevArrays& d, const BucketGeom& bg, const PipeConfig& pc, int keybuf, int specbuf,
                          int use_spec, cudaStream_t st) {
     bucket_keys_kernel<<<dim3((d.cap + 255) / 256, d.n_seq), 256, 0, st>>>(d, bg);
+    bucket_count_kernel<<<dim3((bg.nb + 1023) / 1024, d.n_seq), 1024, 0, st>>>(d, bg, keybuf);
     bucket_merge_kernel<<<dim3((bg.nb + 1023) / 1024, d.n_seq), 1024, 0, st>>>(d, bg, pc, keybuf, specbuf, use_spec);
 }
 
