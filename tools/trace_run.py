@@ -15,8 +15,9 @@ from stereo_visual_odometry_b200._lib import FrameResult, check, default_params,
 
 W, H = 1241, 376
 N = 30
-seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=N, seed=0)
-Ls, Rs = zip(*[seq.render(i) for i in range(N)])
+OFF = int(os.environ.get("TRACE_OFFSET", "0"))   # first frame of the 30-frame window (the bench's 1000-frame sequence gets richer in features)
+seq = synth.make_sequence(width=W, height=H, calib="kitti00", n_frames=max(N + OFF, int(os.environ.get("TRACE_TOTAL", "0"))), seed=0)
+Ls, Rs = zip(*[seq.render(OFF + i) for i in range(N)])
 Lp = torch.from_numpy(np.stack(Ls)).pin_memory()
 Rp = torch.from_numpy(np.stack(Rs)).pin_memory()
 L_ = lib()
